@@ -1,0 +1,151 @@
+/*
+ * mla_preprocess_b200.h — C ABI of the B200 (sm_100a) implementation of sgl-kernel-npu's
+ * `mla_preprocess` operator (DeepSeek-V3 MLA attention prologue).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch types.  The torch operator
+ * `torch.ops.npu.mla_preprocess` (csrc/mlapo_torch_op.cpp) and any other host (ctypes, cgo, JNI ...)
+ * bind exactly these symbols.  All pointers are DEVICE pointers unless stated; all calls are
+ * asynchronous on `stream` (a cudaStream_t passed as void*), never synchronise the host and never
+ * allocate device memory: the caller owns every buffer, including the workspace.
+ *
+ * Reference interface replaced (paths relative to the sgl-kernel-npu tree):
+ *   - operator entry      sglang::npu_kernel::mla_preprocess   csrc/mla_preprocess/op_host/mla_preprocess.cpp:623-704
+ *   - operator schema     csrc/pytorch_extensions.cpp:105-115, include/sgl_kenel_npu_ops.h:102-119
+ *   - device entry        extern "C" mla_preprocess(31 GM_ADDR) csrc/mla_preprocess/op_kernel/mla_preprocess_kernel.cpp:20-25
+ *   - workspace sizing    MlaPreprocessTiling::SetWorkspace     csrc/mla_preprocess/op_host/mla_preprocess.cpp:508-540
+ */
+#ifndef MLA_PREPROCESS_B200_H_
+#define MLA_PREPROCESS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Return codes (0 = success, negative = failure; mlapo_last_error() has the text). */
+#define MLAPO_OK 0
+#define MLAPO_ERR_INVALID_ARG (-1)   /* bad pointer / size / mode value                                  */
+#define MLAPO_ERR_UNSUPPORTED (-2)   /* combination the path does not implement (e.g. fp16 + NZ cache)    */
+#define MLAPO_ERR_WORKSPACE (-3)     /* workspace missing, misaligned or too small                        */
+#define MLAPO_ERR_CUDA (-4)          /* a CUDA runtime call or launch failed                              */
+#define MLAPO_ERR_DRIVER (-5)        /* cuTensorMapEncodeTiled unavailable or failed                      */
+
+/* Activation type of hiddenState / outputs (reference: inDtype, op_host/mla_preprocess.cpp:666). */
+#define MLAPO_ACT_BF16 0
+#define MLAPO_ACT_FP16 1
+
+/* cache_mode values = reference cache_mode_map (op_host/mla_preprocess.cpp:605-606). */
+#define MLAPO_CACHE_KROPE_CTKV 1     /* "krope_ctkv":   ND caches [B,bs,1,512] + [B,bs,1,64]               */
+#define MLAPO_CACHE_INT8_NZ 2        /* "int8_nzcache": NZ caches, int8 k_nope (C0=32) + int8 q_out0       */
+#define MLAPO_CACHE_NZ 3             /* "nzcache":      NZ caches (C0=16)                                  */
+
+/* quant_mode values = reference quant_mode_map (op_host/mla_preprocess.cpp:608-611). */
+#define MLAPO_QUANT_PER_TENSOR_ASYMM 0
+#define MLAPO_QUANT_PER_TOKEN_SYMM 1
+
+/* Fixed dimensions of the path (op_kernel/mla_preprocess.h:55-64). */
+#define MLAPO_MM1_OUT 2112           /* [k_nope 512 | k_pe 64 | q_a 1536] */
+#define MLAPO_KV_LORA 512
+#define MLAPO_ROPE 64
+#define MLAPO_Q_LORA 1536
+#define MLAPO_Q_NOPE 128
+#define MLAPO_Q_HEAD 192
+
+/*
+ * Arguments of one call.  Field names follow the operator schema (csrc/pytorch_extensions.cpp:105-115).
+ * gamma0/beta0 of the schema are not here: the reference binds them and never reads them
+ * (mla_preprocess_mix_bf16.hpp:2762, 424-486 — step 1 is quantisation only).
+ */
+typedef struct MlapoParams {
+  uint32_t struct_bytes;        /* = sizeof(MlapoParams), ABI check                                       */
+  int32_t num_tokens;           /* N  = hiddenState.size(0)        (op_host/mla_preprocess.cpp:658)       */
+  int32_t num_heads;            /* H  = wuk.size(0)                (:659)                                 */
+  int32_t hidden_dim;           /* D  = hiddenState.size(-1), multiple of 128 (:660)                      */
+  int32_t act_dtype;            /* MLAPO_ACT_*                                                            */
+  int32_t cache_mode;           /* MLAPO_CACHE_*                                                          */
+  int32_t quant_mode;           /* MLAPO_QUANT_*                                                          */
+  int32_t num_cache_blocks;     /* B of the cache tensors                                                 */
+  int32_t cache_block_size;     /* bs; must be 128 in the NZ modes (mla_preprocess_mix_bf16.hpp:2549-2550)*/
+  int32_t descale_is_int64;     /* 1: descale0/1 are int64 carrying fp32 bits in the low word (fp16 path) */
+  int32_t reserved0;
+
+  const void* hidden_state;     /* act  [N, D]                                                            */
+  const void* wdqkv_km;         /* int8 [2112, D]   K-major, from mlapo_repack_nz_weight()                */
+  const void* descale0;         /* f32|int64 [2112]                                                       */
+  const void* bias0;            /* int32 [2112]     (ignored in per-token mode)                           */
+  const void* quant_scale0;     /* act  [1]         (per-tensor mode)                                     */
+  const void* quant_offset0;    /* int8 [1]                                                               */
+  const void* gamma1;           /* act  [1536]                                                            */
+  const void* beta1;            /* act  [1536]                                                            */
+  const void* quant_scale1;     /* act  [1]                                                               */
+  const void* quant_offset1;    /* int8 [1]                                                               */
+  const void* wuq_km;           /* int8 [192*H, 1536] K-major, from mlapo_repack_nz_weight()              */
+  const void* descale1;         /* f32|int64 [192*H]                                                      */
+  const void* bias1;            /* int32 [192*H]                                                          */
+  const void* gamma2;           /* act  [512]                                                             */
+  const void* cos;              /* act  [N, 64]                                                           */
+  const void* sin;              /* act  [N, 64]                                                           */
+  const void* wuk;              /* act  [H, 128, 512] ND                                                  */
+  const void* slot_mapping;     /* int32 [N]; -1 = skip the kv side of that token                         */
+  const void* ctkv_scale;       /* act  [1]   required in MLAPO_CACHE_INT8_NZ, else may be NULL           */
+  const void* q_nope_scale;     /* act  [H]   required in MLAPO_CACHE_INT8_NZ, else may be NULL           */
+
+  void* q_out0;                 /* act|int8 [N, H, 512]                                                   */
+  void* q_out1;                 /* act  [N, H, 64]                                                        */
+  void* kv_cache;               /* = kv_cache_out0 (same storage, updated in place)                       */
+  void* kv_cache_rope;          /* = kv_cache_out1                                                        */
+} MlapoParams;
+
+/* Byte offsets of the intermediates inside the workspace (for tests / debugging; 0-based, 256 B aligned). */
+typedef struct MlapoWorkspaceLayout {
+  size_t total_bytes;
+  size_t a0;                    /* int8  [N, D]            quantised hiddenState (reference s1)           */
+  size_t partial0;              /* int32 [splits0, N, 2112] split-K partial sums of MM1 (reference s2)    */
+  size_t a1;                    /* int8  [N, 1536]         quantised q_a (reference s1 reuse)             */
+  size_t q_nope;                /* act   [N, H, 128]       MM2 nope slice before absorption (reference s4)*/
+  size_t tok_scale;             /* f32   [2, N]            per-token scales (reference s5)                */
+  int32_t splits0;              /* split-K factor chosen for MM1                                          */
+  int32_t reserved;
+} MlapoWorkspaceLayout;
+
+/* Library identification; replaces sgl_kernel_npu_version() (csrc/pytorch_extensions.cpp:26-27, csrc/utils/version.h:23-45). */
+const char* mlapo_version(void);
+
+/* Text of the last failure on the calling thread ("" if none). No reference counterpart (TORCH_CHECK messages there). */
+const char* mlapo_last_error(void);
+
+/*
+ * Workspace the call needs (bytes) / where each intermediate lives in it.
+ * Replaces MlaPreprocessTiling::SetWorkspace + the at::empty workspace (op_host/mla_preprocess.cpp:508-540, 677-680).
+ */
+int mlapo_get_workspace_size(const MlapoParams* p, size_t* bytes);
+int mlapo_get_workspace_layout(const MlapoParams* p, MlapoWorkspaceLayout* layout);
+
+/*
+ * Load-time repack of an Ascend FRACTAL_NZ int8 weight [1, K/32, n_out, 32] into the K-major
+ * [n_out, K] layout the TMA descriptors of this library tile with 128-byte swizzle.
+ * Replaces the NZ addressing done inside the reference GEMM (GetOffsetB, mla_preprocess_mix_bf16.hpp:1581-1588);
+ * the test-side packer it inverts is transdata() (tests/python/sgl_kernel_npu/test_mla_preprocess.py:38-54).
+ */
+int mlapo_repack_nz_weight(const void* w_nz, void* w_km, int32_t k, int32_t n_out, void* stream);
+
+/*
+ * The operator.  Enqueues the whole prologue on `stream`:
+ *   quant -> W_DQKV int8 GEMM -> dequant -> { q_a RMSNorm+quant -> W_UQ int8 GEMM -> dequant -> RoPE | W_UK absorb }
+ *                                        -> { latent RMSNorm(512), RoPE(64) -> paged-cache scatter by slot_mapping }.
+ * Replaces sglang::npu_kernel::mla_preprocess (op_host/mla_preprocess.cpp:623-704) and the device entry
+ * mla_preprocess (op_kernel/mla_preprocess_kernel.cpp:20-25).  `workspace` must be 256-byte aligned and at
+ * least mlapo_get_workspace_size() bytes.  num_tokens == 0 is a no-op.  There is no token cap
+ * (the reference's is 1024: op_host/mla_preprocess.cpp:63, 689-695).
+ */
+int mla_preprocess_launch(const MlapoParams* p, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Number of kernels one mla_preprocess_launch() enqueues for these parameters (for launch accounting). */
+int mlapo_launches_per_call(const MlapoParams* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MLA_PREPROCESS_B200_H_ */

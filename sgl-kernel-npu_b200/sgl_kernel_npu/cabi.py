@@ -1,0 +1,221 @@
+"""ctypes binding of the C ABI in include/mla_preprocess_b200.h.
+
+Host-side mirror of the reference operator for callers that do not go through the torch
+dispatcher (tests, bench, other runtimes): `mla_preprocess(...)` below has the argument
+list of `torch.ops.npu.mla_preprocess` (reference csrc/pytorch_extensions.cpp:105-115),
+validates like the op host should (reference op_host/mla_preprocess.cpp:623-704 only checks
+the two mode strings and N) and calls `mla_preprocess_launch` with raw device pointers.
+
+There is no CPU fallback: if the CUDA library is missing, importing this module raises.
+"""
+import ctypes
+import os
+
+import torch
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libmla_preprocess_b200.so")
+
+CACHE_MODE_MAP = {"krope_ctkv": 1, "int8_nzcache": 2, "nzcache": 3}            # op_host/mla_preprocess.cpp:605-606
+QUANT_MODE_MAP = {"per_tensor_quant_asymm": 0, "per_token_quant_symm": 1}      # :608-611
+DEFAULT_CACHE_MODE = "krope_ctkv"                                              # :634
+DEFAULT_QUANT_MODE = "per_token_quant_symm"                                    # :635
+
+EXPORTS = ["mlapo_version", "mlapo_last_error", "mlapo_get_workspace_size", "mlapo_get_workspace_layout",
+           "mlapo_repack_nz_weight", "mla_preprocess_launch", "mlapo_launches_per_call"]
+
+
+class MlapoParams(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_uint32 if n == "struct_bytes" else ctypes.c_int32) for n in (
+        "struct_bytes", "num_tokens", "num_heads", "hidden_dim", "act_dtype", "cache_mode", "quant_mode",
+        "num_cache_blocks", "cache_block_size", "descale_is_int64", "reserved0")] + [
+        (n, ctypes.c_void_p) for n in (
+            "hidden_state", "wdqkv_km", "descale0", "bias0", "quant_scale0", "quant_offset0", "gamma1", "beta1",
+            "quant_scale1", "quant_offset1", "wuq_km", "descale1", "bias1", "gamma2", "cos", "sin", "wuk",
+            "slot_mapping", "ctkv_scale", "q_nope_scale", "q_out0", "q_out1", "kv_cache", "kv_cache_rope")]
+
+
+class MlapoWorkspaceLayout(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_size_t) for n in ("total_bytes", "a0", "partial0", "a1", "q_nope", "tok_scale")] + [
+        ("splits0", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+
+
+def _load():
+    if not os.path.exists(_LIB_PATH):
+        raise ImportError(f"{_LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(there is no CPU fallback for mla_preprocess)")
+    lib = ctypes.CDLL(_LIB_PATH)
+    lib.mlapo_version.restype = ctypes.c_char_p
+    lib.mlapo_last_error.restype = ctypes.c_char_p
+    lib.mlapo_get_workspace_size.argtypes = [ctypes.POINTER(MlapoParams), ctypes.POINTER(ctypes.c_size_t)]
+    lib.mlapo_get_workspace_layout.argtypes = [ctypes.POINTER(MlapoParams), ctypes.POINTER(MlapoWorkspaceLayout)]
+    lib.mlapo_repack_nz_weight.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+    lib.mla_preprocess_launch.argtypes = [ctypes.POINTER(MlapoParams), ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+    lib.mlapo_launches_per_call.argtypes = [ctypes.POINTER(MlapoParams)]
+    lib.mlapo_set_debug_flags.argtypes = [ctypes.c_int]
+    return lib
+
+
+lib = _load()
+
+
+class MlapoError(RuntimeError):
+    pass
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise MlapoError(f"{what} failed ({rc}): {lib.mlapo_last_error().decode()}")
+
+
+def version() -> str:
+    return lib.mlapo_version().decode()
+
+
+def set_debug_flags(flags: int) -> int:
+    """bit0: synchronise + check after each kernel; bit1: also write the y0 tap at the end of the workspace."""
+    return lib.mlapo_set_debug_flags(flags)
+
+
+def _stream_ptr(t: torch.Tensor):
+    return ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def repack_nz_weight(w_nz: torch.Tensor) -> torch.Tensor:
+    """FRACTAL_NZ int8 [1, K/32, n_out, 32] -> K-major [n_out, K] (load-time, once per weight)."""
+    if w_nz.dtype != torch.int8 or w_nz.dim() != 4 or w_nz.shape[0] != 1 or w_nz.shape[3] != 32:
+        raise ValueError(f"expected int8 FRACTAL_NZ weight [1, K/32, n_out, 32], got {tuple(w_nz.shape)} {w_nz.dtype}")
+    if not w_nz.is_cuda or not w_nz.is_contiguous():
+        raise ValueError("weight must be a contiguous CUDA tensor")
+    k, n_out = w_nz.shape[1] * 32, w_nz.shape[2]
+    out = torch.empty((n_out, k), dtype=torch.int8, device=w_nz.device)
+    with torch.cuda.device(w_nz.device):
+        _check(lib.mlapo_repack_nz_weight(w_nz.data_ptr(), out.data_ptr(), k, n_out, _stream_ptr(w_nz)), "mlapo_repack_nz_weight")
+    return out
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def build_params(hiddenState, wdqkv_km, descale0, gamma1, beta1, wuq_km, descale1, gamma2, cos, sin, wuk,
+                 kv_cache, kv_cache_rope, slotmapping, quant_scale0, quant_offset0, bias0, quant_scale1,
+                 quant_offset1, bias1, ctkv_scale, q_nope_scale, cache_mode, quant_mode, q_out0, q_out1) -> MlapoParams:
+    cache_mode = DEFAULT_CACHE_MODE if cache_mode is None else cache_mode
+    quant_mode = DEFAULT_QUANT_MODE if quant_mode is None else quant_mode
+    if cache_mode not in CACHE_MODE_MAP:
+        raise RuntimeError(f"Unsupported cache_mode value: '{cache_mode}'")
+    if quant_mode not in QUANT_MODE_MAP:
+        raise RuntimeError(f"Unsupported quant_mode value: '{quant_mode}'")
+    act = hiddenState.dtype
+    if act not in (torch.bfloat16, torch.float16):
+        raise RuntimeError(f"hiddenState must be bfloat16 or float16, got {act}")
+    n, d = hiddenState.shape
+    h = wuk.shape[0]
+    cm = CACHE_MODE_MAP[cache_mode]
+
+    def need(name, t, dtype, shape=None, optional=False):
+        if t is None:
+            if optional:
+                return
+            raise RuntimeError(f"{name} is required")
+        if not t.is_cuda or t.device != hiddenState.device:
+            raise RuntimeError(f"{name} must be on {hiddenState.device}")
+        if not t.is_contiguous():
+            raise RuntimeError(f"{name} must be contiguous")
+        if dtype is not None and t.dtype != dtype:
+            raise RuntimeError(f"{name} must be {dtype}, got {t.dtype}")
+        if shape is not None and tuple(t.shape) != tuple(shape):
+            raise RuntimeError(f"{name} must have shape {tuple(shape)}, got {tuple(t.shape)}")
+
+    need("hiddenState", hiddenState, act)
+    need("wdqkv (K-major)", wdqkv_km, torch.int8, (2112, d))
+    need("wuq (K-major)", wuq_km, torch.int8, (192 * h, 1536))
+    dsc_dt = descale0.dtype
+    if dsc_dt not in (torch.float32, torch.int64):
+        raise RuntimeError("descale0 must be float32 (bf16 path) or int64 (fp16 path)")
+    need("descale0", descale0, dsc_dt, (2112,))
+    need("descale1", descale1, dsc_dt, (192 * h,))
+    need("gamma1", gamma1, act, (1536,))
+    need("beta1", beta1, act, (1536,))
+    need("gamma2", gamma2, act, (512,))
+    need("cos", cos, act, (n, 64))
+    need("sin", sin, act, (n, 64))
+    need("wuk", wuk, act, (h, 128, 512))
+    need("slotmapping", slotmapping, torch.int32, (n,))
+    per_tensor = QUANT_MODE_MAP[quant_mode] == 0
+    need("quant_scale0", quant_scale0, act, optional=not per_tensor)
+    need("quant_offset0", quant_offset0, torch.int8, optional=not per_tensor)
+    need("bias0", bias0, torch.int32, (2112,), optional=not per_tensor)
+    need("quant_scale1", quant_scale1, act, optional=not per_tensor)
+    need("quant_offset1", quant_offset1, torch.int8, optional=not per_tensor)
+    need("bias1", bias1, torch.int32, (192 * h,), optional=not per_tensor)
+    q0_dt = torch.int8 if cm == 2 else act
+    need("q_out0", q_out0, q0_dt, (n, h, 512))
+    need("q_out1", q_out1, act, (n, h, 64))
+    need("kv_cache", kv_cache, q0_dt)
+    need("kv_cache_rope", kv_cache_rope, act)
+    need("ctkv_scale", ctkv_scale, act, optional=cm != 2)
+    need("q_nope_scale", q_nope_scale, act, (h,), optional=cm != 2)
+    if kv_cache.dim() != 4:
+        raise RuntimeError("kv_cache must be 4-D")
+    if cm == 1:
+        blocks, bs = kv_cache.shape[0], kv_cache.shape[1]
+        if kv_cache.shape[2] * kv_cache.shape[3] != 512 or kv_cache_rope.numel() != blocks * bs * 64:
+            raise RuntimeError("krope_ctkv caches must be [B,bs,1,512] and [B,bs,1,64]")
+    else:
+        blocks, bs = kv_cache.shape[0], kv_cache.shape[2]
+        c0 = 32 if cm == 2 else 16
+        if tuple(kv_cache.shape[1:]) != (512 // c0, 128, c0) or tuple(kv_cache_rope.shape) != (blocks, 4, 128, 16):
+            raise RuntimeError(f"NZ caches must be [B,{512 // c0},128,{c0}] and [B,4,128,16] (block size 128)")
+
+    p = MlapoParams()
+    p.struct_bytes = ctypes.sizeof(MlapoParams)
+    p.num_tokens, p.num_heads, p.hidden_dim = n, h, d
+    p.act_dtype = 0 if act == torch.bfloat16 else 1
+    p.cache_mode, p.quant_mode = cm, QUANT_MODE_MAP[quant_mode]
+    p.num_cache_blocks, p.cache_block_size = blocks, bs
+    p.descale_is_int64 = 1 if dsc_dt == torch.int64 else 0
+    p.hidden_state, p.wdqkv_km, p.descale0, p.bias0 = _ptr(hiddenState), _ptr(wdqkv_km), _ptr(descale0), _ptr(bias0)
+    p.quant_scale0, p.quant_offset0 = _ptr(quant_scale0), _ptr(quant_offset0)
+    p.gamma1, p.beta1 = _ptr(gamma1), _ptr(beta1)
+    p.quant_scale1, p.quant_offset1 = _ptr(quant_scale1), _ptr(quant_offset1)
+    p.wuq_km, p.descale1, p.bias1, p.gamma2 = _ptr(wuq_km), _ptr(descale1), _ptr(bias1), _ptr(gamma2)
+    p.cos, p.sin, p.wuk, p.slot_mapping = _ptr(cos), _ptr(sin), _ptr(wuk), _ptr(slotmapping)
+    p.ctkv_scale, p.q_nope_scale = _ptr(ctkv_scale), _ptr(q_nope_scale)
+    p.q_out0, p.q_out1, p.kv_cache, p.kv_cache_rope = _ptr(q_out0), _ptr(q_out1), _ptr(kv_cache), _ptr(kv_cache_rope)
+    return p
+
+
+def workspace_layout(p: MlapoParams) -> MlapoWorkspaceLayout:
+    l = MlapoWorkspaceLayout()
+    _check(lib.mlapo_get_workspace_layout(ctypes.byref(p), ctypes.byref(l)), "mlapo_get_workspace_layout")
+    return l
+
+
+def launch(p: MlapoParams, workspace: torch.Tensor, stream=None):
+    s = ctypes.c_void_p(stream if stream is not None else torch.cuda.current_stream(workspace.device).cuda_stream)
+    _check(lib.mla_preprocess_launch(ctypes.byref(p), workspace.data_ptr(), workspace.numel() * workspace.element_size(), s),
+           "mla_preprocess_launch")
+
+
+def mla_preprocess(hiddenState, gamma0, beta0, wdqkv_km, descale0, gamma1, beta1, wuq_km, descale1, gamma2,
+                   cos, sin, wuk, kv_cache, kv_cache_rope, slotmapping,
+                   quant_scale0, quant_offset0, bias0, quant_scale1, quant_offset1, bias1, *,
+                   ctkv_scale=None, q_nope_scale=None, cache_mode=None, quant_mode=None,
+                   q_out0, kv_cache_out0, q_out1, kv_cache_out1, workspace=None):
+    """Operator-shaped call through the C ABI.  `wdqkv_km` / `wuq_km` are the repacked (K-major) weights.
+
+    gamma0/beta0 are accepted and ignored, as in the reference (bf16.hpp:2762, 424-486).
+    kv_cache_out0/1 must alias kv_cache/kv_cache_rope (reference test_mla:575-577).
+    Returns (q_out0, kv_cache_out0, q_out1, kv_cache_out1) like op_host/mla_preprocess.cpp:703.
+    """
+    if kv_cache_out0.data_ptr() != kv_cache.data_ptr() or kv_cache_out1.data_ptr() != kv_cache_rope.data_ptr():
+        raise RuntimeError("kv_cache_out0/1 must be the same storage as kv_cache/kv_cache_rope")
+    p = build_params(hiddenState, wdqkv_km, descale0, gamma1, beta1, wuq_km, descale1, gamma2, cos, sin, wuk,
+                     kv_cache, kv_cache_rope, slotmapping, quant_scale0, quant_offset0, bias0, quant_scale1,
+                     quant_offset1, bias1, ctkv_scale, q_nope_scale, cache_mode, quant_mode, q_out0, q_out1)
+    with torch.cuda.device(hiddenState.device):
+        if workspace is None:
+            workspace = torch.empty(max(workspace_layout(p).total_bytes, 256), dtype=torch.uint8, device=hiddenState.device)
+        launch(p, workspace)
+    return q_out0, kv_cache_out0, q_out1, kv_cache_out1
