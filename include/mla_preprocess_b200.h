@@ -145,6 +145,17 @@ int mla_preprocess_launch(const MlapoParams* p, void* workspace, size_t workspac
 /* Number of kernels one mla_preprocess_launch() enqueues for these parameters (for launch accounting). */
 int mlapo_launches_per_call(const MlapoParams* p);
 
+/*
+ * Debug / profiling hooks (process-wide; no reference counterpart — the reference has DEBUG_MODE printf builds only,
+ * CMakeLists.txt:48-53).  flags: bit0 = synchronise and check after every kernel (errors name the kernel),
+ * bit1 = also write the dequantised MM1 rows y0 (act [N,2112]) after the last workspace region,
+ * bit2 = record CUDA events around every kernel of the next launches.  Returns the previous flags.
+ */
+int mlapo_set_debug_flags(int flags);
+/* With bit2 set: per-kernel durations (ms) of the last launch, in launch order; returns how many were written. */
+int mlapo_get_kernel_times_ms(float* out_ms, int cap);
+const char* mlapo_kernel_name(int index);
+
 #ifdef __cplusplus
 }
 #endif

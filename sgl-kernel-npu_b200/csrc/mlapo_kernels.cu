@@ -671,7 +671,22 @@ bmm_absorb_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
 
 // ============================================================================================ host side
 thread_local char g_err[512] = "";
-static int g_debug_flags = 0;  // bit0: sync + check after each kernel; bit1: write the y0 tap
+static int g_debug_flags = 0;  // bit0: sync + check after each kernel; bit1: write the y0 tap; bit2: time each kernel
+constexpr int kMaxKernels = 8;
+static cudaEvent_t g_ev[kMaxKernels + 1];
+static bool g_ev_ready = false;
+static int g_ev_count = 0;  // events recorded by the last launch
+static const char* g_kernel_names[kMaxKernels] = {"quant_hidden", "gemm1_i8_splitk", "norm_rope_cache", "gemm2_i8_rope",
+                                                  "bmm_absorb", "", "", ""};
+static void record_event(int i, cudaStream_t st) {
+  if (!(g_debug_flags & 4)) return;
+  if (!g_ev_ready) {
+    for (int k = 0; k <= kMaxKernels; ++k) cudaEventCreate(&g_ev[k]);
+    g_ev_ready = true;
+  }
+  cudaEventRecord(g_ev[i], st);
+  g_ev_count = i + 1;
+}
 
 static int fail(int code, const char* fmt, ...) {
   va_list ap;
@@ -733,7 +748,7 @@ constexpr int kMm1Stages = 4;
 constexpr int kMm2Stages = 4;
 
 static int choose_splits0(int n_tokens, int hidden_dim) {
-  const int m_tiles = (n_tokens + kBlockM - 1) / kBlockM;
+  const int m_tiles = n_tokens > 0 ? (n_tokens + kBlockM - 1) / kBlockM : 1;
   const int n_tiles = (MLAPO_MM1_OUT + kMm1BlockN - 1) / kMm1BlockN;
   const int kb_total = hidden_dim / kBlockKBytes;
   int s = (2 * 148 + n_tiles * m_tiles / 2) / (n_tiles * m_tiles);
@@ -792,8 +807,12 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   float* tok_scale = reinterpret_cast<float*>(ws + l.tok_scale);
   const CUtensorMapDataType act_dt = std::is_same<T, __nv_bfloat16>::value ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   int rc;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
 
   // ---- k1
+  record_event(0, st);
   if (per_token) {
     quant_hidden_per_token_kernel<T><<<n, 256, 0, st>>>(reinterpret_cast<const T*>(p->hidden_state), a0, tok_scale, d);
   } else {
@@ -805,6 +824,7 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
                                                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec);
   }
   MLAPO_CHECK_LAUNCH("quant_hidden");
+  record_event(1, st);
 
   // ---- k2: MM1, split-K partial sums
   {
@@ -816,16 +836,17 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     ea.n_total = MLAPO_MM1_OUT;
     auto kern = gemm_i8_kernel<T, kMm1BlockN, kMm1Stages, kEpiPartial>;
     constexpr int smem = gemm_smem_bytes<kMm1BlockN>(kMm1Stages);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {};
+    if (!attr_set[dev]) {
       if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
         return fail(MLAPO_ERR_CUDA, "cudaFuncSetAttribute(gemm1): %s", cudaGetErrorString(cudaGetLastError()));
-      attr_set = true;
+      attr_set[dev] = true;
     }
     dim3 grid((MLAPO_MM1_OUT + kMm1BlockN - 1) / kMm1BlockN, l.splits0, m_tiles);
     kern<<<grid, kGemmThreads, smem, st>>>(tm_a, tm_b, ea, n, d / kBlockKBytes);
     MLAPO_CHECK_LAUNCH("gemm1_i8");
   }
+  record_event(2, st);
 
   // ---- k3
   {
@@ -848,6 +869,7 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     norm_rope_cache_kernel<T><<<n, kNormThreads, 0, st>>>(a);
     MLAPO_CHECK_LAUNCH("norm_rope_cache");
   }
+  record_event(3, st);
 
   // ---- k4: MM2 per head + dequant + RoPE
   {
@@ -862,16 +884,17 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     ea.q_nope = q_nope; ea.q_out1 = p->q_out1; ea.num_heads = h;
     auto kern = gemm_i8_kernel<T, MLAPO_Q_HEAD, kMm2Stages, kEpiQ>;
     constexpr int smem = gemm_smem_bytes<MLAPO_Q_HEAD>(kMm2Stages);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {};
+    if (!attr_set[dev]) {
       if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
         return fail(MLAPO_ERR_CUDA, "cudaFuncSetAttribute(gemm2): %s", cudaGetErrorString(cudaGetLastError()));
-      attr_set = true;
+      attr_set[dev] = true;
     }
     dim3 grid(h, 1, m_tiles);
     kern<<<grid, kGemmThreads, smem, st>>>(tm_a, tm_b, ea, n, MLAPO_Q_LORA / kBlockKBytes);
     MLAPO_CHECK_LAUNCH("gemm2_i8_rope");
   }
+  record_event(4, st);
 
   // ---- k5: absorb W_UK
   {
@@ -883,17 +906,18 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     dim3 grid(h, m_tiles);
     if (p->cache_mode == MLAPO_CACHE_INT8_NZ) {
       auto kern = bmm_absorb_kernel<T, true>;
-      static bool attr_set = false;
-      if (!attr_set) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBmmSmemBytes); attr_set = true; }
+      static bool attr_set[64] = {};
+      if (!attr_set[dev]) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBmmSmemBytes); attr_set[dev] = true; }
       kern<<<grid, kGemmThreads, kBmmSmemBytes, st>>>(tm_a, tm_b, ba);
     } else {
       auto kern = bmm_absorb_kernel<T, false>;
-      static bool attr_set = false;
-      if (!attr_set) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBmmSmemBytes); attr_set = true; }
+      static bool attr_set[64] = {};
+      if (!attr_set[dev]) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBmmSmemBytes); attr_set[dev] = true; }
       kern<<<grid, kGemmThreads, kBmmSmemBytes, st>>>(tm_a, tm_b, ba);
     }
     MLAPO_CHECK_LAUNCH("bmm_absorb");
   }
+  record_event(5, st);
   return MLAPO_OK;
 }
 
@@ -912,6 +936,17 @@ int mlapo_set_debug_flags(int flags) {
   g_debug_flags = flags;
   return old;
 }
+
+// Debug/profiling hook (flag bit2): per-kernel durations of the last mla_preprocess_launch on this thread's device.
+int mlapo_get_kernel_times_ms(float* out_ms, int cap) {
+  if (!g_ev_ready || g_ev_count < 2) return 0;
+  if (cudaEventSynchronize(g_ev[g_ev_count - 1]) != cudaSuccess) return fail(MLAPO_ERR_CUDA, "event sync failed");
+  int n = g_ev_count - 1;
+  if (n > cap) n = cap;
+  for (int i = 0; i < n; ++i) cudaEventElapsedTime(&out_ms[i], g_ev[i], g_ev[i + 1]);
+  return n;
+}
+const char* mlapo_kernel_name(int i) { return (i >= 0 && i < kMaxKernels) ? g_kernel_names[i] : ""; }
 
 int mlapo_get_workspace_layout(const MlapoParams* p, MlapoWorkspaceLayout* layout) {
   int rc = check_params(p);
