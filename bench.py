@@ -58,10 +58,9 @@ def kernel_algorithmic_bytes(name, n, h, d, cache_mode):
     q0 = 1 if cache_mode == "int8_nzcache" else 2
     return {
         "quant_hidden": n * d * 2 + n * d,
-        "gemm1_i8_splitk": 2112 * d + n * d + n * 2112 * 4,
+        "mm1_splitk": 2112 * d + n * d + n * 2112 * 4,
         "norm_rope_cache": n * 2112 * 4 + n * 1536 + n * (512 * q0 + 128) + n * 260 + 8 * 2112 + 4 * 1536 + 1024,
-        "gemm2_i8_rope": 1536 * 192 * h + n * 1536 + n * h * (64 + 128) * 2 + 8 * 192 * h + n * 256,
-        "bmm_absorb": 2 * 128 * 512 * h + n * h * 128 * 2 + n * h * 512 * q0,
+        "q_fused": 1536 * 192 * h + 2 * 128 * 512 * h + n * 1536 + n * h * 64 * 2 + n * h * 512 * q0 + 8 * 192 * h + n * 256,
     }.get(name, 0)
 
 

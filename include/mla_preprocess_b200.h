@@ -104,8 +104,8 @@ typedef struct MlapoWorkspaceLayout {
   size_t a0;                    /* int8  [N, D]            quantised hiddenState (reference s1)           */
   size_t partial0;              /* int32 [splits0, N, 2112] split-K partial sums of MM1 (reference s2)    */
   size_t a1;                    /* int8  [N, 1536]         quantised q_a (reference s1 reuse)             */
-  size_t q_nope;                /* act   [N, H, 128]       MM2 nope slice before absorption (reference s4)*/
   size_t tok_scale;             /* f32   [2, N]            per-token scales (reference s5)                */
+  size_t y0_tap;                /* act   [N, 2112]         dequantised MM1 rows (reference s3); only with debug bit1 */
   int32_t splits0;              /* split-K factor chosen for MM1                                          */
   int32_t reserved;
 } MlapoWorkspaceLayout;

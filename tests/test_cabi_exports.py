@@ -46,7 +46,7 @@ def test_struct_size_matches_and_validation_errors():
     assert cabi.lib.mlapo_get_workspace_size(ctypes.byref(p), ctypes.byref(sz)) == 0
     lay = cabi.workspace_layout(p)
     assert lay.total_bytes == sz.value and lay.splits0 >= 1
-    assert lay.a0 % 256 == 0 and lay.partial0 >= 256 * 7168 and lay.q_nope > lay.a1 > lay.partial0
+    assert lay.a0 % 256 == 0 and lay.partial0 >= 256 * 7168 and lay.tok_scale > lay.a1 > lay.partial0
     # empty batch sizes fine on the host side (no division by the tile count)
     p.num_tokens = 0
     assert cabi.lib.mlapo_get_workspace_size(ctypes.byref(p), ctypes.byref(sz)) == 0

@@ -32,7 +32,7 @@ CASES = [
 
 
 def check(res, case):
-    exact = ["a0", "acc0", "y0", "a1", "q_nope_in", "q_out1", "kv_cache", "kv_cache_rope"]
+    exact = ["a0", "acc0", "y0", "a1", "q_out1", "kv_cache", "kv_cache_rope"]
     for k in exact:
         assert res[k][0] == 0, f"{k}: {res[k]}"
     if case.cache_mode == "int8_nzcache":
