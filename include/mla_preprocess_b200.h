@@ -106,6 +106,7 @@ typedef struct MlapoWorkspaceLayout {
   size_t a1;                    /* int8  [N, 1536]         quantised q_a (reference s1 reuse)             */
   size_t tok_scale;             /* f32   [2, N]            per-token scales (reference s5)                */
   size_t y0_tap;                /* act   [N, 2112]         dequantised MM1 rows (reference s3); only with debug bit1 */
+  size_t timeline;              /* int64 [2, 4096, 16]     per-CTA clock marks of mm1_splitk / q_fused; only with debug bit3 */
   int32_t splits0;              /* split-K factor chosen for MM1                                          */
   int32_t reserved;
 } MlapoWorkspaceLayout;
@@ -149,7 +150,8 @@ int mlapo_launches_per_call(const MlapoParams* p);
  * Debug / profiling hooks (process-wide; no reference counterpart — the reference has DEBUG_MODE printf builds only,
  * CMakeLists.txt:48-53).  flags: bit0 = synchronise and check after every kernel (errors name the kernel),
  * bit1 = also write the dequantised MM1 rows y0 (act [N,2112]) after the last workspace region,
- * bit2 = record CUDA events around every kernel of the next launches.  Returns the previous flags.
+ * bit2 = record CUDA events around every kernel of the next launches, bit3 = per-CTA clock marks (timeline region).
+ * Returns the previous flags.
  */
 int mlapo_set_debug_flags(int flags);
 /* With bit2 set: per-kernel durations (ms) of the last launch, in launch order; returns how many were written. */

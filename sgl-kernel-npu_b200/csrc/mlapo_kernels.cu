@@ -73,6 +73,22 @@ __device__ __forceinline__ float load_descale(const void* p, int is_i64, int i) 
   return reinterpret_cast<const float*>(p)[i];
 }
 
+// Debug timeline (flag bit3): per-CTA clock64 marks, 16 slots per CTA, written only when the pointer is non-null.
+__device__ __forceinline__ void tl_mark(long long* tl, int slot) {
+  if (tl) {
+    const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+    tl[cta * 16 + slot] = clock64();
+  }
+}
+__device__ __forceinline__ void tl_mark_global(long long* tl, int slot) {
+  if (tl) {
+    const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    tl[cta * 16 + slot] = (long long)t;
+  }
+}
+
 // ============================================================================================ k0: NZ -> K-major repack
 // FRACTAL_NZ [1, K/32, n_out, 32]: element (n,k) at ((k/32)*n_out + n)*32 + k%32  ->  [n_out, K] row-major.
 __global__ void repack_nz_kernel(const int8_t* __restrict__ nz, int8_t* __restrict__ km, int k, int n_out) {
@@ -163,8 +179,9 @@ constexpr int mm1_smem_bytes() {
 template <int MT>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
-                  const __grid_constant__ CUtensorMap tm_p, int m_total, int kb_total) {
+                  const __grid_constant__ CUtensorMap tm_p, int m_total, int kb_total, long long* tl) {
   constexpr int STAGES = kMm1Stages;
+  if (threadIdx.x == 0) { tl_mark_global(tl, 0); tl_mark(tl, 1); }
   constexpr int A_BYTES = MT * kTile16K;
   constexpr int B_BYTES = kMm1BlockN * kBlockKBytes;
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
@@ -212,6 +229,7 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
   ptx::tc_fence_after();
   const uint32_t tmem_acc = *tmem_slot;
   ptx::griddep_launch_dependents();
+  if (threadIdx.x == 0) tl_mark(tl, 2);  // prologue done
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -224,6 +242,7 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         ptx::tma_load_2d(ptx::smem_u32(smem + i * STAGE_BYTES + A_BYTES), &tm_b, fb, (kb0 + i) * kBlockKBytes, n0, ptx::kEvictFirst);
       }
       ptx::griddep_wait();  // a0 is produced by the quantise kernel
+      tl_mark(tl, 3);       // upstream complete
       for (int i = 0; i < pre; ++i) {
         const uint32_t fb = ptx::smem_u32(full_bar + i);
         for (int m = 0; m < mt_valid; ++m)
@@ -250,6 +269,8 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
       ptx::mbar_wait(ptx::smem_u32(full_bar + stage), phase);
       ptx::tc_fence_after();
       if (lane == 0) {
+        if (i == 0) tl_mark(tl, 4);             // first stage landed
+        if (i == nkb - 1) tl_mark(tl, 5);       // last stage landed
         const uint32_t a_base = ptx::smem_u32(smem + stage * STAGE_BYTES);
         const uint32_t b_base = a_base + A_BYTES;
         for (int m = 0; m < mt_valid; ++m) {
@@ -275,6 +296,7 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     const bool issuer = threadIdx.x == 64;
     ptx::mbar_wait(ptx::smem_u32(done_bar), 0);   // all MMAs retired => every pipeline stage has been consumed
     ptx::tc_fence_after();
+    if (issuer) tl_mark(tl, 6);                   // MMAs retired
     for (int m = 0; m < mt_valid; ++m) {
 #pragma unroll 1
       for (int g = 0; g < 4; ++g) {  // granule = 32 int32 columns = one 128-byte row per token
@@ -295,12 +317,13 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         ptx::tma_store_commit();
       }
     }
-    if (issuer) ptx::tma_store_wait_read<0>();
+    if (issuer) { tl_mark(tl, 7); ptx::tma_store_wait_read<0>(); tl_mark(tl, 8); }
   }
 
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 1) ptx::tmem_dealloc(tmem_acc, TMEM_COLS);
+  if (threadIdx.x == 32) tl_mark(tl, 9);
 }
 
 // ============================================================================================ k3: norms, quant, rope, cache
@@ -521,7 +544,8 @@ template <class T, bool kInt8Out>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__ CUtensorMap tm_wuq,
                const __grid_constant__ CUtensorMap tm_wuk, const __grid_constant__ CUtensorMap tm_out0,
-               const __grid_constant__ CUtensorMap tm_out1, QArgs qa) {
+               const __grid_constant__ CUtensorMap tm_out1, QArgs qa, long long* tl) {
+  if (threadIdx.x == 0) { tl_mark_global(tl, 0); tl_mark(tl, 1); }
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kQBarOff);
@@ -569,6 +593,7 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   ptx::griddep_launch_dependents();
+  if (threadIdx.x == 0) tl_mark(tl, 2);  // prologue done
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -590,6 +615,7 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
       load_b(1);            // weights first (slots 1, 3): independent of the upstream kernel
       load_b(3);
       ptx::griddep_wait();  // a1 is produced by the norm kernel
+      tl_mark(tl, 3);
       load_a(0);
       load_a(2);
       for (int l = 4; l < 28; ++l) {
@@ -616,6 +642,8 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
       ptx::mbar_wait(ptx::smem_u32(slot_full + (lb & 3)), (lb >> 2) & 1);
       ptx::tc_fence_after();
       if (lane == 0) {
+        if (kb == 0) tl_mark(tl, 4);
+        if (kb == kQKBlocks - 1) tl_mark(tl, 5);
         const uint32_t a_base = ptx::smem_u32(smem + kQRingOff + (la & 3) * kQSlotBytes);
         const uint32_t b_base = ptx::smem_u32(smem + kQRingOff + (lb & 3) * kQSlotBytes);
         for (int m = 0; m < num_mt; ++m) {
@@ -683,6 +711,7 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
 
     ptx::mbar_wait(ptx::smem_u32(mm2_done), 0);
     ptx::tc_fence_after();
+    if (issuer) tl_mark(tl, 6);  // MM2 retired
 
     for (int m = 0; m < num_mt; ++m) {
       const int t = tok0 + m * kBlockM + row;
@@ -765,12 +794,15 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
     }
 
     // absorb drains
+    if (issuer) tl_mark(tl, 7);  // epi2 done
     float qs = 1.f;
     if (kInt8Out) qs = Act<T>::to_f(reinterpret_cast<const T*>(qa.q_nope_scale)[head]);
     for (int u = 0; u < num_units; ++u) {
       const int m = u >> 2, c = u & 3;
       ptx::mbar_wait(ptx::smem_u32(unit_full + c), (u >> 2) & 1);
       ptx::tc_fence_after();
+      if (issuer && u == 0) tl_mark(tl, 8);  // first absorb unit ready
+      if (issuer && u == 4) tl_mark(tl, 9);
       const uint32_t acc3 = lane_base + c * 128;
       if (kInt8Out) {
         // S9: int8( fp16( act(acc) * q_nope_scale[h] ) )   (golden test_mla:86-92, 466-470); 128 cols = one 128-byte row
@@ -825,12 +857,13 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
         }
       }
     }
-    if (issuer) ptx::tma_store_wait_read<0>();
+    if (issuer) { tl_mark(tl, 10); ptx::tma_store_wait_read<0>(); tl_mark(tl, 11); }
   }
 
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 1) ptx::tmem_dealloc(tmem, 512);
+  if (threadIdx.x == 32) tl_mark(tl, 12);
 }
 
 // ============================================================================================ host side
@@ -960,7 +993,10 @@ static int compute_layout(const MlapoParams* p, MlapoWorkspaceLayout* l) {
   l->a1 = off;        off = align_up(off + n * MLAPO_Q_LORA, 256);
   l->tok_scale = off; off = align_up(off + 2 * n * 4, 256);
   l->y0_tap = off;
-  l->total_bytes = off + (g_debug_flags & 2 ? align_up(n * MLAPO_MM1_OUT * 2, 256) : 0);
+  if (g_debug_flags & 2) off += align_up(n * MLAPO_MM1_OUT * 2, 256);
+  l->timeline = off;   // flag bit3: 2 kernels x 4096 CTAs x 16 marks
+  if (g_debug_flags & 8) off += 2 * 4096 * 16 * 8;
+  l->total_bytes = off;
   l->splits0 = splits;
   l->reserved = 0;
   return MLAPO_OK;
@@ -988,6 +1024,8 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   const bool per_token = p->quant_mode == MLAPO_QUANT_PER_TOKEN_SYMM;
   const bool int8_out = p->cache_mode == MLAPO_CACHE_INT8_NZ;
   const bool pdl = (g_debug_flags & 5) == 0;  // per-kernel sync/timing wants serialised kernels
+  long long* tl1 = (g_debug_flags & 8) ? reinterpret_cast<long long*>(ws + l.timeline) : nullptr;
+  long long* tl4 = tl1 ? tl1 + 4096 * 16 : nullptr;
   int8_t* a0 = reinterpret_cast<int8_t*>(ws + l.a0);
   int32_t* partial0 = reinterpret_cast<int32_t*>(ws + l.partial0);
   int8_t* a1 = reinterpret_cast<int8_t*>(ws + l.a1);
@@ -1026,12 +1064,12 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
       static bool done[64] = {};
       if ((rc = set_smem_attr(mm1_splitk_kernel<2>, mm1_smem_bytes<2>(), &done[dev], "mm1<2>"))) return rc;
       e__ = launch_k(mm1_splitk_kernel<2>, dim3(n_tiles, l.splits0, (n + 255) / 256), dim3(kGemmThreads), mm1_smem_bytes<2>(), st, pdl,
-                     tm_a, tm_b, tm_p, n, d / kBlockKBytes);
+                     tm_a, tm_b, tm_p, n, d / kBlockKBytes, tl1);
     } else {
       static bool done[64] = {};
       if ((rc = set_smem_attr(mm1_splitk_kernel<1>, mm1_smem_bytes<1>(), &done[dev], "mm1<1>"))) return rc;
       e__ = launch_k(mm1_splitk_kernel<1>, dim3(n_tiles, l.splits0, 1), dim3(kGemmThreads), mm1_smem_bytes<1>(), st, pdl, tm_a, tm_b,
-                     tm_p, n, d / kBlockKBytes);
+                     tm_p, n, d / kBlockKBytes, tl1);
     }
     MLAPO_CHECK_LAUNCH("mm1_splitk");
   }
@@ -1084,11 +1122,11 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     if (int8_out) {
       static bool done[64] = {};
       if ((rc = set_smem_attr(q_fused_kernel<T, true>, kQSmemBytes, &done[dev], "q_fused<int8>"))) return rc;
-      e__ = launch_k(q_fused_kernel<T, true>, grid, dim3(kGemmThreads), kQSmemBytes, st, pdl, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1, qa);
+      e__ = launch_k(q_fused_kernel<T, true>, grid, dim3(kGemmThreads), kQSmemBytes, st, pdl, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, tl4);
     } else {
       static bool done[64] = {};
       if ((rc = set_smem_attr(q_fused_kernel<T, false>, kQSmemBytes, &done[dev], "q_fused"))) return rc;
-      e__ = launch_k(q_fused_kernel<T, false>, grid, dim3(kGemmThreads), kQSmemBytes, st, pdl, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1, qa);
+      e__ = launch_k(q_fused_kernel<T, false>, grid, dim3(kGemmThreads), kQSmemBytes, st, pdl, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, tl4);
     }
     MLAPO_CHECK_LAUNCH("q_fused");
   }

@@ -35,7 +35,7 @@ class MlapoParams(ctypes.Structure):
 
 
 class MlapoWorkspaceLayout(ctypes.Structure):
-    _fields_ = [(n, ctypes.c_size_t) for n in ("total_bytes", "a0", "partial0", "a1", "tok_scale", "y0_tap")] + [
+    _fields_ = [(n, ctypes.c_size_t) for n in ("total_bytes", "a0", "partial0", "a1", "tok_scale", "y0_tap", "timeline")] + [
         ("splits0", ctypes.c_int32), ("reserved", ctypes.c_int32)]
 
 

@@ -1,0 +1,57 @@
+"""GPU diagnostic: per-CTA clock marks of mm1_splitk and q_fused (debug flag bit3). Not a test."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "sgl-kernel-npu_b200")]
+import numpy as np
+import torch
+
+import bench
+from sgl_kernel_npu import cabi
+
+MM1 = ["gtimer", "start", "prologue", "upstream", "first_full", "last_full", "mma_done", "epi_issued", "stores_read", "end"]
+QF = ["gtimer", "start", "prologue", "upstream", "first_full", "last_full", "mm2_done", "epi2_done", "unit0", "unit4", "drain_issued",
+      "stores_read", "end"]
+
+
+def main(workload="c2", pdl=False):
+    n, h, d, cache_mode, _ = bench.WORKLOADS[workload]
+    dev = torch.device("cuda:0")
+    gen = torch.Generator(device=dev).manual_seed(1)
+    sets = [bench.make_weight_set(torch, h, d, dev, gen) for _ in range(3)]
+    hh, ch, sh, slh = bench.make_host_batch(torch, n, d, 64 * 128, 5)
+    hid, cos, sin, sl = (t.to(dev) for t in (hh, ch, sh, slh))
+    kv, kvr = bench.cache_tensors(torch, cache_mode, 64, dev)
+    q0 = torch.zeros((n, h, 512), dtype=torch.int8 if cache_mode == "int8_nzcache" else torch.bfloat16, device=dev)
+    q1 = torch.zeros((n, h, 64), dtype=torch.bfloat16, device=dev)
+    cabi.set_debug_flags(8 | (0 if pdl else 1))
+    ps = []
+    for w in sets:
+        ps.append(cabi.build_params(hid, w["wdqkv_km"], w["descale0"], w["gamma1"], w["beta1"], w["wuq_km"], w["descale1"], w["gamma2"],
+                                    cos, sin, w["wuk"], kv, kvr, sl, w["quant_scale0"], w["quant_offset0"], w["bias0"], w["quant_scale1"],
+                                    w["quant_offset1"], w["bias1"], w["ctkv_scale"], w["q_nope_scale"], cache_mode,
+                                    "per_tensor_quant_asymm", q0, q1))
+    lay = cabi.workspace_layout(ps[0])
+    ws = torch.zeros(lay.total_bytes, dtype=torch.uint8, device=dev)
+    for i in range(6):
+        cabi.launch(ps[i % 3], ws)
+    torch.cuda.synchronize()
+    tl = ws[lay.timeline:lay.timeline + 2 * 4096 * 16 * 8].view(torch.int64).reshape(2, 4096, 16).cpu().numpy()
+    for k, (name, labels) in enumerate([("mm1_splitk", MM1), ("q_fused", QF)]):
+        a = tl[k]
+        used = a[:, 1] != 0
+        a = a[used]
+        print(f"{name}: {a.shape[0]} CTAs; cycles since CTA start (median / p10 / p90 / max):")
+        for j in range(2, len(labels)):
+            dlt = a[:, j] - a[:, 1]
+            dlt = dlt[a[:, j] != 0]
+            if dlt.size:
+                print(f"   {labels[j]:14s} {np.median(dlt):9.0f} {np.percentile(dlt, 10):9.0f} {np.percentile(dlt, 90):9.0f} {dlt.max():9.0f}")
+        g = a[:, 0]
+        print(f"   CTA start skew (globaltimer ns): p50-min {np.median(g) - g.min():.0f}  max-min {g.max() - g.min():.0f}")
+    cabi.set_debug_flags(0)
+
+
+if __name__ == "__main__":
+    main(sys.argv[1] if len(sys.argv) > 1 else "c2", pdl=len(sys.argv) > 2 and sys.argv[2] == "pdl")
