@@ -510,23 +510,27 @@ __global__ void __launch_bounds__(kNormThreads) norm_rope_cache_kernel(NormArgs 
 }
 
 // ============================================================================================ k4: fused per-head q path
-// One CTA per (head, super-tile of up to 256 tokens):
+// One CTA per (head, super-tile of up to 256 tokens = 2 token tiles):
 //   MM2   acc2[m] (int32 [128 x 192], TMEM) = a1[m-tile] . Wuq[head]^T              (PpMatmulW8a8Aic, bf16.hpp:1515-1975)
 //   epi2  dequant (+bias, *descale) -> act; cols 128..191 -> RoPE -> q_out1;         (PpMatmulW8a8Aiv :1981-2361, RopeFp16 :27-244)
 //         cols 0..127 -> act q_nope tile written straight into swizzled smem as the next MMA's A operand
 //   BMM3  acc3 (f32 [128 x 128] per unit, TMEM) = q_nope[m] . Wuk[head][:, chunk]    (PpMatmulEinSum :1074-1513)
 //   epi3  -> act (or int8 re-quant, EinSumQuant :842-1065) -> swizzled smem -> TMA store into q_out0
-// Weights stream exactly once per CTA through a 4-slot x 32 KB ring (Wuq k-blocks, then the four Wuk chunks, which stay).
-// TMEM (512 cols): acc2[0] = [0,192), acc2[1] = [256,448); absorb buffers A..D = [0,128),[128,256),[256,384),[384,512).
-constexpr int kQSlots = 4;
-constexpr int kQSlotBytes = 32768;
-constexpr int kQRingOff = 0;
-constexpr int kQNopeOff = kQSlots * kQSlotBytes;          // 4 x 16 KB: (m, kb) tiles of the absorb A operand
-constexpr int kQStageOff = kQNopeOff + 4 * kTile16K;      // 2 x 16 KB output staging (ping-pong)
-constexpr int kQBarOff = kQStageOff + 2 * kTile16K;
-constexpr int kQSmemBytes = kQBarOff + 256 + 2 * MLAPO_Q_HEAD * 4 + 1024;
+// 10 warps: w0 TMA producer, w1 MMA issuer, w2..w5 epilogue group 0 (token tile 0), w6..w9 epilogue group 1 (token tile 1).
+// Shared memory (224 KB) is one 4-stage MM2 pipeline (A 2x16 KB + B 24 KB per k-block); once MM2 has retired the same
+// bytes are re-used as [Wuk chunks 4x32 KB | q_nope tiles 4x16 KB | output staging 2x16 KB].
+// TMEM (512 cols): acc2[m] = [256m, 256m+192); absorb buffers of tile m = [256m, 256m+128), [256m+128, 256m+256).
+constexpr int kQThreads = 320;
+constexpr int kQStages = 4;
+constexpr int kQStageBytes = 2 * kTile16K + MLAPO_Q_HEAD * kBlockKBytes;  // 57344
+constexpr int kQWukOff = 0;                                 // 4 x 32 KB (two [128 k x 64 n] atoms per 128-column chunk)
+constexpr int kQNopeOff = 4 * 32768;                        // 4 x 16 KB: (m, kb) tiles of the absorb A operand
+constexpr int kQStageOff = kQNopeOff + 4 * kTile16K;        // 2 x 16 KB output staging (one per epilogue group)
+constexpr int kQBarOff = kQStages * kQStageBytes;           // 229376
+static_assert(kQStageOff + 2 * kTile16K == kQBarOff, "smem regions must tile the pipeline exactly");
+constexpr int kQSmemBytes = kQBarOff + 256 + MLAPO_Q_HEAD * 8 + 1024;
 static_assert(kQSmemBytes <= 232448, "q_fused smem");
-constexpr int kQKBlocks = MLAPO_Q_LORA / kBlockKBytes;    // 12
+constexpr int kQKBlocks = MLAPO_Q_LORA / kBlockKBytes;      // 12
 
 struct QArgs {
   const void* descale1;       // [192*H]
@@ -541,7 +545,7 @@ struct QArgs {
 };
 
 template <class T, bool kInt8Out>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(kQThreads, 1)
 q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__ CUtensorMap tm_wuq,
                const __grid_constant__ CUtensorMap tm_wuk, const __grid_constant__ CUtensorMap tm_out0,
                const __grid_constant__ CUtensorMap tm_out1, QArgs qa, long long* tl) {
@@ -549,21 +553,20 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kQBarOff);
-  uint64_t* slot_full = bars;            // [4]
-  uint64_t* slot_empty = bars + 4;       // [4]
+  uint64_t* full_bar = bars;             // [4]  TMA -> MMA
+  uint64_t* empty_bar = bars + 4;        // [4]  MMA -> TMA
   uint64_t* mm2_done = bars + 8;         // [1]
-  uint64_t* qn_ready = bars + 9;         // [2]  epilogue -> MMA: q_nope tile m in smem and acc2[m] drained
-  uint64_t* unit_full = bars + 11;       // [4]  MMA -> epilogue: absorb buffer holds a finished unit
-  uint64_t* buf_empty = bars + 15;       // [4]  epilogue -> MMA: absorb buffer drained
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
-  float* s_descale = reinterpret_cast<float*>(smem + kQBarOff + 256);
-  int32_t* s_bias = reinterpret_cast<int32_t*>(s_descale + MLAPO_Q_HEAD);
+  uint64_t* wuk_full = bars + 9;         // [4]
+  uint64_t* qn_ready = bars + 13;        // [2]  epilogue group m -> MMA: q_nope tile m in smem and acc2[m] drained
+  uint64_t* unit_full = bars + 15;       // [4]  (m*2 + buffer) MMA -> epilogue
+  uint64_t* buf_empty = bars + 19;       // [4]  (m*2 + buffer) epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
+  int2* s_cst = reinterpret_cast<int2*>(smem + kQBarOff + 256);  // per column {bias, descale bits}
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int head = blockIdx.x;
   const int tok0 = blockIdx.y * 256;
   const int num_mt = (qa.m_total - tok0) > kBlockM ? 2 : 1;
-  const int num_units = 4 * num_mt;
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tm_a1);
@@ -574,8 +577,7 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
   }
   if (warp == 1) {
     if (lane == 0) {
-      for (int i = 0; i < 8; ++i) ptx::mbar_init(ptx::smem_u32(bars + i), 1);
-      ptx::mbar_init(ptx::smem_u32(mm2_done), 1);
+      for (int i = 0; i < 13; ++i) ptx::mbar_init(ptx::smem_u32(bars + i), 1);
       ptx::mbar_init(ptx::smem_u32(qn_ready), 128);
       ptx::mbar_init(ptx::smem_u32(qn_ready + 1), 128);
       for (int i = 0; i < 4; ++i) {
@@ -597,39 +599,48 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    // load sequence l = 0..27: l < 24: kb = l/2, even = a1 tiles (A), odd = Wuq k-block (B); l >= 24: Wuk chunk l-24.
     if (lane == 0) {
-      const uint32_t a_tx = (uint32_t)(num_mt * kTile16K), b_tx = MLAPO_Q_HEAD * kBlockKBytes;
-      auto slot_addr = [&](int l) { return ptx::smem_u32(smem + kQRingOff + (l & 3) * kQSlotBytes); };
-      auto load_a = [&](int l) {
-        const uint32_t fb = ptx::smem_u32(slot_full + (l & 3));
-        ptx::mbar_arrive_expect_tx(fb, a_tx);
+      const uint32_t stage_tx = (uint32_t)(num_mt * kTile16K + MLAPO_Q_HEAD * kBlockKBytes);
+      auto load_b = [&](int kb) {
+        const int s = kb & 3;
+        ptx::tma_load_2d(ptx::smem_u32(smem + s * kQStageBytes + 2 * kTile16K), &tm_wuq, ptx::smem_u32(full_bar + s),
+                         kb * kBlockKBytes, head * MLAPO_Q_HEAD, ptx::kEvictFirst);
+      };
+      auto load_a = [&](int kb) {
+        const int s = kb & 3;
         for (int m = 0; m < num_mt; ++m)
-          ptx::tma_load_2d(slot_addr(l) + m * kTile16K, &tm_a1, fb, (l >> 1) * kBlockKBytes, tok0 + m * kBlockM, ptx::kEvictLast);
+          ptx::tma_load_2d(ptx::smem_u32(smem + s * kQStageBytes + m * kTile16K), &tm_a1, ptx::smem_u32(full_bar + s),
+                           kb * kBlockKBytes, tok0 + m * kBlockM, ptx::kEvictLast);
       };
-      auto load_b = [&](int l) {
-        const uint32_t fb = ptx::smem_u32(slot_full + (l & 3));
-        ptx::mbar_arrive_expect_tx(fb, b_tx);
-        ptx::tma_load_2d(slot_addr(l), &tm_wuq, fb, (l >> 1) * kBlockKBytes, head * MLAPO_Q_HEAD, ptx::kEvictFirst);
-      };
-      load_b(1);            // weights first (slots 1, 3): independent of the upstream kernel
-      load_b(3);
+      for (int kb = 0; kb < kQStages; ++kb) {  // weights first: independent of the upstream kernel
+        ptx::mbar_arrive_expect_tx(ptx::smem_u32(full_bar + kb), stage_tx);
+        load_b(kb);
+      }
       ptx::griddep_wait();  // a1 is produced by the norm kernel
       tl_mark(tl, 3);
-      load_a(0);
-      load_a(2);
-      for (int l = 4; l < 28; ++l) {
-        ptx::mbar_wait(ptx::smem_u32(slot_empty + (l & 3)), ((l >> 2) & 1) ^ 1);
-        if (l < 24) {
-          if (l & 1) load_b(l); else load_a(l);
-        } else {
-          const int c = l - 24;  // Wuk chunk: columns [c*128, c*128+128) = two [128 k x 64 n] atoms
-          const uint32_t fb = ptx::smem_u32(slot_full + (l & 3));
-          ptx::mbar_arrive_expect_tx(fb, 2 * kTile16K);
-          for (int at = 0; at < 2; ++at)
-            ptx::tma_load_2d(slot_addr(l) + at * kTile16K, &tm_wuk, fb, c * 128 + at * 64, head * MLAPO_Q_NOPE, ptx::kEvictFirst);
-        }
+      for (int kb = 0; kb < kQStages; ++kb) load_a(kb);
+      for (int kb = kQStages; kb < kQKBlocks; ++kb) {
+        const int s = kb & 3;
+        ptx::mbar_wait(ptx::smem_u32(empty_bar + s), ((kb >> 2) & 1) ^ 1);
+        ptx::mbar_arrive_expect_tx(ptx::smem_u32(full_bar + s), stage_tx);
+        load_b(kb);
+        load_a(kb);
       }
+      // Wuk chunk c -> bytes [32K*c, 32K*c+32K): needs the last use (3rd release, parity 0) of the stages it overlaps
+      auto load_wuk = [&](int c) {
+        const uint32_t fb = ptx::smem_u32(wuk_full + c);
+        ptx::mbar_arrive_expect_tx(fb, 2 * kTile16K);
+        for (int at = 0; at < 2; ++at)
+          ptx::tma_load_2d(ptx::smem_u32(smem + kQWukOff + c * 32768 + at * kTile16K), &tm_wuk, fb, c * 128 + at * 64,
+                           head * MLAPO_Q_NOPE, ptx::kEvictFirst);
+      };
+      ptx::mbar_wait(ptx::smem_u32(empty_bar + 0), 0);
+      load_wuk(0);                                   // [0, 32K)    in stage 0
+      ptx::mbar_wait(ptx::smem_u32(empty_bar + 1), 0);
+      load_wuk(1);                                   // [32K, 64K)  in stages 0, 1
+      load_wuk(2);                                   // [64K, 96K)  in stage 1
+      ptx::mbar_wait(ptx::smem_u32(empty_bar + 2), 0);
+      load_wuk(3);                                   // [96K, 128K) in stages 1, 2
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
@@ -637,15 +648,14 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
     constexpr uint32_t kAFmt = std::is_same<T, __nv_bfloat16>::value ? ptx::kFmtBF16 : ptx::kFmtF16;
     constexpr uint32_t idesc3 = ptx::make_idesc(ptx::kCFmtF32, kAFmt, kAFmt, 0, 1, kBlockM, 128);
     for (int kb = 0; kb < kQKBlocks; ++kb) {
-      const int la = 2 * kb, lb = 2 * kb + 1;
-      ptx::mbar_wait(ptx::smem_u32(slot_full + (la & 3)), (la >> 2) & 1);
-      ptx::mbar_wait(ptx::smem_u32(slot_full + (lb & 3)), (lb >> 2) & 1);
+      const int s = kb & 3;
+      ptx::mbar_wait(ptx::smem_u32(full_bar + s), (kb >> 2) & 1);
       ptx::tc_fence_after();
       if (lane == 0) {
         if (kb == 0) tl_mark(tl, 4);
         if (kb == kQKBlocks - 1) tl_mark(tl, 5);
-        const uint32_t a_base = ptx::smem_u32(smem + kQRingOff + (la & 3) * kQSlotBytes);
-        const uint32_t b_base = ptx::smem_u32(smem + kQRingOff + (lb & 3) * kQSlotBytes);
+        const uint32_t a_base = ptx::smem_u32(smem + s * kQStageBytes);
+        const uint32_t b_base = a_base + 2 * kTile16K;
         for (int m = 0; m < num_mt; ++m) {
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
@@ -654,74 +664,74 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
             ptx::umma_i8(tmem + m * 256, da, db, idesc2, (kb > 0 || k > 0) ? 1u : 0u);
           }
         }
-        ptx::umma_commit(ptx::smem_u32(slot_empty + (la & 3)));
-        ptx::umma_commit(ptx::smem_u32(slot_empty + (lb & 3)));
+        ptx::umma_commit(ptx::smem_u32(empty_bar + s));
       }
       __syncwarp();
     }
     if (lane == 0) ptx::umma_commit(ptx::smem_u32(mm2_done));
     __syncwarp();
-    // absorb units u = (m, c): buffer u&3; Wuk chunk c lives in ring slot c (loads 24..27)
-    for (int u = 0; u < num_units; ++u) {
-      const int m = u >> 2, c = u & 3;
-      if (c == 0) ptx::mbar_wait(ptx::smem_u32(qn_ready + m), 0);
-      if (u == 2 && num_mt == 2) ptx::mbar_wait(ptx::smem_u32(qn_ready + 1), 0);  // buffers C, D overlap acc2[1]
-      if (u >= 4) ptx::mbar_wait(ptx::smem_u32(buf_empty + c), 0);
-      if (m == 0) ptx::mbar_wait(ptx::smem_u32(slot_full + c), 0);                // load 24+c: 7th use of slot c -> parity 0
-      ptx::tc_fence_after();
-      if (lane == 0) {
-        const uint32_t b_base = ptx::smem_u32(smem + kQRingOff + c * kQSlotBytes);
+    // absorb units (c, m): token tile m ping-pongs its own two TMEM buffers over the four Wuk chunks
+    for (int c = 0; c < 4; ++c) {
+      for (int m = 0; m < num_mt; ++m) {
+        const int ub = m * 2 + (c & 1);
+        if (c == 0) ptx::mbar_wait(ptx::smem_u32(qn_ready + m), 0);
+        if (c >= 2) ptx::mbar_wait(ptx::smem_u32(buf_empty + ub), 0);
+        if (m == 0) ptx::mbar_wait(ptx::smem_u32(wuk_full + c), 0);
+        ptx::tc_fence_after();
+        if (lane == 0) {
+          const uint32_t b_base = ptx::smem_u32(smem + kQWukOff + c * 32768);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {  // 8 x UMMA_K(16) = 128
-          const uint32_t a_addr = ptx::smem_u32(smem + kQNopeOff + (m * 2 + (k >> 2)) * kTile16K) + (k & 3) * kUmmaKBytes;
-          const uint64_t da = ptx::make_smem_desc(a_addr, 1024, 0);
-          const uint64_t db = ptx::make_smem_desc(b_base + k * 2048, 1024, kTile16K);  // MN-major: SBO 8 k-rows, LBO next 64-col atom
-          ptx::umma_f16(tmem + c * 128, da, db, idesc3, k > 0 ? 1u : 0u);
+          for (int k = 0; k < 8; ++k) {  // 8 x UMMA_K(16) = 128
+            const uint32_t a_addr = ptx::smem_u32(smem + kQNopeOff + (m * 2 + (k >> 2)) * kTile16K) + (k & 3) * kUmmaKBytes;
+            const uint64_t da = ptx::make_smem_desc(a_addr, 1024, 0);
+            const uint64_t db = ptx::make_smem_desc(b_base + k * 2048, 1024, kTile16K);  // MN-major: SBO 8 k-rows, LBO next 64-col atom
+            ptx::umma_f16(tmem + m * 256 + (c & 1) * 128, da, db, idesc3, k > 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(ptx::smem_u32(unit_full + ub));
         }
-        ptx::umma_commit(ptx::smem_u32(unit_full + c));
+        __syncwarp();
       }
-      __syncwarp();
     }
   } else {
-    // ------------------------------------------------------------------ epilogue warps (128 threads, thread = token row)
+    // ------------------------------------------------------------------ epilogue groups (128 threads each, thread = token row)
+    const int g = (warp - 2) >> 2;           // group = token tile
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
-    const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
-    const int et = threadIdx.x - 64;
+    const int et = threadIdx.x - 64 - g * 128;
     const bool issuer = et == 0;
-    int granule = 0;  // output staging ping-pong counter
-    auto stage_acquire = [&]() -> uint32_t {  // returns the staging tile that may be overwritten now
-      if (issuer) ptx::tma_store_wait_read<1>();
-      ptx::named_bar_sync(1, 128);
-      return ptx::smem_u32(smem + kQStageOff + (granule & 1) * kTile16K);
+    const int bar_id = 1 + g;
+    const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
+    const uint32_t st_tile = ptx::smem_u32(smem + kQStageOff + g * kTile16K);
+    auto stage_acquire = [&]() {  // previous TMA store of this group has finished reading the staging tile
+      if (issuer) ptx::tma_store_wait_read<0>();
+      ptx::named_bar_sync(bar_id, 128);
     };
-    auto stage_publish = [&]() {              // all rows written -> one thread hands the tile to the TMA engine
+    auto stage_publish = [&]() {  // all rows written -> visible to the async proxy
       ptx::fence_proxy_async_smem();
-      ptx::named_bar_sync(1, 128);
-      ++granule;
+      ptx::named_bar_sync(bar_id, 128);
     };
 
-    for (int c = et; c < MLAPO_Q_HEAD; c += 128) {
-      s_descale[c] = load_descale(qa.descale1, qa.descale_is_i64, head * MLAPO_Q_HEAD + c);
-      s_bias[c] = qa.bias1 ? qa.bias1[head * MLAPO_Q_HEAD + c] : 0;
+    if (g == 0) {
+      for (int c = et; c < MLAPO_Q_HEAD; c += 128) {
+        const float dsc = load_descale(qa.descale1, qa.descale_is_i64, head * MLAPO_Q_HEAD + c);
+        s_cst[c] = make_int2(qa.bias1 ? qa.bias1[head * MLAPO_Q_HEAD + c] : 0, __float_as_int(dsc));
+      }
     }
     ptx::griddep_wait();  // tok_scale1 comes from the norm kernel (and keeps the PDL completion chain transitive)
-    ptx::named_bar_sync(1, 128);
-    const bool per_token = qa.tok_scale1 != nullptr;
+    ptx::named_bar_sync(3, 256);
 
-    ptx::mbar_wait(ptx::smem_u32(mm2_done), 0);
-    ptx::tc_fence_after();
-    if (issuer) tl_mark(tl, 6);  // MM2 retired
-
-    for (int m = 0; m < num_mt; ++m) {
+    if (g < num_mt) {
+      const int m = g;
+      const bool per_token = qa.tok_scale1 != nullptr;
       const int t = tok0 + m * kBlockM + row;
       const int tc = t < qa.m_total ? t : qa.m_total - 1;  // clamped row for loads; TMA stores clip rows >= N
       const float ts = per_token ? qa.tok_scale1[tc] : 1.f;
       auto deq = [&](uint32_t acc, int c) -> float {
-        return per_token ? __fmul_rn(__fmul_rn(__int2float_rn((int)acc), s_descale[c]), ts)
-                         : __fmul_rn(__int2float_rn((int)acc + s_bias[c]), s_descale[c]);
+        const int2 cst = s_cst[c];
+        return per_token ? __fmul_rn(__fmul_rn(__int2float_rn((int)acc), __int_as_float(cst.y)), ts)
+                         : __fmul_rn(__int2float_rn((int)acc + cst.x), __int_as_float(cst.y));
       };
-      // cos/sin rows of this token (issued early; consumed after the nope slice)
+      // cos/sin rows of this token (issued before the MM2 wait; consumed after the nope slice)
       uint4 cs[8], sn[8];
       {
         const uint4* cp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(qa.cos) + (long long)tc * 64);
@@ -729,6 +739,11 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
 #pragma unroll
         for (int j = 0; j < 8; ++j) { cs[j] = ptx::ld_global_nc_v4(cp + j); sn[j] = ptx::ld_global_nc_v4(sp + j); }
       }
+
+      ptx::mbar_wait(ptx::smem_u32(mm2_done), 0);
+      ptx::tc_fence_after();
+      if (issuer && g == 0) tl_mark(tl, 6);  // MM2 retired
+
       const uint32_t acc2 = lane_base + m * 256;
       // nope slice -> swizzled A-operand tiles (kb = c0/64)
 #pragma unroll 1
@@ -763,18 +778,18 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
       ptx::tc_fence_before();
       ptx::mbar_arrive(ptx::smem_u32(qn_ready + m));
 
-      const uint32_t st_tile = stage_acquire();
+      stage_acquire();
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
+      for (int gg = 0; gg < 4; ++gg) {
         float c_lo[8], s_lo[8], c_hi[8], s_hi[8];
-        unpack8<T>(cs[g], c_lo);
-        unpack8<T>(sn[g], s_lo);
-        unpack8<T>(cs[g + 4], c_hi);
-        unpack8<T>(sn[g + 4], s_hi);
+        unpack8<T>(cs[gg], c_lo);
+        unpack8<T>(sn[gg], s_lo);
+        unpack8<T>(cs[gg + 4], c_hi);
+        unpack8<T>(sn[gg + 4], s_hi);
         uint32_t wl[4], wh[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-          const int i0 = g * 8 + 2 * u, i1 = i0 + 1;
+          const int i0 = gg * 8 + 2 * u, i1 = i0 + 1;
           // out[i] = x[i]*cos[i] + (-x[i+32])*sin[i];  out[i+32] = x[i+32]*cos[i+32] + x[i]*sin[i+32]   (test_mla:57-67)
           const float a0 = __fadd_rn(__fmul_rn(x[i0], c_lo[2 * u]), __fmul_rn(-x[i0 + 32], s_lo[2 * u]));
           const float a1 = __fadd_rn(__fmul_rn(x[i1], c_lo[2 * u + 1]), __fmul_rn(-x[i1 + 32], s_lo[2 * u + 1]));
@@ -783,81 +798,86 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
           wl[u] = Act<T>::pack(a0, a1);
           wh[u] = Act<T>::pack(b0, b1);
         }
-        ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, g), wl[0], wl[1], wl[2], wl[3]);
-        ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, g + 4), wh[0], wh[1], wh[2], wh[3]);
+        ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, gg), wl[0], wl[1], wl[2], wl[3]);
+        ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, gg + 4), wh[0], wh[1], wh[2], wh[3]);
       }
       stage_publish();
       if (issuer) {
         ptx::tma_store_2d(&tm_out1, st_tile, head * MLAPO_ROPE, tok0 + m * kBlockM);
         ptx::tma_store_commit();
       }
-    }
+      if (issuer && g == 0) tl_mark(tl, 7);  // epi2 done
 
-    // absorb drains
-    if (issuer) tl_mark(tl, 7);  // epi2 done
-    float qs = 1.f;
-    if (kInt8Out) qs = Act<T>::to_f(reinterpret_cast<const T*>(qa.q_nope_scale)[head]);
-    for (int u = 0; u < num_units; ++u) {
-      const int m = u >> 2, c = u & 3;
-      ptx::mbar_wait(ptx::smem_u32(unit_full + c), (u >> 2) & 1);
-      ptx::tc_fence_after();
-      if (issuer && u == 0) tl_mark(tl, 8);  // first absorb unit ready
-      if (issuer && u == 4) tl_mark(tl, 9);
-      const uint32_t acc3 = lane_base + c * 128;
-      if (kInt8Out) {
-        // S9: int8( fp16( act(acc) * q_nope_scale[h] ) )   (golden test_mla:86-92, 466-470); 128 cols = one 128-byte row
-        uint32_t w[32];
-#pragma unroll
-        for (int c0 = 0; c0 < 128; c0 += 32) {
-          uint32_t r[32];
-          ptx::tmem_ld_32x32b_x32(acc3 + c0, r);
-          ptx::tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            int q[4];
-#pragma unroll
-            for (int v = 0; v < 4; ++v) q[v] = sat_i8(__fmul_rn(Act<T>::round(__uint_as_float(r[4 * j + v])), qs));
-            w[(c0 >> 2) + j] = pack4_i8(q[0], q[1], q[2], q[3]);
-          }
-        }
-        ptx::tc_fence_before();
-        if (u + 4 < num_units) ptx::mbar_arrive(ptx::smem_u32(buf_empty + c));
-        const uint32_t st_tile = stage_acquire();
-#pragma unroll
-        for (int j = 0; j < 8; ++j) ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
-        stage_publish();
-        if (issuer) {
-          ptx::tma_store_2d(&tm_out0, st_tile, head * MLAPO_KV_LORA + c * 128, tok0 + m * kBlockM);
-          ptx::tma_store_commit();
-        }
-      } else {
+      // absorb drains
+      float qs = 1.f;
+      if (kInt8Out) qs = Act<T>::to_f(reinterpret_cast<const T*>(qa.q_nope_scale)[head]);
 #pragma unroll 1
-        for (int half = 0; half < 2; ++half) {  // 64 act columns = one 128-byte row per token
+      for (int c = 0; c < 4; ++c) {
+        const int ub = m * 2 + (c & 1);
+        ptx::mbar_wait(ptx::smem_u32(unit_full + ub), (c >> 1) & 1);
+        ptx::tc_fence_after();
+        if (issuer && g == 0 && c == 0) tl_mark(tl, 8);  // first absorb unit ready
+        if (issuer && g == 0 && c == 3) tl_mark(tl, 9);
+        const uint32_t acc3 = lane_base + m * 256 + (c & 1) * 128;
+        if (kInt8Out) {
+          // S9: int8( fp16( act(acc) * q_nope_scale[h] ) )   (golden test_mla:86-92, 466-470); 128 cols = one 128-byte row
           uint32_t w[32];
 #pragma unroll
-          for (int c0 = 0; c0 < 64; c0 += 32) {
+          for (int c0 = 0; c0 < 128; c0 += 32) {
             uint32_t r[32];
-            ptx::tmem_ld_32x32b_x32(acc3 + half * 64 + c0, r);
+            ptx::tmem_ld_32x32b_x32(acc3 + c0, r);
             ptx::tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 16; ++j) w[(c0 >> 1) + j] = Act<T>::pack(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+            for (int j = 0; j < 8; ++j) {
+              int q[4];
+#pragma unroll
+              for (int v = 0; v < 4; ++v) q[v] = sat_i8(__fmul_rn(Act<T>::round(__uint_as_float(r[4 * j + v])), qs));
+              w[(c0 >> 2) + j] = pack4_i8(q[0], q[1], q[2], q[3]);
+            }
           }
-          if (half == 1) {
-            ptx::tc_fence_before();
-            if (u + 4 < num_units) ptx::mbar_arrive(ptx::smem_u32(buf_empty + c));
-          }
-          const uint32_t st_tile = stage_acquire();
+          ptx::tc_fence_before();
+          if (c < 2) ptx::mbar_arrive(ptx::smem_u32(buf_empty + ub));
+          stage_acquire();
 #pragma unroll
           for (int j = 0; j < 8; ++j) ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
           stage_publish();
           if (issuer) {
-            ptx::tma_store_2d(&tm_out0, st_tile, head * MLAPO_KV_LORA + c * 128 + half * 64, tok0 + m * kBlockM);
+            ptx::tma_store_2d(&tm_out0, st_tile, head * MLAPO_KV_LORA + c * 128, tok0 + m * kBlockM);
             ptx::tma_store_commit();
+          }
+        } else {
+#pragma unroll 1
+          for (int half = 0; half < 2; ++half) {  // 64 act columns = one 128-byte row per token
+            uint32_t w[32];
+#pragma unroll
+            for (int c0 = 0; c0 < 64; c0 += 32) {
+              uint32_t r[32];
+              ptx::tmem_ld_32x32b_x32(acc3 + half * 64 + c0, r);
+              ptx::tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 16; ++j) w[(c0 >> 1) + j] = Act<T>::pack(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+            }
+            if (half == 1) {
+              ptx::tc_fence_before();
+              if (c < 2) ptx::mbar_arrive(ptx::smem_u32(buf_empty + ub));
+            }
+            stage_acquire();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+            stage_publish();
+            if (issuer) {
+              ptx::tma_store_2d(&tm_out0, st_tile, head * MLAPO_KV_LORA + c * 128 + half * 64, tok0 + m * kBlockM);
+              ptx::tma_store_commit();
+            }
           }
         }
       }
+      if (issuer) {
+        if (g == 0) tl_mark(tl, 10);
+        ptx::tma_store_wait_read<0>();
+        if (g == 0) tl_mark(tl, 11);
+      }
     }
-    if (issuer) { tl_mark(tl, 10); ptx::tma_store_wait_read<0>(); tl_mark(tl, 11); }
   }
 
   ptx::tc_fence_before();
@@ -1122,11 +1142,11 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     if (int8_out) {
       static bool done[64] = {};
       if ((rc = set_smem_attr(q_fused_kernel<T, true>, kQSmemBytes, &done[dev], "q_fused<int8>"))) return rc;
-      e__ = launch_k(q_fused_kernel<T, true>, grid, dim3(kGemmThreads), kQSmemBytes, st, pdl, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, tl4);
+      e__ = launch_k(q_fused_kernel<T, true>, grid, dim3(kQThreads), kQSmemBytes, st, pdl, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, tl4);
     } else {
       static bool done[64] = {};
       if ((rc = set_smem_attr(q_fused_kernel<T, false>, kQSmemBytes, &done[dev], "q_fused"))) return rc;
-      e__ = launch_k(q_fused_kernel<T, false>, grid, dim3(kGemmThreads), kQSmemBytes, st, pdl, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, tl4);
+      e__ = launch_k(q_fused_kernel<T, false>, grid, dim3(kQThreads), kQSmemBytes, st, pdl, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, tl4);
     }
     MLAPO_CHECK_LAUNCH("q_fused");
   }
