@@ -110,14 +110,29 @@ __global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict_
   ptx::griddep_launch_dependents();
   const float s = Act<T>::to_f(scale[0]);
   const float zp = (float)offset[0];
+  // x / s, correctly rounded, without the generic IEEE-division sequence: x and s both carry <= 11 significant bits
+  // (bf16/fp16), so the exact quotient lies >= 2^-36 (relative) away from every fp32 rounding boundary, while
+  // q1 = fma(fma(-q0, s, x), r, q0) with r = RN(1/s), q0 = RN(x*r) carries a relative error of ~2^-46 before its
+  // final rounding: q1 == RN(x / s).  Guarded to the range where neither r nor the products leave the normal range.
+  const float rcp = __frcp_rn(s);
+  const bool fast = fabsf(s) > 1e-30f && fabsf(s) < 1e30f;
   ptx::griddep_wait();  // a0 may still be read by the previous call's MM1 until its successors have completed
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_vec8; i += (long long)gridDim.x * blockDim.x) {
     const uint4 v = ptx::ld_global_nc_v4(reinterpret_cast<const uint4*>(x) + i);
     float f[8];
     unpack8<T>(v, f);
     int r[8];
+    if (fast) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) r[j] = sat_i8(__fadd_rn(__fdiv_rn(f[j], s), zp));
+      for (int j = 0; j < 8; ++j) {
+        const float q0 = __fmul_rn(f[j], rcp);
+        const float q1 = __fmaf_rn(__fmaf_rn(-q0, s, f[j]), rcp, q0);
+        r[j] = sat_i8(__fadd_rn(q1, zp));
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) r[j] = sat_i8(__fadd_rn(__fdiv_rn(f[j], s), zp));
+    }
     ptx::st_global_v2(q + i * 8, pack4_i8(r[0], r[1], r[2], r[3]), pack4_i8(r[4], r[5], r[6], r[7]));
   }
 }
@@ -374,24 +389,57 @@ __global__ void __launch_bounds__(kNormThreads) norm_rope_cache_kernel(NormArgs 
   ptx::griddep_launch_dependents();
   ptx::griddep_wait();  // partial sums come from the MM1 kernel
   // ---- sum split-K partials (+bias), dequantise, round to act  (S2 of the contract)
+  // All global loads are issued before anything is consumed (the kernel is latency-, not bandwidth-bound).
   float x[8];
+  uint4 g_vec = make_uint4(0, 0, 0, 0), b_vec = make_uint4(0, 0, 0, 0);  // gamma (+beta) or cos/sin of this thread's 8 columns
   {
-    int acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    if (active) {
-      for (int s = 0; s < a.splits; ++s) {
+    constexpr int kMaxSplits = 8;
+    int4 pu[kMaxSplits], pv[kMaxSplits];
+#pragma unroll
+    for (int s = 0; s < kMaxSplits; ++s) {
+      pu[s] = make_int4(0, 0, 0, 0);
+      pv[s] = make_int4(0, 0, 0, 0);
+      if (active && s < a.splits) {
         const int4* p = reinterpret_cast<const int4*>(a.partial + ((long long)s * a.n_tokens + t) * MLAPO_MM1_OUT + col);
-        const int4 u = p[0], v = p[1];
-        acc[0] += u.x; acc[1] += u.y; acc[2] += u.z; acc[3] += u.w;
-        acc[4] += v.x; acc[5] += v.y; acc[6] += v.z; acc[7] += v.w;
+        pu[s] = p[0];
+        pv[s] = p[1];
       }
     }
+    float d[8];
+    int bias[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (a.descale_is_i64) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d[j] = load_descale(a.descale0, 1, col + j);
+    } else {
+      const float4 d0 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(a.descale0) + col);
+      const float4 d1 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(a.descale0) + col + 4);
+      d[0] = d0.x; d[1] = d0.y; d[2] = d0.z; d[3] = d0.w; d[4] = d1.x; d[5] = d1.y; d[6] = d1.z; d[7] = d1.w;
+    }
+    if (a.bias0) {
+      const int4 b0 = *reinterpret_cast<const int4*>(a.bias0 + col), b1 = *reinterpret_cast<const int4*>(a.bias0 + col + 4);
+      bias[0] = b0.x; bias[1] = b0.y; bias[2] = b0.z; bias[3] = b0.w; bias[4] = b1.x; bias[5] = b1.y; bias[6] = b1.z; bias[7] = b1.w;
+    }
+    if (is_nope) {
+      g_vec = reinterpret_cast<const uint4*>(a.gamma2)[tid];
+    } else if (is_pe) {
+      g_vec = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.cos) + (long long)t * 64)[lane & 7];
+      b_vec = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.sin) + (long long)t * 64)[lane & 7];
+    } else {
+      g_vec = reinterpret_cast<const uint4*>(a.gamma1)[tid - 96];
+      b_vec = reinterpret_cast<const uint4*>(a.beta1)[tid - 96];
+    }
     const float ts0 = a.tok_scale0 ? a.tok_scale0[t] : 1.f;
+    int acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int s = 0; s < kMaxSplits; ++s) {
+      acc[0] += pu[s].x; acc[1] += pu[s].y; acc[2] += pu[s].z; acc[3] += pu[s].w;
+      acc[4] += pv[s].x; acc[5] += pv[s].y; acc[6] += pv[s].z; acc[7] += pv[s].w;
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float d = load_descale(a.descale0, a.descale_is_i64, col + j);
       float y;
-      if (a.tok_scale0) y = __fmul_rn(__fmul_rn(__int2float_rn(acc[j]), d), ts0);
-      else y = __fmul_rn(__int2float_rn(acc[j] + a.bias0[col + j]), d);
+      if (a.tok_scale0) y = __fmul_rn(__fmul_rn(__int2float_rn(acc[j]), d[j]), ts0);
+      else y = __fmul_rn(__int2float_rn(acc[j] + bias[j]), d[j]);
       x[j] = Act<T>::round(y);
     }
     if (a.y0_tap && active) {
@@ -421,7 +469,7 @@ __global__ void __launch_bounds__(kNormThreads) norm_rope_cache_kernel(NormArgs 
     const float var = __fdiv_rn(__double2float_rn(tot_nope), 512.f);
     const float rs = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var, 1e-6f)));
     float g[8];
-    unpack8<T>(reinterpret_cast<const uint4*>(a.gamma2)[tid], g);
+    unpack8<T>(g_vec, g);
     float y[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) y[j] = __fmul_rn(__fmul_rn(x[j], rs), g[j]);
@@ -449,8 +497,8 @@ __global__ void __launch_bounds__(kNormThreads) norm_rope_cache_kernel(NormArgs 
     if (lane < 8) {
       const int c = lane * 8;  // column within the 64 rope lanes
       float cs[8], sn[8];
-      unpack8<T>(reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.cos) + (long long)t * 64)[lane], cs);
-      unpack8<T>(reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.sin) + (long long)t * 64)[lane], sn);
+      unpack8<T>(g_vec, cs);
+      unpack8<T>(b_vec, sn);
       float y[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -474,8 +522,8 @@ __global__ void __launch_bounds__(kNormThreads) norm_rope_cache_kernel(NormArgs 
     const float var = __fdiv_rn(__double2float_rn(tot_q), 1536.f);
     const float rs = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var, 1e-6f)));
     float g[8], b[8];
-    unpack8<T>(reinterpret_cast<const uint4*>(a.gamma1)[tid - 96], g);
-    unpack8<T>(reinterpret_cast<const uint4*>(a.beta1)[tid - 96], b);
+    unpack8<T>(g_vec, g);
+    unpack8<T>(b_vec, b);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       yq[j] = __fadd_rn(__fmul_rn(__fmul_rn(x[j], rs), g[j]), b[j]);
@@ -706,6 +754,10 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
       if (issuer) ptx::tma_store_wait_read<0>();
       ptx::named_bar_sync(bar_id, 128);
     };
+    auto stage_acquire_pp = [&]() {  // ping-pong variant: only the store before the most recent one must have been read
+      if (issuer) ptx::tma_store_wait_read<1>();
+      ptx::named_bar_sync(bar_id, 128);
+    };
     auto stage_publish = [&]() {  // all rows written -> visible to the async proxy
       ptx::fence_proxy_async_smem();
       ptx::named_bar_sync(bar_id, 128);
@@ -861,12 +913,17 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
               ptx::tc_fence_before();
               if (c < 2) ptx::mbar_arrive(ptx::smem_u32(buf_empty + ub));
             }
-            stage_acquire();
+            // unit_full(c) implies every MMA of chunk c-1 has retired, so Wuk slot c-1 is dead: its g-th 16 KB tile
+            // becomes this group's second staging buffer (first half -> own tile, second half -> dead slot).
+            uint32_t dst = st_tile;
+            if (c >= 1 && half == 1) dst = ptx::smem_u32(smem + kQWukOff + (c - 1) * 32768 + g * kTile16K);
+            if (c >= 2 || (c == 1 && half == 1)) stage_acquire_pp();  // the newest outstanding store reads the other buffer
+            else stage_acquire();
 #pragma unroll
-            for (int j = 0; j < 8; ++j) ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+            for (int j = 0; j < 8; ++j) ptx::st_shared_v4(dst + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
             stage_publish();
             if (issuer) {
-              ptx::tma_store_2d(&tm_out0, st_tile, head * MLAPO_KV_LORA + c * 128 + half * 64, tok0 + m * kBlockM);
+              ptx::tma_store_2d(&tm_out0, dst, head * MLAPO_KV_LORA + c * 128 + half * 64, tok0 + m * kBlockM);
               ptx::tma_store_commit();
             }
           }
