@@ -106,7 +106,8 @@ __global__ void repack_nz_kernel(const int8_t* __restrict__ nz, int8_t* __restri
 // ============================================================================================ k1: quantise hiddenState
 template <class T>
 __global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict__ q, const T* __restrict__ scale,
-                                    const int8_t* __restrict__ offset, long long n_vec8) {
+                                    const int8_t* __restrict__ offset, long long n_vec8, long long* tl) {
+  if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 0);
   ptx::griddep_launch_dependents();
   const float s = Act<T>::to_f(scale[0]);
   const float zp = (float)offset[0];
@@ -135,6 +136,7 @@ __global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict_
     }
     ptx::st_global_v2(q + i * 8, pack4_i8(r[0], r[1], r[2], r[3]), pack4_i8(r[4], r[5], r[6], r[7]));
   }
+  if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 15);
 }
 
 // per-token symmetric (UNPINNED restatement of bf16.hpp:437-475): one block per row
@@ -338,7 +340,7 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 1) ptx::tmem_dealloc(tmem_acc, TMEM_COLS);
-  if (threadIdx.x == 32) tl_mark(tl, 9);
+  if (threadIdx.x == 32) { tl_mark(tl, 9); tl_mark_global(tl, 15); }
 }
 
 // ============================================================================================ k3: norms, quant, rope, cache
@@ -361,6 +363,7 @@ struct NormArgs {
   void* kv_cache; void* kv_cache_rope;
   int cache_mode;
   long long cache_slots;    // num_blocks * block_size
+  long long* tl;            // debug timeline or null
 };
 
 constexpr int kNormThreads = 288;  // warps 0-1: k_nope (512), warp 2 lanes 0-7: k_pe (64), warps 3-8: q_a (1536)
@@ -386,8 +389,10 @@ __global__ void __launch_bounds__(kNormThreads) norm_rope_cache_kernel(NormArgs 
   else if (is_pe) col = 512 + (lane & 7) * 8;
   else col = 576 + (tid - 96) * 8;
 
+  if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 0);
   ptx::griddep_launch_dependents();
   ptx::griddep_wait();  // partial sums come from the MM1 kernel
+  if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 14);
   // ---- sum split-K partials (+bias), dequantise, round to act  (S2 of the contract)
   // All global loads are issued before anything is consumed (the kernel is latency-, not bandwidth-bound).
   float x[8];
@@ -555,6 +560,7 @@ __global__ void __launch_bounds__(kNormThreads) norm_rope_cache_kernel(NormArgs 
     for (int j = 0; j < 8; ++j) q[j] = sat_i8(__fadd_rn(__fdiv_rn(yq[j], s), zp));
     ptx::st_global_v2(a.a1 + (long long)t * MLAPO_Q_LORA + (col - 576), pack4_i8(q[0], q[1], q[2], q[3]), pack4_i8(q[4], q[5], q[6], q[7]));
   }
+  if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 15);
 }
 
 // ============================================================================================ k4: fused per-head q path
@@ -614,7 +620,8 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int head = blockIdx.x;
   const int tok0 = blockIdx.y * 256;
-  const int num_mt = (qa.m_total - tok0) > kBlockM ? 2 : 1;
+  const int num_mt = (qa.m_total - tok0) > kBlockM ? 2 : 1;       // token tiles with valid rows in this CTA
+  const int load_mt = qa.m_total > kBlockM ? 2 : 1;               // token tiles fetched per stage (uniform over the grid)
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tm_a1);
@@ -648,17 +655,16 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      const uint32_t stage_tx = (uint32_t)(num_mt * kTile16K + MLAPO_Q_HEAD * kBlockKBytes);
+      const uint32_t stage_tx = (uint32_t)(load_mt * kTile16K + MLAPO_Q_HEAD * kBlockKBytes);
       auto load_b = [&](int kb) {
         const int s = kb & 3;
         ptx::tma_load_2d(ptx::smem_u32(smem + s * kQStageBytes + 2 * kTile16K), &tm_wuq, ptx::smem_u32(full_bar + s),
                          kb * kBlockKBytes, head * MLAPO_Q_HEAD, ptx::kEvictFirst);
       };
-      auto load_a = [&](int kb) {
+      auto load_a = [&](int kb) {  // one box = all token tiles of the stage (box rows = 128 * load_mt)
         const int s = kb & 3;
-        for (int m = 0; m < num_mt; ++m)
-          ptx::tma_load_2d(ptx::smem_u32(smem + s * kQStageBytes + m * kTile16K), &tm_a1, ptx::smem_u32(full_bar + s),
-                           kb * kBlockKBytes, tok0 + m * kBlockM, ptx::kEvictLast);
+        ptx::tma_load_2d(ptx::smem_u32(smem + s * kQStageBytes), &tm_a1, ptx::smem_u32(full_bar + s), kb * kBlockKBytes, tok0,
+                         ptx::kEvictLast);
       };
       for (int kb = 0; kb < kQStages; ++kb) {  // weights first: independent of the upstream kernel
         ptx::mbar_arrive_expect_tx(ptx::smem_u32(full_bar + kb), stage_tx);
@@ -940,7 +946,7 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 1) ptx::tmem_dealloc(tmem, 512);
-  if (threadIdx.x == 32) tl_mark(tl, 12);
+  if (threadIdx.x == 32) { tl_mark(tl, 12); tl_mark_global(tl, 15); }
 }
 
 // ============================================================================================ host side
@@ -1071,8 +1077,8 @@ static int compute_layout(const MlapoParams* p, MlapoWorkspaceLayout* l) {
   l->tok_scale = off; off = align_up(off + 2 * n * 4, 256);
   l->y0_tap = off;
   if (g_debug_flags & 2) off += align_up(n * MLAPO_MM1_OUT * 2, 256);
-  l->timeline = off;   // flag bit3: 2 kernels x 4096 CTAs x 16 marks
-  if (g_debug_flags & 8) off += 2 * 4096 * 16 * 8;
+  l->timeline = off;   // flag bit3: 4 kernels (mm1, q_fused, quant, norm) x 4096 CTAs x 16 marks
+  if (g_debug_flags & 8) off += 4 * 4096 * 16 * 8;
   l->total_bytes = off;
   l->splits0 = splits;
   l->reserved = 0;
@@ -1103,6 +1109,8 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   const bool pdl = (g_debug_flags & 5) == 0;  // per-kernel sync/timing wants serialised kernels
   long long* tl1 = (g_debug_flags & 8) ? reinterpret_cast<long long*>(ws + l.timeline) : nullptr;
   long long* tl4 = tl1 ? tl1 + 4096 * 16 : nullptr;
+  long long* tl0 = tl1 ? tl1 + 2 * 4096 * 16 : nullptr;
+  long long* tl3 = tl1 ? tl1 + 3 * 4096 * 16 : nullptr;
   int8_t* a0 = reinterpret_cast<int8_t*>(ws + l.a0);
   int32_t* partial0 = reinterpret_cast<int32_t*>(ws + l.partial0);
   int8_t* a1 = reinterpret_cast<int8_t*>(ws + l.a1);
@@ -1124,7 +1132,7 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     int blocks = (int)((nvec + 255) / 256);
     if (blocks > num_sms() * 8) blocks = num_sms() * 8;
     e__ = launch_k(quant_hidden_kernel<T>, dim3(blocks), dim3(256), 0, st, pdl, reinterpret_cast<const T*>(p->hidden_state), a0,
-                   reinterpret_cast<const T*>(p->quant_scale0), reinterpret_cast<const int8_t*>(p->quant_offset0), nvec);
+                   reinterpret_cast<const T*>(p->quant_scale0), reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, tl0);
   }
   MLAPO_CHECK_LAUNCH("quant_hidden");
   record_event(1, st);
@@ -1170,6 +1178,7 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     a.kv_cache = p->kv_cache; a.kv_cache_rope = p->kv_cache_rope;
     a.cache_mode = p->cache_mode;
     a.cache_slots = (long long)p->num_cache_blocks * p->cache_block_size;
+    a.tl = tl3;
     e__ = launch_k(norm_rope_cache_kernel<T>, dim3(n), dim3(kNormThreads), 0, st, pdl, a);
     MLAPO_CHECK_LAUNCH("norm_rope_cache");
   }
@@ -1178,7 +1187,8 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   // ---- k4: fused MM2 + dequant + RoPE + W_UK absorb, one CTA per (head, 256-token super-tile)
   {
     CUtensorMap tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1;
-    if ((rc = make_tmap(&tm_a1, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a1, n, MLAPO_Q_LORA, MLAPO_Q_LORA, kBlockM, 128))) return rc;
+    const int a1_box_rows = (n > kBlockM ? 2 : 1) * kBlockM;  // one box per stage covers every token tile of the CTA
+    if ((rc = make_tmap(&tm_a1, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a1, n, MLAPO_Q_LORA, MLAPO_Q_LORA, a1_box_rows, 128))) return rc;
     if ((rc = make_tmap(&tm_wuq, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wuq_km, (uint64_t)h * MLAPO_Q_HEAD, MLAPO_Q_LORA, MLAPO_Q_LORA,
                         MLAPO_Q_HEAD, 128))) return rc;
     if ((rc = make_tmap(&tm_wuk, act_dt, 2, p->wuk, (uint64_t)h * MLAPO_Q_NOPE, MLAPO_KV_LORA, MLAPO_KV_LORA * 2, 128, 64))) return rc;

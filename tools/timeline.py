@@ -37,7 +37,30 @@ def main(workload="c2", pdl=False):
     for i in range(6):
         cabi.launch(ps[i % 3], ws)
     torch.cuda.synchronize()
-    tl = ws[lay.timeline:lay.timeline + 2 * 4096 * 16 * 8].view(torch.int64).reshape(2, 4096, 16).cpu().numpy()
+    if pdl:  # steady state as the bench runs it: a CUDA graph of back-to-back calls, PDL edges inside
+        gs = torch.cuda.Stream(dev)
+        with torch.cuda.stream(gs):
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=gs):
+                for i in range(6):
+                    cabi.launch(ps[i % 3], ws, gs.cuda_stream)
+            gr.replay()
+            gr.replay()
+        torch.cuda.synchronize()
+    tl = ws[lay.timeline:lay.timeline + 4 * 4096 * 16 * 8].view(torch.int64).reshape(4, 4096, 16).cpu().numpy()
+    # whole-call picture from the global timer: [kernel] first CTA start .. last CTA end, relative to the quant kernel's start
+    spans = {}
+    for k, name in [(2, "quant_hidden"), (0, "mm1_splitk"), (3, "norm_rope_cache"), (1, "q_fused")]:
+        a = tl[k]
+        a = a[a[:, 0] != 0]
+        if a.shape[0]:
+            spans[name] = (a[:, 0].min(), np.median(a[:, 0]), a[:, 15].max(), a[:, 14].max() if k == 3 else 0)
+    if spans:
+        t0 = spans["quant_hidden"][0]
+        print("call timeline (us from quant start): kernel first-CTA-start / median-CTA-start / last-CTA-end")
+        for name, (a0, am, a1, w) in spans.items():
+            extra = f"  upstream-wait passed by {(w - t0) / 1e3:7.2f}" if w else ""
+            print(f"   {name:16s} {(a0 - t0) / 1e3:7.2f} {(am - t0) / 1e3:7.2f} {(a1 - t0) / 1e3:7.2f}{extra}")
     for k, (name, labels) in enumerate([("mm1_splitk", MM1), ("q_fused", QF)]):
         a = tl[k]
         used = a[:, 1] != 0
