@@ -37,10 +37,58 @@ WORKLOADS = {
     "c1": (8, 16, 7168, "krope_ctkv", "DeepSeek-V3 MLA preprocess decode, batch 8, 16 heads (TP8 slice), W8A8, paged block 128"),
     "c2": (256, 128, 7168, "krope_ctkv", "DeepSeek-V3 MLA preprocess decode, batch 256, 128 heads, single B200, paged KV block 128"),
     "c3": (8192, 128, 7168, "krope_ctkv", "DeepSeek-V3 MLA preprocess prefill, 8192 tokens, 128 heads, single B200"),
-    "c4": (512, 16, 7168, "krope_ctkv", "DeepSeek-V3 head-sharded TP=8 slice, decode batch 512, 16 heads per rank"),
+    "c4": (512, 128, 7168, "krope_ctkv", "DeepSeek-V3 head-sharded TP=n_gpus decode batch 512, 128 heads split over ranks, W_UQ/W_UK column-sharded, no collective"),
     "c5": (128, 64, 7168, "int8_nzcache", "Kimi-K2 (64 heads) DP-attention rank, batch 128, ragged slot_mapping, int8_nzcache"),
 }
 METRIC = "MLA-preprocess tokens/s/GPU (DSV3 shapes); % of HBM / INT8-TC roofline"
+TP_WORKLOADS = {"c4"}   # heads sharded over ranks (strong scaling); every other workload runs one replica per rank (weak)
+
+
+# ----------------------------------------------------------------------------------------------- multi-rank plumbing
+def rank_env():
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+
+
+def shard_heads(h_total, world, rank):
+    """TP: rank r owns heads [r*H/tp, (r+1)*H/tp); H must divide evenly."""
+    if h_total % world:
+        raise ValueError(f"{h_total} heads do not split over {world} ranks")
+    per = h_total // world
+    return rank * per, (rank + 1) * per
+
+
+def job_tokens(n_tokens, world, sharding):
+    """Tokens the whole job processes per step: replicas each take their own batch; TP ranks share one batch."""
+    return n_tokens if sharding == "tp" else n_tokens * world
+
+
+class Ranks:
+    """Barrier + max-over-ranks; the data path itself has no collective."""
+
+    def __init__(self, backend="nccl", device=None):
+        self.rank, self.world, self.local = rank_env()
+        self.dist, self.device = None, device
+        if self.world > 1:
+            import torch.distributed as dist
+            kw = {"device_id": device} if (backend == "nccl" and device is not None) else {}
+            dist.init_process_group(backend, **kw)
+            self.dist = dist
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+
+    def max(self, values):
+        if self.dist is None:
+            return [float(v) for v in values]
+        import torch
+        t = torch.tensor(list(values), dtype=torch.float64, device=self.device if self.device is not None else "cpu")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return [float(v) for v in t]
+
+    def close(self):
+        if self.dist is not None:
+            self.dist.destroy_process_group()
 
 
 def algorithmic_bytes(n, h, d, cache_mode):
@@ -168,19 +216,18 @@ def run_ours(args):
     import torch
     from sgl_kernel_npu import cabi   # raises if the CUDA library is missing: no fallback
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
+    rank, world, local = rank_env()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (the product path has no CPU fallback)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
+    ranks = Ranks("nccl", dev)
+    sharding = "tp" if args.workload in TP_WORKLOADS else "replica"
 
     n, h, d, cache_mode, desc = WORKLOADS[args.workload]
+    if sharding == "tp":
+        h0, h1 = shard_heads(h, world, rank)
+        h = h1 - h0           # synthetic weights: each rank simply draws its own head slice
     quant_mode = "per_tensor_quant_asymm"
     bf = torch.bfloat16
     q0_dt = torch.int8 if cache_mode == "int8_nzcache" else bf
@@ -244,9 +291,7 @@ def run_ours(args):
             for i in range(k):
                 step(i)
 
-    def barrier():
-        if dist is not None:
-            dist.barrier()
+    barrier = ranks.barrier
 
     run_steps(max(args.warmup, 3))
     torch.cuda.synchronize(dev)
@@ -319,14 +364,11 @@ def run_ours(args):
             kernels[cabi.lib.mlapo_kernel_name(j).decode()] = v / kcount * 1e3   # us
 
     # ---- reduce over ranks (max time)
-    if dist is not None:
-        tt = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms, e2e_ms = float(tt[0]), float(tt[1])
+    ms, e2e_ms = ranks.max([ms, e2e_ms])
 
     if rank == 0:
         peak, peak_src = load_peaks()
-        tokens_total = n * world
+        tokens_total = job_tokens(n, world, sharding)
         value = tokens_total * args.steps / (ms * 1e-3)
         e2e_value = tokens_total * e2e_steps / (e2e_ms * 1e-3)
         step_us = ms * 1e3 / args.steps
@@ -349,10 +391,12 @@ def run_ours(args):
         op_ach = op_bytes / (step_us * 1e-6) / 1e9
         line = {
             "metric": METRIC, "value": round(value, 1), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 6), "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 6), "higher_is_better": True,
+            "scaling": "strong" if sharding == "tp" else "weak",
             "vs_baseline": None, "dtype": "s8 x s8 -> s32 (MM1/MM2), bf16 -> f32 (absorb), bf16 activations", "data": "synthetic",
-            "config": {"workload": desc, "id": args.workload, "tokens_per_gpu": n, "heads": h, "hidden": d, "cache_mode": cache_mode,
-                       "quant_mode": quant_mode, "sharding": "replicas (DP-attention), no collective" if world > 1 else "single GPU",
+            "config": {"workload": desc, "id": args.workload, "tokens_per_gpu": n, "heads_per_gpu": h, "hidden": d, "cache_mode": cache_mode,
+                       "quant_mode": quant_mode, "sharding": ("single GPU" if world == 1 else "heads split over ranks (TP), no collective" if sharding == "tp"
+                                    else "replicas (DP-attention), no collective"),
                        "l2": f"weights rotate over {n_sets} sets = {n_sets * set_bytes / 1e6:.0f} MB > 126 MB L2; no explicit flush",
                        "launch": launch_mode},
             "e2e": {"value": round(e2e_value, 1), "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -368,8 +412,7 @@ def run_ours(args):
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args.workload, budget_s=20.0)
         print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
+    ranks.close()
 
 
 # ----------------------------------------------------------------------------------------------- CPU legs (oracle port)
