@@ -143,6 +143,34 @@ int mlapo_repack_nz_weight(const void* w_nz, void* w_km, int32_t k, int32_t n_ou
  */
 int mla_preprocess_launch(const MlapoParams* p, void* workspace, size_t workspace_bytes, void* stream);
 
+/*
+ * The same operator for hosts that cannot hand over a workspace.  (No counterpart in the reference: its host always
+ * allocates a fresh workspace tensor per call, op_host/mla_preprocess.cpp:677-680.)
+ *
+ * mla_preprocess_launch() leaves the workspace to you, which normally means a cudaMalloc or a framework allocator call.
+ * Some integrations have neither at the point where they run this operator: a serving engine that claimed the whole
+ * device for its own KV-cache pool at start-up and has no bytes left to ask the driver for; a request loop that must not
+ * risk the device-wide stall a driver allocation can cause; a plugin interface that only passes inputs and outputs and
+ * offers no scratch argument or allocator handle.  For them the library carries its own scratch: one fixed array of
+ * MLAPO_STATIC_SCRATCH_BYTES in device global memory, part of the loaded module, present on every GPU that loads this
+ * library from load until the process exits.  This entry point uses that array as the workspace and otherwise behaves
+ * exactly like mla_preprocess_launch(): same parameters, same kernels, same results, asynchronous on `stream`.  It never
+ * calls cudaMalloc/cudaFree or any allocating routine.
+ *
+ * Limits: num_tokens <= MLAPO_STATIC_MAX_TOKENS and hidden_dim <= MLAPO_STATIC_MAX_HIDDEN (any head count); anything
+ * that would need more than the array returns MLAPO_ERR_WORKSPACE with a message naming the sizes, and nothing is launched.
+ * First use: the first call on each device looks the array's device address up once (the device that owns the buffers in
+ * `p` must be current, as for every call); make that first call during warm-up, before any stream capture.
+ * Sharing: there is one array per device and every call uses it, so two calls that can overlap on the GPU (different
+ * streams, or different host threads driving the same device) race on it — keep calls to this entry point on one stream
+ * or order them yourself.  The array keeps whatever the previous call left in it; that is harmless because every byte
+ * the operator reads from its workspace is written earlier in the same call, so nothing has to be cleared between calls.
+ */
+#define MLAPO_STATIC_MAX_TOKENS 256
+#define MLAPO_STATIC_MAX_HIDDEN 8192
+#define MLAPO_STATIC_SCRATCH_BYTES (20u << 20)
+int mla_preprocess_launch_static(const MlapoParams* p, void* stream);
+
 /* Number of kernels one mla_preprocess_launch() enqueues for these parameters (for launch accounting). */
 int mlapo_launches_per_call(const MlapoParams* p);
 

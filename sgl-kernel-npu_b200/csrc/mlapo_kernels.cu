@@ -1226,6 +1226,12 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
 // ============================================================================================ C ABI
 using namespace mlapo;
 
+// Scratch for mla_preprocess_launch_static(): lives in the module's global memory on every device that loads the library.
+// In host code this name is only a handle for cudaGetSymbolAddress(); it is not a device address.
+static __device__ __align__(256) unsigned char g_static_scratch[MLAPO_STATIC_SCRATCH_BYTES];
+static void* g_static_scratch_addr[64];  // device address of the array, per device ordinal, resolved on first use
+static std::mutex g_static_scratch_mutex;
+
 extern "C" {
 
 const char* mlapo_version(void) { return "mla_preprocess_b200 0.1.0 (sm_100a; tcgen05+TMA; reference sgl-kernel-npu f425bdf1)"; }
@@ -1280,6 +1286,41 @@ int mlapo_repack_nz_weight(const void* w_nz, void* w_km, int32_t k, int32_t n_ou
   cudaError_t e__ = cudaSuccess;
   MLAPO_CHECK_LAUNCH("repack_nz");
   return MLAPO_OK;
+}
+
+// Operator call for hosts that cannot allocate (see the header): the workspace is the library's own fixed device array.
+// Everything the kernels read from the workspace (a0, the split-K partial sums, a1, the per-token scales) is produced
+// earlier in the same call for exactly the rows and columns that are read, so stale contents from the previous call are
+// never observed and nothing is cleared here.  Calls that overlap on the GPU share the array and would race.
+int mla_preprocess_launch_static(const MlapoParams* p, void* stream) {
+  int rc = check_params(p);
+  if (rc) return rc;
+  if (p->num_tokens == 0) return MLAPO_OK;
+  MlapoWorkspaceLayout l;
+  compute_layout(p, &l);
+  if (p->num_tokens > MLAPO_STATIC_MAX_TOKENS || p->hidden_dim > MLAPO_STATIC_MAX_HIDDEN || l.total_bytes > (size_t)MLAPO_STATIC_SCRATCH_BYTES)
+    return fail(MLAPO_ERR_WORKSPACE,
+                "mla_preprocess_launch_static: %d tokens x hidden %d need %zu workspace bytes; the built-in scratch holds %u bytes "
+                "(at most %d tokens, hidden <= %d) - use mla_preprocess_launch() with your own workspace",
+                p->num_tokens, p->hidden_dim, l.total_bytes, (unsigned)MLAPO_STATIC_SCRATCH_BYTES, MLAPO_STATIC_MAX_TOKENS,
+                MLAPO_STATIC_MAX_HIDDEN);
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(MLAPO_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= 64) return fail(MLAPO_ERR_UNSUPPORTED, "device ordinal %d out of range for the built-in scratch table", dev);
+  void* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+    if (!g_static_scratch_addr[dev]) {  // first call on this device: resolve the array's address in this device's module image
+      void* addr = nullptr;
+      e = cudaGetSymbolAddress(&addr, g_static_scratch);
+      if (e != cudaSuccess || !addr)
+        return fail(MLAPO_ERR_CUDA, "cudaGetSymbolAddress(built-in scratch) on device %d: %s", dev, cudaGetErrorString(e));
+      g_static_scratch_addr[dev] = addr;
+    }
+    scratch = g_static_scratch_addr[dev];
+  }
+  return mla_preprocess_launch(p, scratch, (size_t)MLAPO_STATIC_SCRATCH_BYTES, stream);
 }
 
 int mla_preprocess_launch(const MlapoParams* p, void* workspace, size_t workspace_bytes, void* stream) {

@@ -21,7 +21,7 @@ DEFAULT_CACHE_MODE = "krope_ctkv"                                              #
 DEFAULT_QUANT_MODE = "per_token_quant_symm"                                    # :635
 
 EXPORTS = ["mlapo_version", "mlapo_last_error", "mlapo_get_workspace_size", "mlapo_get_workspace_layout",
-           "mlapo_repack_nz_weight", "mla_preprocess_launch", "mlapo_launches_per_call"]
+           "mlapo_repack_nz_weight", "mla_preprocess_launch", "mla_preprocess_launch_static", "mlapo_launches_per_call"]
 
 
 class MlapoParams(ctypes.Structure):
@@ -50,6 +50,7 @@ def _load():
     lib.mlapo_get_workspace_layout.argtypes = [ctypes.POINTER(MlapoParams), ctypes.POINTER(MlapoWorkspaceLayout)]
     lib.mlapo_repack_nz_weight.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
     lib.mla_preprocess_launch.argtypes = [ctypes.POINTER(MlapoParams), ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+    lib.mla_preprocess_launch_static.argtypes = [ctypes.POINTER(MlapoParams), ctypes.c_void_p]
     lib.mlapo_launches_per_call.argtypes = [ctypes.POINTER(MlapoParams)]
     lib.mlapo_set_debug_flags.argtypes = [ctypes.c_int]
     return lib
@@ -196,6 +197,21 @@ def launch(p: MlapoParams, workspace: torch.Tensor, stream=None):
     s = ctypes.c_void_p(stream if stream is not None else torch.cuda.current_stream(workspace.device).cuda_stream)
     _check(lib.mla_preprocess_launch(ctypes.byref(p), workspace.data_ptr(), workspace.numel() * workspace.element_size(), s),
            "mla_preprocess_launch")
+
+
+STATIC_MAX_TOKENS, STATIC_MAX_HIDDEN, STATIC_SCRATCH_BYTES = 256, 8192, 20 << 20   # MLAPO_STATIC_* in the header
+
+
+def launch_static(p: MlapoParams, device, stream=None):
+    """`mla_preprocess_launch_static`: the operator with the library's built-in scratch instead of a caller workspace.
+
+    For hosts that have no way to allocate one (all device memory already pledged to their own pool, no allocator in
+    the call path, or a driver allocation is not acceptable inside the request loop).  Up to 256 tokens at hidden <= 8192;
+    larger calls raise MlapoError and launch nothing.  All calls on a device share the one scratch array, so keep them on a
+    single stream; make the first call per device during warm-up, before capturing anything."""
+    s = ctypes.c_void_p(stream if stream is not None else torch.cuda.current_stream(device).cuda_stream)
+    with torch.cuda.device(device):
+        _check(lib.mla_preprocess_launch_static(ctypes.byref(p), s), "mla_preprocess_launch_static")
 
 
 def mla_preprocess(hiddenState, gamma0, beta0, wdqkv_km, descale0, gamma1, beta1, wuq_km, descale1, gamma2,
