@@ -596,6 +596,7 @@ struct QArgs {
   int num_heads;
   int m_total;
   int descale_is_i64;
+  int cta_tokens;             // 256 (two token tiles per CTA, weights streamed once per 256 tokens) or 128 (more CTAs when heads are few)
 };
 
 template <class T, bool kInt8Out>
@@ -619,9 +620,9 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int head = blockIdx.x;
-  const int tok0 = blockIdx.y * 256;
-  const int num_mt = (qa.m_total - tok0) > kBlockM ? 2 : 1;       // token tiles with valid rows in this CTA
-  const int load_mt = qa.m_total > kBlockM ? 2 : 1;               // token tiles fetched per stage (uniform over the grid)
+  const int tok0 = blockIdx.y * qa.cta_tokens;
+  const int num_mt = (qa.cta_tokens > kBlockM && (qa.m_total - tok0) > kBlockM) ? 2 : 1;  // token tiles with valid rows in this CTA
+  const int load_mt = (qa.cta_tokens > kBlockM && qa.m_total > kBlockM) ? 2 : 1;          // token tiles fetched per stage (uniform over the grid)
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tm_a1);
@@ -1187,7 +1188,10 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   // ---- k4: fused MM2 + dequant + RoPE + W_UK absorb, one CTA per (head, 256-token super-tile)
   {
     CUtensorMap tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1;
-    const int a1_box_rows = (n > kBlockM ? 2 : 1) * kBlockM;  // one box per stage covers every token tile of the CTA
+    // Two token tiles per CTA stream each head's weights once per 256 tokens; when that leaves most SMs idle (few heads,
+    // e.g. a TP slice) one tile per CTA doubles the CTA count at the price of re-reading the head's weights from L2.
+    const int cta_tokens = (n > kBlockM && (long long)h * ((n + 255) / 256) >= 96) ? 256 : 128;
+    const int a1_box_rows = cta_tokens > kBlockM ? 2 * kBlockM : kBlockM;  // one box per stage covers every token tile of the CTA
     if ((rc = make_tmap(&tm_a1, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a1, n, MLAPO_Q_LORA, MLAPO_Q_LORA, a1_box_rows, 128))) return rc;
     if ((rc = make_tmap(&tm_wuq, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wuq_km, (uint64_t)h * MLAPO_Q_HEAD, MLAPO_Q_LORA, MLAPO_Q_LORA,
                         MLAPO_Q_HEAD, 128))) return rc;
@@ -1204,8 +1208,8 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     qa.bias1 = per_token ? nullptr : reinterpret_cast<const int32_t*>(p->bias1);
     qa.tok_scale1 = per_token ? tok_scale + n : nullptr;
     qa.cos = p->cos; qa.sin = p->sin; qa.q_nope_scale = p->q_nope_scale;
-    qa.num_heads = h; qa.m_total = n;
-    dim3 grid(h, (n + 255) / 256);
+    qa.num_heads = h; qa.m_total = n; qa.cta_tokens = cta_tokens;
+    dim3 grid(h, (n + cta_tokens - 1) / cta_tokens);
     if (int8_out) {
       static bool done[64] = {};
       if ((rc = set_smem_attr(q_fused_kernel<T, true>, kQSmemBytes, &done[dev], "q_fused<int8>"))) return rc;
