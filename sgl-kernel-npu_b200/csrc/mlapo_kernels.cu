@@ -104,7 +104,7 @@ __global__ void repack_nz_kernel(const int8_t* __restrict__ nz, int8_t* __restri
 }
 
 // ============================================================================================ k1: quantise hiddenState
-template <class T>
+template <class T, int U>
 __global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict__ q, const T* __restrict__ scale,
                                     const int8_t* __restrict__ offset, long long n_vec8, long long* tl) {
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 0);
@@ -118,23 +118,32 @@ __global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict_
   const float rcp = __frcp_rn(s);
   const bool fast = fabsf(s) > 1e-30f && fabsf(s) < 1e30f;
   ptx::griddep_wait();  // a0 may still be read by the previous call's MM1 until its successors have completed
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_vec8; i += (long long)gridDim.x * blockDim.x) {
-    const uint4 v = ptx::ld_global_nc_v4(reinterpret_cast<const uint4*>(x) + i);
-    float f[8];
-    unpack8<T>(v, f);
-    int r[8];
-    if (fast) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < n_vec8; i0 += stride * U) {
+    uint4 v[U];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float q0 = __fmul_rn(f[j], rcp);
-        const float q1 = __fmaf_rn(__fmaf_rn(-q0, s, f[j]), rcp, q0);
-        r[j] = sat_i8(__fadd_rn(q1, zp));
+    for (int u = 0; u < U; ++u)  // all loads of the batch are issued before any is consumed
+      if (i0 + u * stride < n_vec8) v[u] = ptx::ld_global_nc_v4(reinterpret_cast<const uint4*>(x) + i0 + u * stride);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i >= n_vec8) break;
+      float f[8];
+      unpack8<T>(v[u], f);
+      int r[8];
+      if (fast) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float q0 = __fmul_rn(f[j], rcp);
+          const float q1 = __fmaf_rn(__fmaf_rn(-q0, s, f[j]), rcp, q0);
+          r[j] = sat_i8(__fadd_rn(q1, zp));
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = sat_i8(__fadd_rn(__fdiv_rn(f[j], s), zp));
       }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) r[j] = sat_i8(__fadd_rn(__fdiv_rn(f[j], s), zp));
+      ptx::st_global_v2(q + i * 8, pack4_i8(r[0], r[1], r[2], r[3]), pack4_i8(r[4], r[5], r[6], r[7]));
     }
-    ptx::st_global_v2(q + i * 8, pack4_i8(r[0], r[1], r[2], r[3]), pack4_i8(r[4], r[5], r[6], r[7]));
   }
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 15);
 }
@@ -185,25 +194,29 @@ constexpr int kBlockM = 128;
 constexpr int kBlockKBytes = 128;  // one 128B swizzle atom along K
 constexpr int kUmmaKBytes = 32;    // K per tcgen05.mma for 8-bit (32 elems) and 16-bit (16 elems) operands
 constexpr int kTile16K = 16384;    // [128 rows x 128 B] swizzled tile
-constexpr int kMm1BlockN = 128;
-constexpr int kMm1Stages = 4;
+constexpr int kMm1BlockN = 128;   // decode: 17 weight tiles x up to 8 K-splits fill one wave
+constexpr int kMm1BlockNWide = 256;  // prefill (no split-K): 256 x 256 CTA tiles halve the activation re-reads per weight byte
 
-template <int MT>
+template <int MT, int BN>
+__host__ __device__ constexpr int mm1_stages() { return (MT * kTile16K + BN * kBlockKBytes) > 49152 ? 3 : 4; }
+template <int MT, int BN>
 constexpr int mm1_smem_bytes() {
-  return kMm1Stages * (MT * kTile16K + kMm1BlockN * kBlockKBytes) + 256 + 1024;
+  return mm1_stages<MT, BN>() * (MT * kTile16K + BN * kBlockKBytes) + 256 + 1024;
 }
 
-template <int MT>
+template <int MT, int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                   const __grid_constant__ CUtensorMap tm_p, int m_total, int kb_total, long long* tl) {
-  constexpr int STAGES = kMm1Stages;
+  constexpr int STAGES = mm1_stages<MT, BN>();
   if (threadIdx.x == 0) { tl_mark_global(tl, 0); tl_mark(tl, 1); }
   constexpr int A_BYTES = MT * kTile16K;
-  constexpr int B_BYTES = kMm1BlockN * kBlockKBytes;
+  constexpr int B_BYTES = BN * kBlockKBytes;
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  constexpr int TMEM_COLS = MT * kMm1BlockN;  // 128 or 256
-  static_assert(MT * 4 * kTile16K <= STAGES * STAGE_BYTES, "epilogue staging must fit in the drained pipeline");
+  constexpr int TMEM_COLS = MT * BN;          // 128, 256 or 512
+  constexpr int GRANULES = BN / 32;           // 32 int32 columns = one 128-byte row per token
+  static_assert(TMEM_COLS <= 512 && (TMEM_COLS & (TMEM_COLS - 1)) == 0, "TMEM allocation");
+  static_assert(GRANULES * kTile16K <= STAGES * STAGE_BYTES, "one token tile of epilogue staging must fit in the drained pipeline");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -214,7 +227,7 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * kMm1BlockN;
+  const int n0 = blockIdx.x * BN;
   const int split = blockIdx.y, splits = gridDim.y;
   const int m0 = blockIdx.z * (MT * kBlockM);
   const int kb0 = (int)(((long long)split * kb_total) / splits);
@@ -280,7 +293,7 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (one thread)
-    constexpr uint32_t idesc = ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, kBlockM, kMm1BlockN);
+    constexpr uint32_t idesc = ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, kBlockM, BN);
     uint32_t stage = 0, phase = 0;
     for (int i = 0; i < nkb; ++i) {
       ptx::mbar_wait(ptx::smem_u32(full_bar + stage), phase);
@@ -295,7 +308,7 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
           for (int k = 0; k < kBlockKBytes / kUmmaKBytes; ++k) {
             const uint64_t da = ptx::make_smem_desc(a_base + m * kTile16K + k * kUmmaKBytes, 1024, 0);
             const uint64_t db = ptx::make_smem_desc(b_base + k * kUmmaKBytes, 1024, 0);
-            ptx::umma_i8(tmem_acc + m * kMm1BlockN, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            ptx::umma_i8(tmem_acc + m * BN, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
         }
         ptx::umma_commit(ptx::smem_u32(empty_bar + stage));  // frees the smem slot when these MMAs retire
@@ -315,12 +328,16 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
     ptx::tc_fence_after();
     if (issuer) tl_mark(tl, 6);                   // MMAs retired
     for (int m = 0; m < mt_valid; ++m) {
+      if (m > 0) {  // the staging tiles are re-used per token tile: the previous tile's stores must have been read
+        if (issuer) ptx::tma_store_wait_read<0>();
+        ptx::named_bar_sync(1, 128);
+      }
 #pragma unroll 1
-      for (int g = 0; g < 4; ++g) {  // granule = 32 int32 columns = one 128-byte row per token
+      for (int g = 0; g < GRANULES; ++g) {
         uint32_t r[32];
-        ptx::tmem_ld_32x32b_x32(t_base + m * kMm1BlockN + g * 32, r);
+        ptx::tmem_ld_32x32b_x32(t_base + m * BN + g * 32, r);
         ptx::tmem_ld_wait();
-        const uint32_t tile = ptx::smem_u32(smem + (m * 4 + g) * kTile16K);
+        const uint32_t tile = ptx::smem_u32(smem + g * kTile16K);
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           ptx::st_shared_v4(tile + ptx::sw128_offset(row, j), r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
@@ -328,9 +345,9 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
       ptx::fence_proxy_async_smem();
       ptx::named_bar_sync(1, 128);
       if (issuer) {
-        for (int g = 0; g < 4; ++g)
+        for (int g = 0; g < GRANULES; ++g)
           if (n0 + g * 32 < MLAPO_MM1_OUT)
-            ptx::tma_store_3d(&tm_p, ptx::smem_u32(smem + (m * 4 + g) * kTile16K), n0 + g * 32, m0 + m * kBlockM, split);
+            ptx::tma_store_3d(&tm_p, ptx::smem_u32(smem + g * kTile16K), n0 + g * 32, m0 + m * kBlockM, split);
         ptx::tma_store_commit();
       }
     }
@@ -374,8 +391,8 @@ __device__ __forceinline__ double warp_sum_f64(double v) {
   return v;
 }
 
-template <class T>
-__global__ void __launch_bounds__(kNormThreads) norm_rope_cache_kernel(NormArgs a) {
+template <class T, int kMaxSplits>
+__global__ void __launch_bounds__(kNormThreads, kMaxSplits == 1 ? 4 : 2) norm_rope_cache_kernel(NormArgs a) {
   __shared__ double s_sum[9];
   __shared__ float s_max[9];
   const int t = blockIdx.x;
@@ -398,7 +415,6 @@ __global__ void __launch_bounds__(kNormThreads) norm_rope_cache_kernel(NormArgs 
   float x[8];
   uint4 g_vec = make_uint4(0, 0, 0, 0), b_vec = make_uint4(0, 0, 0, 0);  // gamma (+beta) or cos/sin of this thread's 8 columns
   {
-    constexpr int kMaxSplits = 8;
     int4 pu[kMaxSplits], pv[kMaxSplits];
 #pragma unroll
     for (int s = 0; s < kMaxSplits; ++s) {
@@ -1130,10 +1146,16 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
                    tok_scale, d);
   } else {
     const long long nvec = (long long)n * d / 8;
-    int blocks = (int)((nvec + 255) / 256);
-    if (blocks > num_sms() * 8) blocks = num_sms() * 8;
-    e__ = launch_k(quant_hidden_kernel<T>, dim3(blocks), dim3(256), 0, st, pdl, reinterpret_cast<const T*>(p->hidden_state), a0,
-                   reinterpret_cast<const T*>(p->quant_scale0), reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, tl0);
+    const long long one_wave = (long long)num_sms() * 8 * 256;  // threads of one full wave (8 blocks of 256 per SM)
+    if (nvec <= one_wave) {  // decode sizes: one 16-byte vector per thread
+      e__ = launch_k(quant_hidden_kernel<T, 1>, dim3((unsigned)((nvec + 255) / 256)), dim3(256), 0, st, pdl,
+                     reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
+                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, tl0);
+    } else {                 // prefill sizes: grid-stride, 4 independent loads in flight per thread
+      e__ = launch_k(quant_hidden_kernel<T, 4>, dim3(num_sms() * 8), dim3(256), 0, st, pdl,
+                     reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
+                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, tl0);
+    }
   }
   MLAPO_CHECK_LAUNCH("quant_hidden");
   record_event(1, st);
@@ -1142,20 +1164,27 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   {
     CUtensorMap tm_a, tm_b, tm_p;
     if ((rc = make_tmap(&tm_a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a0, n, d, d, kBlockM, 128))) return rc;
-    if ((rc = make_tmap(&tm_b, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wdqkv_km, MLAPO_MM1_OUT, d, d, kMm1BlockN, 128))) return rc;
+    const bool wide = l.splits0 == 1 && n >= 1024;  // prefill: no split-K, 256-wide weight tiles
+    const int bn = wide ? kMm1BlockNWide : kMm1BlockN;
+    if ((rc = make_tmap(&tm_b, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wdqkv_km, MLAPO_MM1_OUT, d, d, bn, 128))) return rc;
     if ((rc = make_tmap(&tm_p, CU_TENSOR_MAP_DATA_TYPE_INT32, 4, partial0, n, MLAPO_MM1_OUT, MLAPO_MM1_OUT * 4, kBlockM, 32, l.splits0,
                         (uint64_t)n * MLAPO_MM1_OUT * 4))) return rc;
-    const int n_tiles = (MLAPO_MM1_OUT + kMm1BlockN - 1) / kMm1BlockN;
-    if (n > kBlockM) {
+    const int n_tiles = (MLAPO_MM1_OUT + bn - 1) / bn;
+    if (wide) {
       static bool done[64] = {};
-      if ((rc = set_smem_attr(mm1_splitk_kernel<2>, mm1_smem_bytes<2>(), &done[dev], "mm1<2>"))) return rc;
-      e__ = launch_k(mm1_splitk_kernel<2>, dim3(n_tiles, l.splits0, (n + 255) / 256), dim3(kGemmThreads), mm1_smem_bytes<2>(), st, pdl,
-                     tm_a, tm_b, tm_p, n, d / kBlockKBytes, tl1);
+      if ((rc = set_smem_attr(mm1_splitk_kernel<2, kMm1BlockNWide>, mm1_smem_bytes<2, kMm1BlockNWide>(), &done[dev], "mm1<2,256>"))) return rc;
+      e__ = launch_k(mm1_splitk_kernel<2, kMm1BlockNWide>, dim3(n_tiles, 1, (n + 255) / 256), dim3(kGemmThreads),
+                     mm1_smem_bytes<2, kMm1BlockNWide>(), st, pdl, tm_a, tm_b, tm_p, n, d / kBlockKBytes, tl1);
+    } else if (n > kBlockM) {
+      static bool done[64] = {};
+      if ((rc = set_smem_attr(mm1_splitk_kernel<2, kMm1BlockN>, mm1_smem_bytes<2, kMm1BlockN>(), &done[dev], "mm1<2,128>"))) return rc;
+      e__ = launch_k(mm1_splitk_kernel<2, kMm1BlockN>, dim3(n_tiles, l.splits0, (n + 255) / 256), dim3(kGemmThreads),
+                     mm1_smem_bytes<2, kMm1BlockN>(), st, pdl, tm_a, tm_b, tm_p, n, d / kBlockKBytes, tl1);
     } else {
       static bool done[64] = {};
-      if ((rc = set_smem_attr(mm1_splitk_kernel<1>, mm1_smem_bytes<1>(), &done[dev], "mm1<1>"))) return rc;
-      e__ = launch_k(mm1_splitk_kernel<1>, dim3(n_tiles, l.splits0, 1), dim3(kGemmThreads), mm1_smem_bytes<1>(), st, pdl, tm_a, tm_b,
-                     tm_p, n, d / kBlockKBytes, tl1);
+      if ((rc = set_smem_attr(mm1_splitk_kernel<1, kMm1BlockN>, mm1_smem_bytes<1, kMm1BlockN>(), &done[dev], "mm1<1,128>"))) return rc;
+      e__ = launch_k(mm1_splitk_kernel<1, kMm1BlockN>, dim3(n_tiles, l.splits0, 1), dim3(kGemmThreads), mm1_smem_bytes<1, kMm1BlockN>(),
+                     st, pdl, tm_a, tm_b, tm_p, n, d / kBlockKBytes, tl1);
     }
     MLAPO_CHECK_LAUNCH("mm1_splitk");
   }
@@ -1180,7 +1209,8 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     a.cache_mode = p->cache_mode;
     a.cache_slots = (long long)p->num_cache_blocks * p->cache_block_size;
     a.tl = tl3;
-    e__ = launch_k(norm_rope_cache_kernel<T>, dim3(n), dim3(kNormThreads), 0, st, pdl, a);
+    if (l.splits0 == 1) e__ = launch_k(norm_rope_cache_kernel<T, 1>, dim3(n), dim3(kNormThreads), 0, st, pdl, a);  // prefill: no split-K
+    else e__ = launch_k(norm_rope_cache_kernel<T, 8>, dim3(n), dim3(kNormThreads), 0, st, pdl, a);
     MLAPO_CHECK_LAUNCH("norm_rope_cache");
   }
   record_event(3, st);

@@ -28,6 +28,8 @@ CASES = [
     (300, 8, 7168, "bf16", "int8_nzcache", PT, 0.1),
     (64, 4, 7168, "bf16", "krope_ctkv", TOK, 0.1),
     (33, 4, 6144, "fp16", "nzcache", TOK, 0.0),
+    # prefill-sized: no split-K, 256-wide MM1 tiles, many token super-tiles (the reference stops at 1024 tokens)
+    (2400, 2, 7168, "bf16", "krope_ctkv", PT, 0.05),
 ]
 
 
@@ -45,7 +47,7 @@ def check(res, case):
 @pytest.mark.parametrize("cfg", CASES, ids=[f"N{c[0]}-H{c[1]}-D{c[2]}-{c[3]}-{c[4]}-{c[5][:9]}" for c in CASES])
 def test_parity_vs_oracle(cfg, cuda_device):
     n, h, d, dt, mode, qm, neg = cfg
-    case = orc.gen_case(N=n, H=h, D=d, dtype=DT[dt], cache_mode=mode, seed=42, num_blocks=12, neg_slot_frac=neg)
+    case = orc.gen_case(N=n, H=h, D=d, dtype=DT[dt], cache_mode=mode, seed=42, num_blocks=max(12, n // 64), neg_slot_frac=neg)
     case.t["kv_cache"].fill_(5)
     case.t["kv_cache_rope"].fill_(5)
     g, taps = hz.run_cuda(case, cuda_device, quant_mode=qm)
