@@ -104,22 +104,27 @@ __global__ void repack_nz_kernel(const int8_t* __restrict__ nz, int8_t* __restri
 }
 
 // ============================================================================================ k1: quantise hiddenState
+// x / s, correctly rounded, without the generic IEEE-division sequence: x and s both carry <= 11 significant bits
+// (bf16/fp16), so the exact quotient lies >= 2^-36 (relative) away from every fp32 rounding boundary, while
+// q1 = fma(fma(-q0, s, x), r, q0) with r = RN(1/s), q0 = RN(x*r) carries a relative error of ~2^-46 before its
+// final rounding: q1 == RN(x / s).  Guarded to the range where neither r nor the products leave the normal range.
+struct QuantScale {
+  float s, zp, rcp;
+  bool fast;
+  template <class T>
+  __device__ __forceinline__ void load(const T* scale, const int8_t* offset) {
+    s = Act<T>::to_f(scale[0]);
+    zp = (float)offset[0];
+    rcp = __frcp_rn(s);
+    fast = fabsf(s) > 1e-30f && fabsf(s) < 1e30f;
+  }
+};
+
+// Per-tensor quantisation of the 16-byte vectors first, first+stride, ...; U independent loads in flight per thread.
 template <class T, int U>
-__global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict__ q, const T* __restrict__ scale,
-                                    const int8_t* __restrict__ offset, long long n_vec8, long long* tl) {
-  if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 0);
-  ptx::griddep_launch_dependents();
-  const float s = Act<T>::to_f(scale[0]);
-  const float zp = (float)offset[0];
-  // x / s, correctly rounded, without the generic IEEE-division sequence: x and s both carry <= 11 significant bits
-  // (bf16/fp16), so the exact quotient lies >= 2^-36 (relative) away from every fp32 rounding boundary, while
-  // q1 = fma(fma(-q0, s, x), r, q0) with r = RN(1/s), q0 = RN(x*r) carries a relative error of ~2^-46 before its
-  // final rounding: q1 == RN(x / s).  Guarded to the range where neither r nor the products leave the normal range.
-  const float rcp = __frcp_rn(s);
-  const bool fast = fabsf(s) > 1e-30f && fabsf(s) < 1e30f;
-  ptx::griddep_wait();  // a0 may still be read by the previous call's MM1 until its successors have completed
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < n_vec8; i0 += stride * U) {
+__device__ __forceinline__ void quant_vectors(const T* __restrict__ x, int8_t* __restrict__ q, const QuantScale& qs, long long n_vec8,
+                                              long long first, long long stride) {
+  for (long long i0 = first; i0 < n_vec8; i0 += stride * U) {
     uint4 v[U];
 #pragma unroll
     for (int u = 0; u < U; ++u)  // all loads of the batch are issued before any is consumed
@@ -131,30 +136,39 @@ __global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict_
       float f[8];
       unpack8<T>(v[u], f);
       int r[8];
-      if (fast) {
+      if (qs.fast) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          const float q0 = __fmul_rn(f[j], rcp);
-          const float q1 = __fmaf_rn(__fmaf_rn(-q0, s, f[j]), rcp, q0);
-          r[j] = sat_i8(__fadd_rn(q1, zp));
+          const float q0 = __fmul_rn(f[j], qs.rcp);
+          const float q1 = __fmaf_rn(__fmaf_rn(-q0, qs.s, f[j]), qs.rcp, q0);
+          r[j] = sat_i8(__fadd_rn(q1, qs.zp));
         }
       } else {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) r[j] = sat_i8(__fadd_rn(__fdiv_rn(f[j], s), zp));
+        for (int j = 0; j < 8; ++j) r[j] = sat_i8(__fadd_rn(__fdiv_rn(f[j], qs.s), qs.zp));
       }
       ptx::st_global_v2(q + i * 8, pack4_i8(r[0], r[1], r[2], r[3]), pack4_i8(r[4], r[5], r[6], r[7]));
     }
   }
+}
+
+template <class T, int U>
+__global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict__ q, const T* __restrict__ scale,
+                                    const int8_t* __restrict__ offset, long long n_vec8, long long* tl) {
+  if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 0);
+  ptx::griddep_launch_dependents();
+  QuantScale qs;
+  qs.load(scale, offset);
+  ptx::griddep_wait();  // a0 may still be read by the previous call's MM1 until its successors have completed
+  quant_vectors<T, U>(x, q, qs, n_vec8, blockIdx.x * (long long)blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 15);
 }
 
-// per-token symmetric (UNPINNED restatement of bf16.hpp:437-475): one block per row
+// per-token symmetric (UNPINNED restatement of bf16.hpp:437-475): one row, executed by the whole CTA (any block size)
 template <class T>
-__global__ void __launch_bounds__(256) quant_hidden_per_token_kernel(const T* __restrict__ x, int8_t* __restrict__ q,
-                                                                      float* __restrict__ tok_scale, int d) {
-  __shared__ float s_red[8];
-  ptx::griddep_launch_dependents();
-  const int row = blockIdx.x;
+__device__ __forceinline__ void quant_row_per_token(const T* __restrict__ x, int8_t* __restrict__ q, float* __restrict__ tok_scale, int d,
+                                                    int row) {
+  __shared__ float s_red[32];
   const uint4* xr = reinterpret_cast<const uint4*>(x + (long long)row * d);
   float amax = 0.f;
   for (int i = threadIdx.x; i < d / 8; i += blockDim.x) {
@@ -168,11 +182,9 @@ __global__ void __launch_bounds__(256) quant_hidden_per_token_kernel(const T* __
   if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = amax;
   __syncthreads();
   amax = s_red[0];
-#pragma unroll
-  for (int w = 1; w < 8; ++w) amax = fmaxf(amax, s_red[w]);
+  for (int w = 1; w < (int)(blockDim.x >> 5); ++w) amax = fmaxf(amax, s_red[w]);
   const float s = __fdiv_rn(amax, 127.f);
   const float inv = __fdiv_rn(1.f, s);
-  ptx::griddep_wait();
   if (threadIdx.x == 0) tok_scale[row] = s;
   for (int i = threadIdx.x; i < d / 8; i += blockDim.x) {
     float f[8];
@@ -182,6 +194,15 @@ __global__ void __launch_bounds__(256) quant_hidden_per_token_kernel(const T* __
     for (int j = 0; j < 8; ++j) r[j] = sat_i8(__fmul_rn(f[j], inv));
     ptx::st_global_v2(q + (long long)row * d + i * 8, pack4_i8(r[0], r[1], r[2], r[3]), pack4_i8(r[4], r[5], r[6], r[7]));
   }
+  __syncthreads();  // s_red is re-used by the next row
+}
+
+template <class T>
+__global__ void __launch_bounds__(256) quant_hidden_per_token_kernel(const T* __restrict__ x, int8_t* __restrict__ q,
+                                                                      float* __restrict__ tok_scale, int d) {
+  ptx::griddep_launch_dependents();
+  ptx::griddep_wait();
+  quant_row_per_token<T>(x, q, tok_scale, d, blockIdx.x);
 }
 
 // ============================================================================================ k2: MM1 (W_DQKV), split-K
@@ -204,79 +225,83 @@ constexpr int mm1_smem_bytes() {
   return mm1_stages<MT, BN>() * (MT * kTile16K + BN * kBlockKBytes) + 256 + 1024;
 }
 
+// Where one CTA's MM1 work item lives: its k-range, its tiles, its pipeline in shared memory and its TMEM columns.
 template <int MT, int BN>
-__global__ void __launch_bounds__(kGemmThreads, 1)
-mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
-                  const __grid_constant__ CUtensorMap tm_p, int m_total, int kb_total, long long* tl) {
-  constexpr int STAGES = mm1_stages<MT, BN>();
-  if (threadIdx.x == 0) { tl_mark_global(tl, 0); tl_mark(tl, 1); }
-  constexpr int A_BYTES = MT * kTile16K;
-  constexpr int B_BYTES = BN * kBlockKBytes;
-  constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  constexpr int TMEM_COLS = MT * BN;          // 128, 256 or 512
-  constexpr int GRANULES = BN / 32;           // 32 int32 columns = one 128-byte row per token
+struct Mm1Ctx {
+  static constexpr int STAGES = mm1_stages<MT, BN>();
+  static constexpr int A_BYTES = MT * kTile16K;
+  static constexpr int B_BYTES = BN * kBlockKBytes;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int TMEM_COLS = MT * BN;   // 128, 256 or 512
+  static constexpr int GRANULES = BN / 32;    // 32 int32 columns = one 128-byte row per token
+  static constexpr int NUM_BARS = 2 * STAGES + 1;
   static_assert(TMEM_COLS <= 512 && (TMEM_COLS & (TMEM_COLS - 1)) == 0, "TMEM allocation");
   static_assert(GRANULES * kTile16K <= STAGES * STAGE_BYTES, "one token tile of epilogue staging must fit in the drained pipeline");
+  uint8_t* smem;        // STAGES x [A: MT x 16 KB | B: BN x 128 B], 1024-byte aligned
+  uint64_t* bars;       // full[STAGES], empty[STAGES], done
+  uint32_t tmem_acc;    // first TMEM column of the accumulators
+  int n0, split, m0, kb0, nkb, mt_valid, m_total;
 
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
-  uint64_t* full_bar = bars;
-  uint64_t* empty_bar = bars + STAGES;
-  uint64_t* done_bar = bars + 2 * STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 2);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * BN;
-  const int split = blockIdx.y, splits = gridDim.y;
-  const int m0 = blockIdx.z * (MT * kBlockM);
-  const int kb0 = (int)(((long long)split * kb_total) / splits);
-  const int kb1 = (int)(((long long)(split + 1) * kb_total) / splits);
-  const int nkb = kb1 - kb0;
-  // token tiles that hold at least one valid row (the others are neither loaded nor multiplied)
-  const int mt_valid = (m_total - m0 + kBlockM - 1) / kBlockM < MT ? (m_total - m0 + kBlockM - 1) / kBlockM : MT;
-
-  if (warp == 0 && lane == 0) {
-    ptx::prefetch_tmap(&tm_a);
-    ptx::prefetch_tmap(&tm_b);
-    ptx::prefetch_tmap(&tm_p);
+  __device__ void set_work(int n_tile, int split_, int splits, int m_super, int m_total_, int kb_total) {
+    n0 = n_tile * BN;
+    split = split_;
+    m0 = m_super * (MT * kBlockM);
+    m_total = m_total_;
+    kb0 = (int)(((long long)split_ * kb_total) / splits);
+    nkb = (int)(((long long)(split_ + 1) * kb_total) / splits) - kb0;
+    // token tiles that hold at least one valid row (the others are neither loaded nor multiplied)
+    const int tiles = (m_total_ - m0 + kBlockM - 1) / kBlockM;
+    mt_valid = tiles < MT ? tiles : MT;
   }
-  if (warp == 1) {
-    if (lane == 0) {
-      for (int i = 0; i < STAGES; ++i) {
-        ptx::mbar_init(ptx::smem_u32(full_bar + i), 1);
-        ptx::mbar_init(ptx::smem_u32(empty_bar + i), 1);
-      }
-      ptx::mbar_init(ptx::smem_u32(done_bar), 1);
-      ptx::fence_mbar_init();
-    }
-    __syncwarp();
-    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), TMEM_COLS);
-    ptx::tmem_relinquish();
-  }
-  ptx::tc_fence_before();
-  __syncthreads();
-  ptx::tc_fence_after();
-  const uint32_t tmem_acc = *tmem_slot;
-  ptx::griddep_launch_dependents();
-  if (threadIdx.x == 0) tl_mark(tl, 2);  // prologue done
+};
 
+template <int MT, int BN>
+__device__ __forceinline__ void mm1_init_barriers(uint64_t* bars) {  // one thread
+  for (int i = 0; i < Mm1Ctx<MT, BN>::NUM_BARS; ++i) ptx::mbar_init(ptx::smem_u32(bars + i), 1);
+}
+
+// One thread: arm the first pipeline stages and request their weight tiles (which depend on nothing upstream).
+template <int MT, int BN>
+__device__ __forceinline__ void mm1_issue_weights(const Mm1Ctx<MT, BN>& c, const CUtensorMap* tm_b) {
+  using C = Mm1Ctx<MT, BN>;
+  const uint32_t stage_tx = (uint32_t)(c.mt_valid * kTile16K + C::B_BYTES);
+  const int pre = c.nkb < C::STAGES ? c.nkb : C::STAGES;
+  for (int i = 0; i < pre; ++i) {
+    const uint32_t fb = ptx::smem_u32(c.bars + i);
+    ptx::mbar_arrive_expect_tx(fb, stage_tx);
+    ptx::tma_load_2d(ptx::smem_u32(c.smem + i * C::STAGE_BYTES + C::A_BYTES), tm_b, fb, (c.kb0 + i) * kBlockKBytes, c.n0, ptx::kEvictFirst);
+  }
+}
+
+// Warp roles of MM1: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer, warps 2..5 = epilogue (TMEM lane quarter = warp%4);
+// other warps fall through.  kStandalone: own kernel under PDL (requests weights, then waits for the upstream kernel);
+// otherwise the caller has already issued mm1_issue_weights() and guarantees a0 is complete.
+template <int MT, int BN, bool kStandalone>
+__device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtensorMap* tm_a, const CUtensorMap* tm_b,
+                                          const CUtensorMap* tm_p, int warp, int lane, long long* tl) {
+  using C = Mm1Ctx<MT, BN>;
+  constexpr int STAGES = C::STAGES, A_BYTES = C::A_BYTES, B_BYTES = C::B_BYTES, STAGE_BYTES = C::STAGE_BYTES, GRANULES = C::GRANULES;
+  uint8_t* const smem = c.smem;
+  uint64_t* const full_bar = c.bars;
+  uint64_t* const empty_bar = c.bars + STAGES;
+  uint64_t* const done_bar = c.bars + 2 * STAGES;
+  const uint32_t tmem_acc = c.tmem_acc;
+  const int n0 = c.n0, split = c.split, m0 = c.m0, kb0 = c.kb0, nkb = c.nkb, mt_valid = c.mt_valid;
+  (void)B_BYTES;
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       const uint32_t stage_tx = (uint32_t)(mt_valid * kTile16K + B_BYTES);
       const int pre = nkb < STAGES ? nkb : STAGES;
-      for (int i = 0; i < pre; ++i) {  // weights first: independent of the upstream kernel
-        const uint32_t fb = ptx::smem_u32(full_bar + i);
-        ptx::mbar_arrive_expect_tx(fb, stage_tx);
-        ptx::tma_load_2d(ptx::smem_u32(smem + i * STAGE_BYTES + A_BYTES), &tm_b, fb, (kb0 + i) * kBlockKBytes, n0, ptx::kEvictFirst);
+      if (kStandalone) {
+        mm1_issue_weights<MT, BN>(c, tm_b);  // weights first: independent of the upstream kernel
+        ptx::griddep_wait();                 // a0 is produced by the quantise kernel
+        tl_mark(tl, 3);                      // upstream complete
       }
-      ptx::griddep_wait();  // a0 is produced by the quantise kernel
-      tl_mark(tl, 3);       // upstream complete
       for (int i = 0; i < pre; ++i) {
         const uint32_t fb = ptx::smem_u32(full_bar + i);
         for (int m = 0; m < mt_valid; ++m)
-          ptx::tma_load_2d(ptx::smem_u32(smem + i * STAGE_BYTES + m * kTile16K), &tm_a, fb, (kb0 + i) * kBlockKBytes,
+          ptx::tma_load_2d(ptx::smem_u32(smem + i * STAGE_BYTES + m * kTile16K), tm_a, fb, (kb0 + i) * kBlockKBytes,
                            m0 + m * kBlockM, ptx::kEvictLast);
       }
       uint32_t stage = 0, phase = 1;  // stages 0..pre-1 are in their first use; the next wrap waits for phase 0 of empty
@@ -284,9 +309,9 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
         ptx::mbar_wait(ptx::smem_u32(empty_bar + stage), phase ^ 1);
         const uint32_t fb = ptx::smem_u32(full_bar + stage);
         ptx::mbar_arrive_expect_tx(fb, stage_tx);
-        ptx::tma_load_2d(ptx::smem_u32(smem + stage * STAGE_BYTES + A_BYTES), &tm_b, fb, (kb0 + i) * kBlockKBytes, n0, ptx::kEvictFirst);
+        ptx::tma_load_2d(ptx::smem_u32(smem + stage * STAGE_BYTES + A_BYTES), tm_b, fb, (kb0 + i) * kBlockKBytes, n0, ptx::kEvictFirst);
         for (int m = 0; m < mt_valid; ++m)
-          ptx::tma_load_2d(ptx::smem_u32(smem + stage * STAGE_BYTES + m * kTile16K), &tm_a, fb, (kb0 + i) * kBlockKBytes,
+          ptx::tma_load_2d(ptx::smem_u32(smem + stage * STAGE_BYTES + m * kTile16K), tm_a, fb, (kb0 + i) * kBlockKBytes,
                            m0 + m * kBlockM, ptx::kEvictLast);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
@@ -347,16 +372,55 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
       if (issuer) {
         for (int g = 0; g < GRANULES; ++g)
           if (n0 + g * 32 < MLAPO_MM1_OUT)
-            ptx::tma_store_3d(&tm_p, ptx::smem_u32(smem + g * kTile16K), n0 + g * 32, m0 + m * kBlockM, split);
+            ptx::tma_store_3d(tm_p, ptx::smem_u32(smem + g * kTile16K), n0 + g * 32, m0 + m * kBlockM, split);
         ptx::tma_store_commit();
       }
     }
     if (issuer) { tl_mark(tl, 7); ptx::tma_store_wait_read<0>(); tl_mark(tl, 8); }
   }
 
+}
+
+template <int MT, int BN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+                  const __grid_constant__ CUtensorMap tm_p, int m_total, int kb_total, long long* tl) {
+  using C = Mm1Ctx<MT, BN>;
+  if (threadIdx.x == 0) { tl_mark_global(tl, 0); tl_mark(tl, 1); }
+  extern __shared__ uint8_t smem_raw[];
+  C c;
+  c.smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  c.bars = reinterpret_cast<uint64_t*>(c.smem + C::STAGES * C::STAGE_BYTES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(c.bars + C::NUM_BARS + 1);
+  c.set_work(blockIdx.x, blockIdx.y, gridDim.y, blockIdx.z, m_total, kb_total);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tm_a);
+    ptx::prefetch_tmap(&tm_b);
+    ptx::prefetch_tmap(&tm_p);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      mm1_init_barriers<MT, BN>(c.bars);
+      ptx::fence_mbar_init();
+    }
+    __syncwarp();
+    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), C::TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 1) ptx::tmem_dealloc(tmem_acc, TMEM_COLS);
+  ptx::tc_fence_after();
+  c.tmem_acc = *tmem_slot;
+  ptx::griddep_launch_dependents();
+  if (threadIdx.x == 0) tl_mark(tl, 2);  // prologue done
+
+  mm1_roles<MT, BN, true>(c, &tm_a, &tm_b, &tm_p, warp, lane, tl);
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(c.tmem_acc, C::TMEM_COLS);
   if (threadIdx.x == 32) { tl_mark(tl, 9); tl_mark_global(tl, 15); }
 }
 
@@ -391,25 +455,20 @@ __device__ __forceinline__ double warp_sum_f64(double v) {
   return v;
 }
 
+// One token row, executed by every thread of the CTA (threads beyond the first 288 only take part in the barriers).
 template <class T, int kMaxSplits>
-__global__ void __launch_bounds__(kNormThreads, kMaxSplits == 1 ? 4 : 2) norm_rope_cache_kernel(NormArgs a) {
+__device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const int tid) {
   __shared__ double s_sum[9];
   __shared__ float s_max[9];
-  const int t = blockIdx.x;
-  const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
   const bool is_nope = warp < 2;
   const bool is_pe = warp == 2;
-  const bool active = is_nope || (is_pe && lane < 8) || warp >= 3;
+  const bool is_q = warp >= 3 && warp < 9;
+  const bool active = is_nope || (is_pe && lane < 8) || is_q;
   int col = 0;  // first of this thread's 8 columns in [0, 2112)
   if (is_nope) col = tid * 8;
   else if (is_pe) col = 512 + (lane & 7) * 8;
-  else col = 576 + (tid - 96) * 8;
-
-  if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 0);
-  ptx::griddep_launch_dependents();
-  ptx::griddep_wait();  // partial sums come from the MM1 kernel
-  if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 14);
+  else if (is_q) col = 576 + (tid - 96) * 8;
   // ---- sum split-K partials (+bias), dequantise, round to act  (S2 of the contract)
   // All global loads are issued before anything is consumed (the kernel is latency-, not bandwidth-bound).
   float x[8];
@@ -445,7 +504,7 @@ __global__ void __launch_bounds__(kNormThreads, kMaxSplits == 1 ? 4 : 2) norm_ro
     } else if (is_pe) {
       g_vec = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.cos) + (long long)t * 64)[lane & 7];
       b_vec = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.sin) + (long long)t * 64)[lane & 7];
-    } else {
+    } else if (is_q) {
       g_vec = reinterpret_cast<const uint4*>(a.gamma1)[tid - 96];
       b_vec = reinterpret_cast<const uint4*>(a.beta1)[tid - 96];
     }
@@ -476,7 +535,7 @@ __global__ void __launch_bounds__(kNormThreads, kMaxSplits == 1 ? 4 : 2) norm_ro
     for (int j = 0; j < 8; ++j) ss += (double)x[j] * (double)x[j];
   }
   ss = warp_sum_f64(ss);
-  if (lane == 0) s_sum[warp] = ss;
+  if (lane == 0 && warp < 9) s_sum[warp] = ss;
   __syncthreads();
   const double tot_nope = s_sum[0] + s_sum[1];
   const double tot_q = ((s_sum[3] + s_sum[4]) + (s_sum[5] + s_sum[6])) + (s_sum[7] + s_sum[8]);
@@ -539,7 +598,7 @@ __global__ void __launch_bounds__(kNormThreads, kMaxSplits == 1 ? 4 : 2) norm_ro
   // S4: q_a RMSNorm(+beta) + quant -> a1   (golden test_mla:432, 436-438); needs all warps for the per-token max
   float yq[8];
   float amax = 0.f;
-  if (warp >= 3) {
+  if (is_q) {
     const float var = __fdiv_rn(__double2float_rn(tot_q), 1536.f);
     const float rs = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var, 1e-6f)));
     float g[8], b[8];
@@ -554,7 +613,7 @@ __global__ void __launch_bounds__(kNormThreads, kMaxSplits == 1 ? 4 : 2) norm_ro
   if (a.tok_scale1) {  // per-token symmetric (UNPINNED; bf16.hpp:739-777)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-    if (lane == 0) s_max[warp] = amax;
+    if (lane == 0 && warp < 9) s_max[warp] = amax;
     __syncthreads();
     float m = s_max[3];
 #pragma unroll
@@ -562,13 +621,13 @@ __global__ void __launch_bounds__(kNormThreads, kMaxSplits == 1 ? 4 : 2) norm_ro
     const float s1 = __fdiv_rn(m, 127.f);
     const float inv = __fdiv_rn(1.f, s1);
     if (tid == 96) a.tok_scale1[t] = s1;
-    if (warp >= 3) {
+    if (is_q) {
       int q[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) q[j] = sat_i8(__fmul_rn(yq[j], inv));
       ptx::st_global_v2(a.a1 + (long long)t * MLAPO_Q_LORA + (col - 576), pack4_i8(q[0], q[1], q[2], q[3]), pack4_i8(q[4], q[5], q[6], q[7]));
     }
-  } else if (warp >= 3) {
+  } else if (is_q) {
     const float s = Act<T>::to_f(reinterpret_cast<const T*>(a.quant_scale1)[0]);
     const float zp = (float)a.quant_offset1[0];
     int q[8];
@@ -576,6 +635,16 @@ __global__ void __launch_bounds__(kNormThreads, kMaxSplits == 1 ? 4 : 2) norm_ro
     for (int j = 0; j < 8; ++j) q[j] = sat_i8(__fadd_rn(__fdiv_rn(yq[j], s), zp));
     ptx::st_global_v2(a.a1 + (long long)t * MLAPO_Q_LORA + (col - 576), pack4_i8(q[0], q[1], q[2], q[3]), pack4_i8(q[4], q[5], q[6], q[7]));
   }
+}
+
+template <class T, int kMaxSplits>
+__global__ void __launch_bounds__(kNormThreads, kMaxSplits == 1 ? 4 : 2) norm_rope_cache_kernel(NormArgs a) {
+  const int tid = threadIdx.x;
+  if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 0);
+  ptx::griddep_launch_dependents();
+  ptx::griddep_wait();  // partial sums come from the MM1 kernel
+  if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 14);
+  norm_token<T, kMaxSplits>(a, blockIdx.x, tid);
   if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 15);
 }
 
@@ -615,80 +684,80 @@ struct QArgs {
   int cta_tokens;             // 256 (two token tiles per CTA, weights streamed once per 256 tokens) or 128 (more CTAs when heads are few)
 };
 
-template <class T, bool kInt8Out>
-__global__ void __launch_bounds__(kQThreads, 1)
-q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__ CUtensorMap tm_wuq,
-               const __grid_constant__ CUtensorMap tm_wuk, const __grid_constant__ CUtensorMap tm_out0,
-               const __grid_constant__ CUtensorMap tm_out1, QArgs qa, long long* tl) {
-  if (threadIdx.x == 0) { tl_mark_global(tl, 0); tl_mark(tl, 1); }
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kQBarOff);
-  uint64_t* full_bar = bars;             // [4]  TMA -> MMA
-  uint64_t* empty_bar = bars + 4;        // [4]  MMA -> TMA
-  uint64_t* mm2_done = bars + 8;         // [1]
-  uint64_t* wuk_full = bars + 9;         // [4]
-  uint64_t* qn_ready = bars + 13;        // [2]  epilogue group m -> MMA: q_nope tile m in smem and acc2[m] drained
-  uint64_t* unit_full = bars + 15;       // [4]  (m*2 + buffer) MMA -> epilogue
-  uint64_t* buf_empty = bars + 19;       // [4]  (m*2 + buffer) epilogue -> MMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
-  int2* s_cst = reinterpret_cast<int2*>(smem + kQBarOff + 256);  // per column {bias, descale bits}
+// Where one CTA's q-path work item lives.
+struct QCtx {
+  uint8_t* smem;     // 224 KB pipeline / overlay region, 1024-byte aligned
+  uint64_t* bars;    // full[4] empty[4] mm2_done wuk_full[4] qn_ready[2] unit_full[4] buf_empty[4]
+  int2* s_cst;       // per column {bias, descale bits}
+  uint32_t tmem;     // base of a 512-column TMEM allocation
+  int head, tok0, num_mt, load_mt;
+  static constexpr int NUM_BARS = 23;
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int head = blockIdx.x;
-  const int tok0 = blockIdx.y * qa.cta_tokens;
-  const int num_mt = (qa.cta_tokens > kBlockM && (qa.m_total - tok0) > kBlockM) ? 2 : 1;  // token tiles with valid rows in this CTA
-  const int load_mt = (qa.cta_tokens > kBlockM && qa.m_total > kBlockM) ? 2 : 1;          // token tiles fetched per stage (uniform over the grid)
-
-  if (warp == 0 && lane == 0) {
-    ptx::prefetch_tmap(&tm_a1);
-    ptx::prefetch_tmap(&tm_wuq);
-    ptx::prefetch_tmap(&tm_wuk);
-    ptx::prefetch_tmap(&tm_out0);
-    ptx::prefetch_tmap(&tm_out1);
+  __device__ void set_work(int head_, int tok_tile, const QArgs& qa) {
+    head = head_;
+    tok0 = tok_tile * qa.cta_tokens;
+    num_mt = (qa.cta_tokens > kBlockM && (qa.m_total - tok0) > kBlockM) ? 2 : 1;  // token tiles with valid rows in this CTA
+    load_mt = (qa.cta_tokens > kBlockM && qa.m_total > kBlockM) ? 2 : 1;          // token tiles fetched per stage (uniform over the grid)
   }
-  if (warp == 1) {
-    if (lane == 0) {
-      for (int i = 0; i < 13; ++i) ptx::mbar_init(ptx::smem_u32(bars + i), 1);
-      ptx::mbar_init(ptx::smem_u32(qn_ready), 128);
-      ptx::mbar_init(ptx::smem_u32(qn_ready + 1), 128);
-      for (int i = 0; i < 4; ++i) {
-        ptx::mbar_init(ptx::smem_u32(unit_full + i), 1);
-        ptx::mbar_init(ptx::smem_u32(buf_empty + i), 128);
-      }
-      ptx::fence_mbar_init();
-    }
-    __syncwarp();
-    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
-    ptx::tmem_relinquish();
-  }
-  ptx::tc_fence_before();
-  __syncthreads();
-  ptx::tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-  ptx::griddep_launch_dependents();
-  if (threadIdx.x == 0) tl_mark(tl, 2);  // prologue done
+};
 
+__device__ __forceinline__ void q_init_barriers(uint64_t* bars) {  // one thread
+  for (int i = 0; i < 13; ++i) ptx::mbar_init(ptx::smem_u32(bars + i), 1);
+  ptx::mbar_init(ptx::smem_u32(bars + 13), 128);
+  ptx::mbar_init(ptx::smem_u32(bars + 14), 128);
+  for (int i = 0; i < 4; ++i) {
+    ptx::mbar_init(ptx::smem_u32(bars + 15 + i), 1);
+    ptx::mbar_init(ptx::smem_u32(bars + 19 + i), 128);
+  }
+}
+
+// One thread: arm the four MM2 stages and request their W_UQ k-blocks (which depend on nothing upstream).
+__device__ __forceinline__ void q_issue_weights(const QCtx& c, const CUtensorMap* tm_wuq) {
+  const uint32_t stage_tx = (uint32_t)(c.load_mt * kTile16K + MLAPO_Q_HEAD * kBlockKBytes);
+  for (int kb = 0; kb < kQStages; ++kb) {
+    const uint32_t fb = ptx::smem_u32(c.bars + kb);
+    ptx::mbar_arrive_expect_tx(fb, stage_tx);
+    ptx::tma_load_2d(ptx::smem_u32(c.smem + kb * kQStageBytes + 2 * kTile16K), tm_wuq, fb, kb * kBlockKBytes, c.head * MLAPO_Q_HEAD,
+                     ptx::kEvictFirst);
+  }
+}
+
+// Warp roles of the q path: warp 0 = TMA producer, warp 1 = MMA issuer, warps 2..5 / 6..9 = epilogue groups of token tile 0 / 1.
+// kStandalone: own kernel under PDL; otherwise the caller has issued q_issue_weights() and guarantees a1 is complete.
+template <class T, bool kInt8Out, bool kStandalone>
+__device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1, const CUtensorMap* tm_wuq, const CUtensorMap* tm_wuk,
+                                        const CUtensorMap* tm_out0, const CUtensorMap* tm_out1, const QArgs& qa, int warp, int lane,
+                                        long long* tl) {
+  uint8_t* const smem = c.smem;
+  uint64_t* const full_bar = c.bars;        // [4]  TMA -> MMA
+  uint64_t* const empty_bar = c.bars + 4;   // [4]  MMA -> TMA
+  uint64_t* const mm2_done = c.bars + 8;    // [1]
+  uint64_t* const wuk_full = c.bars + 9;    // [4]
+  uint64_t* const qn_ready = c.bars + 13;   // [2]  epilogue group m -> MMA: q_nope tile m in smem and acc2[m] drained
+  uint64_t* const unit_full = c.bars + 15;  // [4]  (m*2 + buffer) MMA -> epilogue
+  uint64_t* const buf_empty = c.bars + 19;  // [4]  (m*2 + buffer) epilogue -> MMA
+  int2* const s_cst = c.s_cst;
+  const uint32_t tmem = c.tmem;
+  const int head = c.head, tok0 = c.tok0, num_mt = c.num_mt, load_mt = c.load_mt;
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       const uint32_t stage_tx = (uint32_t)(load_mt * kTile16K + MLAPO_Q_HEAD * kBlockKBytes);
       auto load_b = [&](int kb) {
         const int s = kb & 3;
-        ptx::tma_load_2d(ptx::smem_u32(smem + s * kQStageBytes + 2 * kTile16K), &tm_wuq, ptx::smem_u32(full_bar + s),
+        ptx::tma_load_2d(ptx::smem_u32(smem + s * kQStageBytes + 2 * kTile16K), tm_wuq, ptx::smem_u32(full_bar + s),
                          kb * kBlockKBytes, head * MLAPO_Q_HEAD, ptx::kEvictFirst);
       };
       auto load_a = [&](int kb) {  // one box = all token tiles of the stage (box rows = 128 * load_mt)
         const int s = kb & 3;
-        ptx::tma_load_2d(ptx::smem_u32(smem + s * kQStageBytes), &tm_a1, ptx::smem_u32(full_bar + s), kb * kBlockKBytes, tok0,
+        ptx::tma_load_2d(ptx::smem_u32(smem + s * kQStageBytes), tm_a1, ptx::smem_u32(full_bar + s), kb * kBlockKBytes, tok0,
                          ptx::kEvictLast);
       };
-      for (int kb = 0; kb < kQStages; ++kb) {  // weights first: independent of the upstream kernel
-        ptx::mbar_arrive_expect_tx(ptx::smem_u32(full_bar + kb), stage_tx);
-        load_b(kb);
+      if (kStandalone) {
+        q_issue_weights(c, tm_wuq);  // weights first: independent of the upstream kernel
+        ptx::griddep_wait();         // a1 is produced by the norm kernel
+        tl_mark(tl, 3);
       }
-      ptx::griddep_wait();  // a1 is produced by the norm kernel
-      tl_mark(tl, 3);
       for (int kb = 0; kb < kQStages; ++kb) load_a(kb);
       for (int kb = kQStages; kb < kQKBlocks; ++kb) {
         const int s = kb & 3;
@@ -702,7 +771,7 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
         const uint32_t fb = ptx::smem_u32(wuk_full + c);
         ptx::mbar_arrive_expect_tx(fb, 2 * kTile16K);
         for (int at = 0; at < 2; ++at)
-          ptx::tma_load_2d(ptx::smem_u32(smem + kQWukOff + c * 32768 + at * kTile16K), &tm_wuk, fb, c * 128 + at * 64,
+          ptx::tma_load_2d(ptx::smem_u32(smem + kQWukOff + c * 32768 + at * kTile16K), tm_wuk, fb, c * 128 + at * 64,
                            head * MLAPO_Q_NOPE, ptx::kEvictFirst);
       };
       ptx::mbar_wait(ptx::smem_u32(empty_bar + 0), 0);
@@ -792,7 +861,7 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
         s_cst[c] = make_int2(qa.bias1 ? qa.bias1[head * MLAPO_Q_HEAD + c] : 0, __float_as_int(dsc));
       }
     }
-    ptx::griddep_wait();  // tok_scale1 comes from the norm kernel (and keeps the PDL completion chain transitive)
+    if (kStandalone) ptx::griddep_wait();  // tok_scale1 comes from the norm kernel (and keeps the PDL completion chain transitive)
     ptx::named_bar_sync(3, 256);
 
     if (g < num_mt) {
@@ -878,7 +947,7 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
       }
       stage_publish();
       if (issuer) {
-        ptx::tma_store_2d(&tm_out1, st_tile, head * MLAPO_ROPE, tok0 + m * kBlockM);
+        ptx::tma_store_2d(tm_out1, st_tile, head * MLAPO_ROPE, tok0 + m * kBlockM);
         ptx::tma_store_commit();
       }
       if (issuer && g == 0) tl_mark(tl, 7);  // epi2 done
@@ -917,7 +986,7 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
           for (int j = 0; j < 8; ++j) ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
           stage_publish();
           if (issuer) {
-            ptx::tma_store_2d(&tm_out0, st_tile, head * MLAPO_KV_LORA + c * 128, tok0 + m * kBlockM);
+            ptx::tma_store_2d(tm_out0, st_tile, head * MLAPO_KV_LORA + c * 128, tok0 + m * kBlockM);
             ptx::tma_store_commit();
           }
         } else {
@@ -946,7 +1015,7 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
             for (int j = 0; j < 8; ++j) ptx::st_shared_v4(dst + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
             stage_publish();
             if (issuer) {
-              ptx::tma_store_2d(&tm_out0, dst, head * MLAPO_KV_LORA + c * 128 + half * 64, tok0 + m * kBlockM);
+              ptx::tma_store_2d(tm_out0, dst, head * MLAPO_KV_LORA + c * 128 + half * 64, tok0 + m * kBlockM);
               ptx::tma_store_commit();
             }
           }
@@ -960,9 +1029,51 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
     }
   }
 
+}
+
+template <class T, bool kInt8Out>
+__global__ void __launch_bounds__(kQThreads, 1)
+q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__ CUtensorMap tm_wuq,
+               const __grid_constant__ CUtensorMap tm_wuk, const __grid_constant__ CUtensorMap tm_out0,
+               const __grid_constant__ CUtensorMap tm_out1, QArgs qa, long long* tl) {
+  if (threadIdx.x == 0) { tl_mark_global(tl, 0); tl_mark(tl, 1); }
+  extern __shared__ uint8_t smem_raw[];
+  QCtx c;
+  c.smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  c.bars = reinterpret_cast<uint64_t*>(c.smem + kQBarOff);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(c.bars + 24);
+  c.s_cst = reinterpret_cast<int2*>(c.smem + kQBarOff + 256);
+  c.set_work(blockIdx.x, blockIdx.y, qa);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tm_a1);
+    ptx::prefetch_tmap(&tm_wuq);
+    ptx::prefetch_tmap(&tm_wuk);
+    ptx::prefetch_tmap(&tm_out0);
+    ptx::prefetch_tmap(&tm_out1);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      q_init_barriers(c.bars);
+      ptx::fence_mbar_init();
+    }
+    __syncwarp();
+    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
+    ptx::tmem_relinquish();
+  }
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 1) ptx::tmem_dealloc(tmem, 512);
+  ptx::tc_fence_after();
+  c.tmem = *tmem_slot;
+  ptx::griddep_launch_dependents();
+  if (threadIdx.x == 0) tl_mark(tl, 2);  // prologue done
+
+  q_roles<T, kInt8Out, true>(c, &tm_a1, &tm_wuq, &tm_wuk, &tm_out0, &tm_out1, qa, warp, lane, tl);
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(c.tmem, 512);
   if (threadIdx.x == 32) { tl_mark(tl, 12); tl_mark_global(tl, 15); }
 }
 
