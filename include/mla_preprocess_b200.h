@@ -178,10 +178,14 @@ int mlapo_launches_per_call(const MlapoParams* p);
  * Debug / profiling hooks (process-wide; no reference counterpart — the reference has DEBUG_MODE printf builds only,
  * CMakeLists.txt:48-53).  flags: bit0 = synchronise and check after every kernel (errors name the kernel),
  * bit1 = also write the dequantised MM1 rows y0 (act [N,2112]) after the last workspace region,
- * bit2 = record CUDA events around every kernel of the next launches, bit3 = per-CTA clock marks (timeline region).
+ * bit2 = record CUDA events around every kernel of the next launches, bit3 = per-CTA clock marks (timeline region),
+ * bit5 = run decode-sized calls (<= 256 tokens) as the single persistent cooperative kernel instead of four chained kernels,
+ * bits 8-10 = leave the persistent kernel after that phase, bit11 = log stuck barrier waits to a host-mapped buffer before trapping.
  * Returns the previous flags.
  */
 int mlapo_set_debug_flags(int flags);
+/* Debug (flag bit11 = log stuck barrier waits instead of trapping): {count, {cta, thread, barrier, parity} x count}. */
+int mlapo_debug_read_wait_log(unsigned* out, int cap_words);
 /* With bit2 set: per-kernel durations (ms) of the last launch, in launch order; returns how many were written. */
 int mlapo_get_kernel_times_ms(float* out_ms, int cap);
 const char* mlapo_kernel_name(int index);

@@ -8,7 +8,9 @@
 //                          latent RMSNorm(512), RoPE(64), paged-cache scatter (RmsNormAndRopeConvergence1, :2499-2686)
 //   k4 q_fused (per head)  a1 . Wuq[h]^T, dequant, RoPE -> q_out1; nope slice stays in smem and is absorbed:
 //                          q_nope . Wuk[h] -> q_out0 (+ int8 re-quant)      (PpMatmulW8a8Aiv, RopeFp16, PpMatmulEinSum, EinSumQuant)
-// Kernels are chained with programmatic dependent launch: each requests its weight tiles, then griddepcontrol.wait.
+//   k5 decode_persistent   k1..k4 as phases of ONE cooperative kernel with grid barriers, for calls of <= 256 tokens
+// As separate kernels (prefill sizes) k1..k4 are chained with programmatic dependent launch: each requests its weight
+// tiles, then griddepcontrol.wait.
 // The contractions are tcgen05.mma (kind::i8 with int32 accumulators, kind::f16 for the bf16/fp16 absorb) fed by TMA
 // into 128B-swizzled shared memory with accumulators in TMEM.  Arithmetic follows the reference's torch golden
 // (tests/python/sgl_kernel_npu/test_mla_preprocess.py:57-107, 407-484) operation by operation (see oracle/).
@@ -304,6 +306,7 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
           ptx::tma_load_2d(ptx::smem_u32(smem + i * STAGE_BYTES + m * kTile16K), tm_a, fb, (kb0 + i) * kBlockKBytes,
                            m0 + m * kBlockM, ptx::kEvictLast);
       }
+      ptx::progress_mark(0, 1);
       uint32_t stage = 0, phase = 1;  // stages 0..pre-1 are in their first use; the next wrap waits for phase 0 of empty
       for (int i = pre; i < nkb; ++i) {
         ptx::mbar_wait(ptx::smem_u32(empty_bar + stage), phase ^ 1);
@@ -322,6 +325,7 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
     uint32_t stage = 0, phase = 0;
     for (int i = 0; i < nkb; ++i) {
       ptx::mbar_wait(ptx::smem_u32(full_bar + stage), phase);
+      __syncwarp();
       ptx::tc_fence_after();
       if (lane == 0) {
         if (i == 0) tl_mark(tl, 4);             // first stage landed
@@ -337,24 +341,27 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
           }
         }
         ptx::umma_commit(ptx::smem_u32(empty_bar + stage));  // frees the smem slot when these MMAs retire
+        ptx::progress_mark(1, 10 + i);
       }
       __syncwarp();
       if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }
     if (lane == 0) ptx::umma_commit(ptx::smem_u32(done_bar));
     __syncwarp();
-  } else {
+  } else if (warp < 6) {
     // ------------------------------------------------------------------ epilogue: TMEM -> swizzled smem -> TMA store
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const uint32_t t_base = tmem_acc + ((uint32_t)(quarter * 32) << 16);
     const bool issuer = threadIdx.x == 64;
     ptx::mbar_wait(ptx::smem_u32(done_bar), 0);   // all MMAs retired => every pipeline stage has been consumed
+    __syncwarp();
     ptx::tc_fence_after();
-    if (issuer) tl_mark(tl, 6);                   // MMAs retired
+    if (issuer) { tl_mark(tl, 6); ptx::progress_mark(2, 40); }  // MMAs retired
+    __syncwarp();                                 // tcgen05.ld below is warp-aligned: reconverge after the one-lane branch
     for (int m = 0; m < mt_valid; ++m) {
       if (m > 0) {  // the staging tiles are re-used per token tile: the previous tile's stores must have been read
-        if (issuer) ptx::tma_store_wait_read<0>();
+        if (issuer) { ptx::progress_mark(2, 42); ptx::tma_store_wait_read<0>(); ptx::progress_mark(2, 43); }
         ptx::named_bar_sync(1, 128);
       }
 #pragma unroll 1
@@ -374,6 +381,7 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
           if (n0 + g * 32 < MLAPO_MM1_OUT)
             ptx::tma_store_3d(tm_p, ptx::smem_u32(smem + g * kTile16K), n0 + g * 32, m0 + m * kBlockM, split);
         ptx::tma_store_commit();
+        ptx::progress_mark(2, 44 + m);
       }
     }
     if (issuer) { tl_mark(tl, 7); ptx::tma_store_wait_read<0>(); tl_mark(tl, 8); }
@@ -790,6 +798,7 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
     for (int kb = 0; kb < kQKBlocks; ++kb) {
       const int s = kb & 3;
       ptx::mbar_wait(ptx::smem_u32(full_bar + s), (kb >> 2) & 1);
+      __syncwarp();
       ptx::tc_fence_after();
       if (lane == 0) {
         if (kb == 0) tl_mark(tl, 4);
@@ -817,6 +826,7 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
         if (c == 0) ptx::mbar_wait(ptx::smem_u32(qn_ready + m), 0);
         if (c >= 2) ptx::mbar_wait(ptx::smem_u32(buf_empty + ub), 0);
         if (m == 0) ptx::mbar_wait(ptx::smem_u32(wuk_full + c), 0);
+        __syncwarp();
         ptx::tc_fence_after();
         if (lane == 0) {
           const uint32_t b_base = ptx::smem_u32(smem + kQWukOff + c * 32768);
@@ -885,6 +895,7 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
       }
 
       ptx::mbar_wait(ptx::smem_u32(mm2_done), 0);
+      __syncwarp();
       ptx::tc_fence_after();
       if (issuer && g == 0) tl_mark(tl, 6);  // MM2 retired
 
@@ -959,6 +970,7 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
       for (int c = 0; c < 4; ++c) {
         const int ub = m * 2 + (c & 1);
         ptx::mbar_wait(ptx::smem_u32(unit_full + ub), (c >> 1) & 1);
+        __syncwarp();
         ptx::tc_fence_after();
         if (issuer && g == 0 && c == 0) tl_mark(tl, 8);  // first absorb unit ready
         if (issuer && g == 0 && c == 3) tl_mark(tl, 9);
@@ -1077,9 +1089,180 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
   if (threadIdx.x == 32) { tl_mark(tl, 12); tl_mark_global(tl, 15); }
 }
 
+// ============================================================================================ k5: decode — the whole chain in one persistent kernel
+// For decode-sized calls (<= 256 tokens, every phase fits one wave) the four phases run inside ONE cooperative kernel with
+// one CTA per SM (10 warps, 224 KB smem, 512 TMEM columns):
+//   quantise hidden -> | grid barrier | -> MM1 split-K -> | grid barrier | -> norm / RoPE / cache scatter -> | grid barrier | -> q path
+// Shared memory is one region that is the MM1 pipeline first and the q-path pipeline afterwards, so the TMA producer runs
+// ahead of the barriers: W_DQKV tiles are requested before the quantise phase and the first four W_UQ k-blocks as soon as
+// the MM1 pipeline has drained (they land while the norm phase runs).  Intermediates (a0, partial sums, a1) stay in L2.
+struct DecodeArgs {
+  const void* hidden;          // act [N, D]
+  int8_t* a0;                  // int8 [N, D]
+  const void* quant_scale0;    // act [1]   (per-tensor)
+  const int8_t* quant_offset0; // int8 [1]
+  float* tok_scale0;           // f32 [N]   (per-token) or null
+  int hidden_dim;
+  int n_tokens;
+  int splits0;                 // MM1 K-splits; 17 * splits0 CTAs take part in MM1
+  int q_tok_tiles;             // token tiles of the q grid; num_heads * q_tok_tiles CTAs take part in the q path
+  NormArgs norm;
+  QArgs q;
+  long long* tl_mm1;           // debug timelines or null
+  long long* tl_q;
+  int stop_after;              // debug: leave after this phase (0 = run everything)
+};
+constexpr int kMm1NTiles = (MLAPO_MM1_OUT + kMm1BlockN - 1) / kMm1BlockN;  // 17
+constexpr int kDecodeMm1BarOff = kQBarOff + 256;  // MM1's barriers share bytes with the q path's per-column constants (disjoint phases)
+constexpr int kDecodeSmemBytes = kQSmemBytes;
+constexpr int kDecodeStaticSmem = 256;            // reduction scratch of the quant / norm phases (static __shared__)
+static_assert(kDecodeSmemBytes + kDecodeStaticSmem <= 232448, "persistent decode smem");
+
+// Grid barrier state {arrivals, generation}.  Self-cleaning (arrivals return to 0), so it is valid from module load on;
+// one per device, which is enough because cooperative launches of this kernel on one device are stream-ordered.
+__device__ unsigned g_grid_sync_state[2];
+
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// All CTAs of the (co-resident) grid.  Global writes made before it by any thread — through the generic proxy or by
+// completed TMA stores — are visible afterwards to generic loads and to TMA loads of every CTA.
+__device__ __forceinline__ void grid_sync(unsigned nblocks) {
+  fence_proxy_async_all();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned* st = g_grid_sync_state;
+    const unsigned gen = ld_acquire_gpu(st + 1);
+    __threadfence();
+    if (atomicAdd(st, 1u) == nblocks - 1) {
+      atomicExch(st, 0u);
+      __threadfence();
+      atomicAdd(st + 1, 1u);
+    } else {
+      const long long t0 = clock64();
+      while (ld_acquire_gpu(st + 1) == gen) {
+        __nanosleep(32);
+        const long long dt = clock64() - t0;
+        if (dt > 4000000000LL) ptx::wait_timeout(blockIdx.x, 0xFFFFu, gen, 0);  // a missing participant becomes a launch failure, not a hang
+      }
+    }
+    __threadfence();
+  }
+  __syncthreads();
+  fence_proxy_async_all();
+}
+
+template <class T, bool kInt8Out, int MT>
+__global__ void __launch_bounds__(kQThreads, 1)
+mla_decode_persistent_kernel(const __grid_constant__ CUtensorMap tm_a0, const __grid_constant__ CUtensorMap tm_wdqkv,
+                             const __grid_constant__ CUtensorMap tm_part, const __grid_constant__ CUtensorMap tm_a1,
+                             const __grid_constant__ CUtensorMap tm_wuq, const __grid_constant__ CUtensorMap tm_wuk,
+                             const __grid_constant__ CUtensorMap tm_out0, const __grid_constant__ CUtensorMap tm_out1, DecodeArgs da) {
+  using M1 = Mm1Ctx<MT, kMm1BlockN>;
+  static_assert(M1::STAGES * M1::STAGE_BYTES <= kQBarOff, "MM1 pipeline must fit under the q-path barrier block");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int cta = blockIdx.x;
+  const unsigned nblocks = gridDim.x;
+  if (threadIdx.x == 0) { tl_mark_global(da.tl_mm1, 0); tl_mark(da.tl_mm1, 1); }
+
+  QCtx qc;
+  qc.smem = smem;
+  qc.bars = reinterpret_cast<uint64_t*>(smem + kQBarOff);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(qc.bars + 24);
+  qc.s_cst = reinterpret_cast<int2*>(smem + kQBarOff + 256);
+  M1 mc;
+  mc.smem = smem;
+  mc.bars = reinterpret_cast<uint64_t*>(smem + kDecodeMm1BarOff);
+
+  const bool has_mm1 = cta < kMm1NTiles * da.splits0;
+  const bool has_q = cta < da.q.num_heads * da.q_tok_tiles;
+  if (has_mm1) mc.set_work(cta % kMm1NTiles, cta / kMm1NTiles, da.splits0, 0, da.n_tokens, da.hidden_dim / kBlockKBytes);
+  if (has_q) qc.set_work(cta % da.q.num_heads, cta / da.q.num_heads, da.q);
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tm_a0);
+    ptx::prefetch_tmap(&tm_wdqkv);
+    ptx::prefetch_tmap(&tm_part);
+    ptx::prefetch_tmap(&tm_a1);
+    ptx::prefetch_tmap(&tm_wuq);
+    ptx::prefetch_tmap(&tm_wuk);
+    ptx::prefetch_tmap(&tm_out0);
+    ptx::prefetch_tmap(&tm_out1);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      mm1_init_barriers<MT, kMm1BlockN>(mc.bars);
+      q_init_barriers(qc.bars);
+      ptx::fence_mbar_init();
+    }
+    __syncwarp();
+    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  mc.tmem_acc = qc.tmem = *tmem_slot;
+
+  // W_DQKV tiles of this CTA's MM1 work item: requested now, consumed after the first grid barrier
+  if (warp == 0 && lane == 0 && has_mm1) mm1_issue_weights<MT, kMm1BlockN>(mc, &tm_wdqkv);
+
+  // ---- phase 1: quantise hiddenState -> a0
+  if (da.tok_scale0) {
+    for (int row = cta; row < da.n_tokens; row += (int)nblocks)
+      quant_row_per_token<T>(reinterpret_cast<const T*>(da.hidden), da.a0, da.tok_scale0, da.hidden_dim, row);
+  } else {
+    QuantScale qs;
+    qs.load(reinterpret_cast<const T*>(da.quant_scale0), da.quant_offset0);
+    quant_vectors<T, 4>(reinterpret_cast<const T*>(da.hidden), da.a0, qs, (long long)da.n_tokens * da.hidden_dim / 8,
+                        (long long)cta * blockDim.x + threadIdx.x, (long long)nblocks * blockDim.x);
+  }
+  grid_sync(nblocks);
+
+  // ---- phase 2: MM1 split-K partial sums
+  if (threadIdx.x == 0) tl_mark(da.tl_mm1, 2);
+  if (da.stop_after == 1) {  // debug exit: the requested weight tiles must still land before the CTA leaves
+    if (has_mm1 && warp == 1) for (int i = 0; i < (mc.nkb < M1::STAGES ? mc.nkb : M1::STAGES); ++i) (void)i;
+  }
+  if (has_mm1 && da.stop_after != 1) mm1_roles<MT, kMm1BlockN, false>(mc, &tm_a0, &tm_wdqkv, &tm_part, warp, lane, da.tl_mm1);
+  if (threadIdx.x == 64 && has_mm1) { ptx::progress_mark(2, 50); ptx::tma_store_wait<0>(); ptx::progress_mark(2, 51); }  // partial tiles fully written, not just read out of smem
+  ptx::tc_fence_before();
+  __syncthreads();                                              // the MM1 pipeline bytes are free again
+  ptx::tc_fence_after();
+  if (threadIdx.x == 0) ptx::progress_mark(3, 60);
+  if (threadIdx.x == 32) tl_mark(da.tl_mm1, 9);
+  // first W_UQ k-blocks of this CTA's head: requested now, they land while the norm phase runs
+  if (warp == 0 && lane == 0 && has_q && (da.stop_after == 0 || da.stop_after > 3)) q_issue_weights(qc, &tm_wuq);
+  grid_sync(nblocks);
+  const bool run3 = da.stop_after == 0 || da.stop_after >= 3;
+
+  // ---- phase 3: norms, quant, RoPE, cache scatter (one token at a time per CTA)
+  for (int t = cta; run3 && t < da.n_tokens; t += (int)nblocks) {
+    norm_token<T, 8>(da.norm, t, threadIdx.x);
+    __syncthreads();  // the reduction scratch is re-used by the next token
+  }
+  grid_sync(nblocks);
+
+  // ---- phase 4: per-head q path
+  if (threadIdx.x == 0) { tl_mark_global(da.tl_q, 0); tl_mark(da.tl_q, 1); tl_mark(da.tl_q, 2); }
+  if (has_q && da.stop_after == 0) q_roles<T, kInt8Out, false>(qc, &tm_a1, &tm_wuq, &tm_wuk, &tm_out0, &tm_out1, da.q, warp, lane, da.tl_q);
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(qc.tmem, 512);
+  if (threadIdx.x == 32) { tl_mark(da.tl_q, 12); tl_mark_global(da.tl_q, 15); tl_mark_global(da.tl_mm1, 15); }
+}
+
 // ============================================================================================ host side
 thread_local char g_err[512] = "";
 static int g_debug_flags = 0;  // bit0: sync + check after each kernel; bit1: write the y0 tap; bit2: time each kernel
+static unsigned* g_wait_log_host = nullptr;  // host-mapped log of stuck barrier waits (debug flag bit11)
 constexpr int kMaxKernels = 8;
 static cudaEvent_t g_ev[kMaxKernels + 1];
 static bool g_ev_ready = false;
@@ -1229,6 +1412,23 @@ static int set_smem_attr(K kern, int bytes, bool* done, const char* name) {
   return MLAPO_OK;
 }
 
+// Token rows per q-path CTA: two token tiles per CTA stream each head's weights once per 256 tokens; when that leaves most
+// SMs idle (few heads, e.g. a TP slice) one tile per CTA doubles the CTA count at the price of re-reading the head's
+// weights from L2.
+static int q_cta_tokens(int n, int h) { return (n > kBlockM && (long long)h * ((n + 255) / 256) >= 96) ? 256 : 128; }
+
+// Decode-sized calls CAN run as one persistent cooperative kernel (k5) when every phase fits a single wave of CTAs.
+// It is opt-in (flag bit5): measured on B200 at C2 it takes 52.4 us against 38.5 us for the four PDL-chained kernels —
+// each of its three grid barriers costs 2-3 us and the norm phase handles a CTA's tokens one after the other
+// (profiles/README.md, "persistent decode kernel") — so the chain stays the default until those two costs are fixed.
+static bool decode_persistent_eligible(const MlapoParams* p, int splits0) {
+  if (!(g_debug_flags & 32)) return false;  // bit5: use the persistent decode kernel where eligible
+  const int n = p->num_tokens, h = p->num_heads;
+  if (n < 1 || n > 256) return false;
+  const int ct = q_cta_tokens(n, h);
+  return kMm1NTiles * splits0 <= num_sms() && h * ((n + ct - 1) / ct) <= num_sms();
+}
+
 template <class T>
 static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLayout& l, cudaStream_t st) {
   const int n = p->num_tokens, d = p->hidden_dim, h = p->num_heads;
@@ -1249,6 +1449,95 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   int dev = 0;
   cudaGetDevice(&dev);
   dev &= 63;
+  const bool persistent = decode_persistent_eligible(p, l.splits0);
+
+  // ---- tensor maps and argument blocks shared by both launch shapes
+  const bool wide = !persistent && l.splits0 == 1 && n >= 1024;  // prefill: no split-K, 256-wide weight tiles
+  const int bn = wide ? kMm1BlockNWide : kMm1BlockN;
+  CUtensorMap tm_a0, tm_wdqkv, tm_part, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1;
+  if ((rc = make_tmap(&tm_a0, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a0, n, d, d, kBlockM, 128))) return rc;
+  if ((rc = make_tmap(&tm_wdqkv, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wdqkv_km, MLAPO_MM1_OUT, d, d, bn, 128))) return rc;
+  if ((rc = make_tmap(&tm_part, CU_TENSOR_MAP_DATA_TYPE_INT32, 4, partial0, n, MLAPO_MM1_OUT, MLAPO_MM1_OUT * 4, kBlockM, 32, l.splits0,
+                      (uint64_t)n * MLAPO_MM1_OUT * 4))) return rc;
+  const int cta_tokens = q_cta_tokens(n, h);
+  const int a1_box_rows = cta_tokens > kBlockM ? 2 * kBlockM : kBlockM;  // one box per stage covers every token tile of the CTA
+  if ((rc = make_tmap(&tm_a1, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a1, n, MLAPO_Q_LORA, MLAPO_Q_LORA, a1_box_rows, 128))) return rc;
+  if ((rc = make_tmap(&tm_wuq, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wuq_km, (uint64_t)h * MLAPO_Q_HEAD, MLAPO_Q_LORA, MLAPO_Q_LORA,
+                      MLAPO_Q_HEAD, 128))) return rc;
+  if ((rc = make_tmap(&tm_wuk, act_dt, 2, p->wuk, (uint64_t)h * MLAPO_Q_NOPE, MLAPO_KV_LORA, MLAPO_KV_LORA * 2, 128, 64))) return rc;
+  if (int8_out) {
+    if ((rc = make_tmap(&tm_o0, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->q_out0, n, (uint64_t)h * MLAPO_KV_LORA, (uint64_t)h * MLAPO_KV_LORA,
+                        kBlockM, 128))) return rc;
+  } else {
+    if ((rc = make_tmap(&tm_o0, act_dt, 2, p->q_out0, n, (uint64_t)h * MLAPO_KV_LORA, (uint64_t)h * MLAPO_KV_LORA * 2, kBlockM, 64))) return rc;
+  }
+  if ((rc = make_tmap(&tm_o1, act_dt, 2, p->q_out1, n, (uint64_t)h * MLAPO_ROPE, (uint64_t)h * MLAPO_ROPE * 2, kBlockM, 64))) return rc;
+
+  NormArgs na{};
+  na.partial = partial0; na.splits = l.splits0; na.n_tokens = n;
+  na.bias0 = per_token ? nullptr : reinterpret_cast<const int32_t*>(p->bias0);
+  na.descale0 = p->descale0; na.descale_is_i64 = p->descale_is_int64;
+  na.tok_scale0 = per_token ? tok_scale : nullptr;
+  na.tok_scale1 = per_token ? tok_scale + n : nullptr;
+  na.gamma1 = p->gamma1; na.beta1 = p->beta1; na.gamma2 = p->gamma2;
+  na.quant_scale1 = p->quant_scale1; na.quant_offset1 = reinterpret_cast<const int8_t*>(p->quant_offset1);
+  na.cos = p->cos; na.sin = p->sin;
+  na.slots = reinterpret_cast<const int32_t*>(p->slot_mapping);
+  na.ctkv_scale = p->ctkv_scale;
+  na.a1 = a1;
+  na.y0_tap = (g_debug_flags & 2) ? ws + l.y0_tap : nullptr;
+  na.kv_cache = p->kv_cache; na.kv_cache_rope = p->kv_cache_rope;
+  na.cache_mode = p->cache_mode;
+  na.cache_slots = (long long)p->num_cache_blocks * p->cache_block_size;
+  na.tl = tl3;
+
+  QArgs qa{};
+  qa.descale1 = p->descale1; qa.descale_is_i64 = p->descale_is_int64;
+  qa.bias1 = per_token ? nullptr : reinterpret_cast<const int32_t*>(p->bias1);
+  qa.tok_scale1 = per_token ? tok_scale + n : nullptr;
+  qa.cos = p->cos; qa.sin = p->sin; qa.q_nope_scale = p->q_nope_scale;
+  qa.num_heads = h; qa.m_total = n; qa.cta_tokens = cta_tokens;
+  const int q_tok_tiles = (n + cta_tokens - 1) / cta_tokens;
+
+  if (persistent) {
+    // ---- k5: one cooperative launch, one CTA per SM
+    DecodeArgs da{};
+    da.hidden = p->hidden_state; da.a0 = a0;
+    da.quant_scale0 = p->quant_scale0; da.quant_offset0 = reinterpret_cast<const int8_t*>(p->quant_offset0);
+    da.tok_scale0 = per_token ? tok_scale : nullptr;
+    da.hidden_dim = d; da.n_tokens = n; da.splits0 = l.splits0; da.q_tok_tiles = q_tok_tiles;
+    da.norm = na; da.q = qa; da.tl_mm1 = tl1; da.tl_q = tl4;
+    da.stop_after = (g_debug_flags >> 8) & 7;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(num_sms());
+    cfg.blockDim = dim3(kQThreads);
+    cfg.dynamicSmemBytes = kDecodeSmemBytes;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeCooperative;  // the grid barriers need every CTA resident
+    at[0].val.cooperative = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    record_event(0, st);
+#define MLAPO_LAUNCH_DECODE(I8, MT)                                                                                        \
+  do {                                                                                                                     \
+    static bool done[64] = {};                                                                                             \
+    if ((rc = set_smem_attr(mla_decode_persistent_kernel<T, I8, MT>, kDecodeSmemBytes, &done[dev], "decode_persistent"))) return rc; \
+    e__ = cudaLaunchKernelEx(&cfg, mla_decode_persistent_kernel<T, I8, MT>, tm_a0, tm_wdqkv, tm_part, tm_a1, tm_wuq, tm_wuk, tm_o0,  \
+                             tm_o1, da);                                                                                   \
+  } while (0)
+    if (n > kBlockM) {
+      if (int8_out) MLAPO_LAUNCH_DECODE(true, 2); else MLAPO_LAUNCH_DECODE(false, 2);
+    } else {
+      if (int8_out) MLAPO_LAUNCH_DECODE(true, 1); else MLAPO_LAUNCH_DECODE(false, 1);
+    }
+#undef MLAPO_LAUNCH_DECODE
+    MLAPO_CHECK_LAUNCH("decode_persistent");
+    record_event(1, st);
+    g_kernel_names[0] = "decode_persistent";
+    return MLAPO_OK;
+  }
+  g_kernel_names[0] = "quant_hidden";
 
   // ---- k1: quantise hiddenState
   record_event(0, st);
@@ -1258,7 +1547,7 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   } else {
     const long long nvec = (long long)n * d / 8;
     const long long one_wave = (long long)num_sms() * 8 * 256;  // threads of one full wave (8 blocks of 256 per SM)
-    if (nvec <= one_wave) {  // decode sizes: one 16-byte vector per thread
+    if (nvec <= one_wave) {  // one 16-byte vector per thread
       e__ = launch_k(quant_hidden_kernel<T, 1>, dim3((unsigned)((nvec + 255) / 256)), dim3(256), 0, st, pdl,
                      reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
                      reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, tl0);
@@ -1273,84 +1562,36 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
 
   // ---- k2: MM1, split-K partial sums
   {
-    CUtensorMap tm_a, tm_b, tm_p;
-    if ((rc = make_tmap(&tm_a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a0, n, d, d, kBlockM, 128))) return rc;
-    const bool wide = l.splits0 == 1 && n >= 1024;  // prefill: no split-K, 256-wide weight tiles
-    const int bn = wide ? kMm1BlockNWide : kMm1BlockN;
-    if ((rc = make_tmap(&tm_b, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wdqkv_km, MLAPO_MM1_OUT, d, d, bn, 128))) return rc;
-    if ((rc = make_tmap(&tm_p, CU_TENSOR_MAP_DATA_TYPE_INT32, 4, partial0, n, MLAPO_MM1_OUT, MLAPO_MM1_OUT * 4, kBlockM, 32, l.splits0,
-                        (uint64_t)n * MLAPO_MM1_OUT * 4))) return rc;
     const int n_tiles = (MLAPO_MM1_OUT + bn - 1) / bn;
     if (wide) {
       static bool done[64] = {};
       if ((rc = set_smem_attr(mm1_splitk_kernel<2, kMm1BlockNWide>, mm1_smem_bytes<2, kMm1BlockNWide>(), &done[dev], "mm1<2,256>"))) return rc;
       e__ = launch_k(mm1_splitk_kernel<2, kMm1BlockNWide>, dim3(n_tiles, 1, (n + 255) / 256), dim3(kGemmThreads),
-                     mm1_smem_bytes<2, kMm1BlockNWide>(), st, pdl, tm_a, tm_b, tm_p, n, d / kBlockKBytes, tl1);
+                     mm1_smem_bytes<2, kMm1BlockNWide>(), st, pdl, tm_a0, tm_wdqkv, tm_part, n, d / kBlockKBytes, tl1);
     } else if (n > kBlockM) {
       static bool done[64] = {};
       if ((rc = set_smem_attr(mm1_splitk_kernel<2, kMm1BlockN>, mm1_smem_bytes<2, kMm1BlockN>(), &done[dev], "mm1<2,128>"))) return rc;
       e__ = launch_k(mm1_splitk_kernel<2, kMm1BlockN>, dim3(n_tiles, l.splits0, (n + 255) / 256), dim3(kGemmThreads),
-                     mm1_smem_bytes<2, kMm1BlockN>(), st, pdl, tm_a, tm_b, tm_p, n, d / kBlockKBytes, tl1);
+                     mm1_smem_bytes<2, kMm1BlockN>(), st, pdl, tm_a0, tm_wdqkv, tm_part, n, d / kBlockKBytes, tl1);
     } else {
       static bool done[64] = {};
       if ((rc = set_smem_attr(mm1_splitk_kernel<1, kMm1BlockN>, mm1_smem_bytes<1, kMm1BlockN>(), &done[dev], "mm1<1,128>"))) return rc;
       e__ = launch_k(mm1_splitk_kernel<1, kMm1BlockN>, dim3(n_tiles, l.splits0, 1), dim3(kGemmThreads), mm1_smem_bytes<1, kMm1BlockN>(),
-                     st, pdl, tm_a, tm_b, tm_p, n, d / kBlockKBytes, tl1);
+                     st, pdl, tm_a0, tm_wdqkv, tm_part, n, d / kBlockKBytes, tl1);
     }
     MLAPO_CHECK_LAUNCH("mm1_splitk");
   }
   record_event(2, st);
 
   // ---- k3: norms, quant, rope, cache scatter
-  {
-    NormArgs a{};
-    a.partial = partial0; a.splits = l.splits0; a.n_tokens = n;
-    a.bias0 = per_token ? nullptr : reinterpret_cast<const int32_t*>(p->bias0);
-    a.descale0 = p->descale0; a.descale_is_i64 = p->descale_is_int64;
-    a.tok_scale0 = per_token ? tok_scale : nullptr;
-    a.tok_scale1 = per_token ? tok_scale + n : nullptr;
-    a.gamma1 = p->gamma1; a.beta1 = p->beta1; a.gamma2 = p->gamma2;
-    a.quant_scale1 = p->quant_scale1; a.quant_offset1 = reinterpret_cast<const int8_t*>(p->quant_offset1);
-    a.cos = p->cos; a.sin = p->sin;
-    a.slots = reinterpret_cast<const int32_t*>(p->slot_mapping);
-    a.ctkv_scale = p->ctkv_scale;
-    a.a1 = a1;
-    a.y0_tap = (g_debug_flags & 2) ? ws + l.y0_tap : nullptr;
-    a.kv_cache = p->kv_cache; a.kv_cache_rope = p->kv_cache_rope;
-    a.cache_mode = p->cache_mode;
-    a.cache_slots = (long long)p->num_cache_blocks * p->cache_block_size;
-    a.tl = tl3;
-    if (l.splits0 == 1) e__ = launch_k(norm_rope_cache_kernel<T, 1>, dim3(n), dim3(kNormThreads), 0, st, pdl, a);  // prefill: no split-K
-    else e__ = launch_k(norm_rope_cache_kernel<T, 8>, dim3(n), dim3(kNormThreads), 0, st, pdl, a);
-    MLAPO_CHECK_LAUNCH("norm_rope_cache");
-  }
+  if (l.splits0 == 1) e__ = launch_k(norm_rope_cache_kernel<T, 1>, dim3(n), dim3(kNormThreads), 0, st, pdl, na);  // prefill: no split-K
+  else e__ = launch_k(norm_rope_cache_kernel<T, 8>, dim3(n), dim3(kNormThreads), 0, st, pdl, na);
+  MLAPO_CHECK_LAUNCH("norm_rope_cache");
   record_event(3, st);
 
-  // ---- k4: fused MM2 + dequant + RoPE + W_UK absorb, one CTA per (head, 256-token super-tile)
+  // ---- k4: fused MM2 + dequant + RoPE + W_UK absorb, one CTA per (head, token super-tile)
   {
-    CUtensorMap tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1;
-    // Two token tiles per CTA stream each head's weights once per 256 tokens; when that leaves most SMs idle (few heads,
-    // e.g. a TP slice) one tile per CTA doubles the CTA count at the price of re-reading the head's weights from L2.
-    const int cta_tokens = (n > kBlockM && (long long)h * ((n + 255) / 256) >= 96) ? 256 : 128;
-    const int a1_box_rows = cta_tokens > kBlockM ? 2 * kBlockM : kBlockM;  // one box per stage covers every token tile of the CTA
-    if ((rc = make_tmap(&tm_a1, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a1, n, MLAPO_Q_LORA, MLAPO_Q_LORA, a1_box_rows, 128))) return rc;
-    if ((rc = make_tmap(&tm_wuq, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wuq_km, (uint64_t)h * MLAPO_Q_HEAD, MLAPO_Q_LORA, MLAPO_Q_LORA,
-                        MLAPO_Q_HEAD, 128))) return rc;
-    if ((rc = make_tmap(&tm_wuk, act_dt, 2, p->wuk, (uint64_t)h * MLAPO_Q_NOPE, MLAPO_KV_LORA, MLAPO_KV_LORA * 2, 128, 64))) return rc;
-    if (int8_out) {
-      if ((rc = make_tmap(&tm_o0, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->q_out0, n, (uint64_t)h * MLAPO_KV_LORA, (uint64_t)h * MLAPO_KV_LORA,
-                          kBlockM, 128))) return rc;
-    } else {
-      if ((rc = make_tmap(&tm_o0, act_dt, 2, p->q_out0, n, (uint64_t)h * MLAPO_KV_LORA, (uint64_t)h * MLAPO_KV_LORA * 2, kBlockM, 64))) return rc;
-    }
-    if ((rc = make_tmap(&tm_o1, act_dt, 2, p->q_out1, n, (uint64_t)h * MLAPO_ROPE, (uint64_t)h * MLAPO_ROPE * 2, kBlockM, 64))) return rc;
-    QArgs qa{};
-    qa.descale1 = p->descale1; qa.descale_is_i64 = p->descale_is_int64;
-    qa.bias1 = per_token ? nullptr : reinterpret_cast<const int32_t*>(p->bias1);
-    qa.tok_scale1 = per_token ? tok_scale + n : nullptr;
-    qa.cos = p->cos; qa.sin = p->sin; qa.q_nope_scale = p->q_nope_scale;
-    qa.num_heads = h; qa.m_total = n; qa.cta_tokens = cta_tokens;
-    dim3 grid(h, (n + cta_tokens - 1) / cta_tokens);
+    dim3 grid(h, q_tok_tiles);
     if (int8_out) {
       static bool done[64] = {};
       if ((rc = set_smem_attr(q_fused_kernel<T, true>, kQSmemBytes, &done[dev], "q_fused<int8>"))) return rc;
@@ -1385,9 +1626,23 @@ const char* mlapo_last_error(void) { return g_err; }
 int mlapo_set_debug_flags(int flags) {
   const int old = g_debug_flags;
   g_debug_flags = flags;
+  if ((flags & 2048) && !g_wait_log_host) {  // bit11: register a host-mapped log for stuck barrier waits
+    unsigned* dptr = nullptr;
+    if (cudaHostAlloc(reinterpret_cast<void**>(&g_wait_log_host), 4096, cudaHostAllocMapped) == cudaSuccess &&
+        cudaHostGetDevicePointer(reinterpret_cast<void**>(&dptr), g_wait_log_host, 0) == cudaSuccess) {
+      memset(g_wait_log_host, 0, 4096);
+      cudaMemcpyToSymbol(ptx::g_wait_log, &dptr, sizeof dptr);
+    }
+  }
   return old;
 }
-
+// Debug: copies the stuck-wait log {count, then {cta, thread, barrier, parity} x count}; returns the count.  Reads host
+// memory only, so it still works after a trap.
+int mlapo_debug_read_wait_log(unsigned* out, int cap_words) {
+  if (!g_wait_log_host) return -1;
+  for (int i = 0; i < cap_words && i < 1024; ++i) out[i] = g_wait_log_host[i];
+  return (int)g_wait_log_host[0];
+}
 // Debug/profiling hook (flag bit2): per-kernel durations of the last mla_preprocess_launch on this thread's device.
 int mlapo_get_kernel_times_ms(float* out_ms, int cap) {
   if (!g_ev_ready || g_ev_count < 2) return 0;
@@ -1416,8 +1671,8 @@ int mlapo_get_workspace_size(const MlapoParams* p, size_t* bytes) {
 }
 
 int mlapo_launches_per_call(const MlapoParams* p) {
-  (void)p;
-  return 4;
+  if (check_params(p)) return 0;
+  return decode_persistent_eligible(p, choose_splits0(p->num_tokens, p->hidden_dim)) ? 1 : 4;
 }
 
 int mlapo_repack_nz_weight(const void* w_nz, void* w_km, int32_t k, int32_t n_out, void* stream) {

@@ -49,12 +49,35 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return done != 0;
 }
-// Bounded wait: a protocol bug becomes a trap (launch failure) instead of a hung GPU.
+// Bounded wait: a protocol bug becomes a trap (launch failure) instead of a hung GPU.  When a host-mapped log buffer has
+// been registered (debug flag bit11) the stuck wait is first recorded there {cta, thread, barrier smem address, parity},
+// where the host can still read it after the trap has taken the context down.
+__device__ unsigned* g_wait_log = nullptr;
+__device__ __forceinline__ void wait_timeout(unsigned a, unsigned b, unsigned c, unsigned d) {
+  unsigned* log = g_wait_log;
+  if (log) {
+    const unsigned i = atomicAdd(log, 1u);
+    if (i < 32) { log[1 + 4 * i] = a; log[2 + 4 * i] = b; log[3 + 4 * i] = c; log[4 + 4 * i] = d; }
+    __threadfence_system();
+    const long long t0 = clock64();
+    while (clock64() - t0 < 200000000LL) {}  // let the other stuck waiters log too
+  }
+  __trap();
+}
+// Debug progress marks into the same host-mapped buffer: word 256 + 4*cta + role.
+__device__ __forceinline__ void progress_mark(int role, unsigned val) {
+  unsigned* log = g_wait_log;
+  if (log) {
+    const unsigned cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+    if (cta < 160) { log[256 + 4 * cta + role] = val; __threadfence_system(); }
+  }
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) __trap();  // ~2 s at 2 GHz
+    if (clock64() - t0 > 4000000000LL)  // ~2 s at 2 GHz
+      wait_timeout(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z), threadIdx.x, bar, parity);
   }
 }
 

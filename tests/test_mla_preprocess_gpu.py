@@ -44,13 +44,18 @@ def check(res, case):
         assert res["q_out0"][0] <= 2e-3 * res["q_out0"][1], res["q_out0"]  # and almost always bit-identical
 
 
+@pytest.mark.parametrize("persistent", [False, True], ids=["chained", "persistent"])
 @pytest.mark.parametrize("cfg", CASES, ids=[f"N{c[0]}-H{c[1]}-D{c[2]}-{c[3]}-{c[4]}-{c[5][:9]}" for c in CASES])
-def test_parity_vs_oracle(cfg, cuda_device):
+def test_parity_vs_oracle(cfg, persistent, cuda_device):
+    """`chained` = the default launch shape (four PDL-chained kernels); `persistent` = the opt-in single cooperative kernel
+    for calls of <= 256 tokens.  Both meet the same bars."""
     n, h, d, dt, mode, qm, neg = cfg
+    if persistent and n > 256:
+        pytest.skip("the persistent decode kernel covers <= 256 tokens")
     case = orc.gen_case(N=n, H=h, D=d, dtype=DT[dt], cache_mode=mode, seed=42, num_blocks=max(12, n // 64), neg_slot_frac=neg)
     case.t["kv_cache"].fill_(5)
     case.t["kv_cache_rope"].fill_(5)
-    g, taps = hz.run_cuda(case, cuda_device, quant_mode=qm)
+    g, taps = hz.run_cuda(case, cuda_device, quant_mode=qm, persistent=persistent)
     res, _, _ = hz.compare(case, qm, g, taps)
     check(res, case)
 

@@ -10,12 +10,12 @@ import torch
 import bench
 from sgl_kernel_npu import cabi
 
-MM1 = ["gtimer", "start", "prologue", "upstream", "first_full", "last_full", "mma_done", "epi_issued", "stores_read", "end"]
+MM1 = ["gtimer", "start", "prologue/phase2", "upstream", "first_full", "last_full", "mma_done", "epi_issued", "stores_read", "end/mm1-phase-done"]
 QF = ["gtimer", "start", "prologue", "upstream", "first_full", "last_full", "mm2_done", "epi2_done", "unit0", "unit4", "drain_issued",
       "stores_read", "end"]
 
 
-def main(workload="c2", pdl=False):
+def main(workload="c2", pdl=False, persistent=False):
     n, h, d, cache_mode, _ = bench.WORKLOADS[workload]
     dev = torch.device("cuda:0")
     gen = torch.Generator(device=dev).manual_seed(1)
@@ -25,7 +25,7 @@ def main(workload="c2", pdl=False):
     kv, kvr = bench.cache_tensors(torch, cache_mode, 64, dev)
     q0 = torch.zeros((n, h, 512), dtype=torch.int8 if cache_mode == "int8_nzcache" else torch.bfloat16, device=dev)
     q1 = torch.zeros((n, h, 64), dtype=torch.bfloat16, device=dev)
-    cabi.set_debug_flags(8 | (0 if pdl else 1))
+    cabi.set_debug_flags(8 | (0 if pdl else 1) | (32 if persistent else 0))
     ps = []
     for w in sets:
         ps.append(cabi.build_params(hid, w["wdqkv_km"], w["descale0"], w["gamma1"], w["beta1"], w["wuq_km"], w["descale1"], w["gamma2"],
@@ -56,7 +56,7 @@ def main(workload="c2", pdl=False):
         if a.shape[0]:
             spans[name] = (a[:, 0].min(), np.median(a[:, 0]), a[:, 15].max(), a[:, 14].max() if k == 3 else 0)
     if spans:
-        t0 = spans["quant_hidden"][0]
+        t0 = spans["quant_hidden"][0] if "quant_hidden" in spans else min(v[0] for v in spans.values())
         print("call timeline (us from quant start): kernel first-CTA-start / median-CTA-start / last-CTA-end")
         for name, (a0, am, a1, w) in spans.items():
             extra = f"  upstream-wait passed by {(w - t0) / 1e3:7.2f}" if w else ""
@@ -77,4 +77,5 @@ def main(workload="c2", pdl=False):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1] if len(sys.argv) > 1 else "c2", pdl=len(sys.argv) > 2 and sys.argv[2] == "pdl")
+    main(sys.argv[1] if len(sys.argv) > 1 else "c2", pdl=len(sys.argv) > 2 and sys.argv[2] in ("pdl", "persistent"),
+         persistent=len(sys.argv) > 2 and sys.argv[2] == "persistent")
