@@ -341,7 +341,6 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
           }
         }
         ptx::umma_commit(ptx::smem_u32(empty_bar + stage));  // frees the smem slot when these MMAs retire
-        ptx::progress_mark(1, 10 + i);
       }
       __syncwarp();
       if (++stage == STAGES) { stage = 0; phase ^= 1; }
