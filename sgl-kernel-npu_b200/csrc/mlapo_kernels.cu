@@ -276,8 +276,8 @@ __device__ __forceinline__ void mm1_issue_weights(const Mm1Ctx<MT, BN>& c, const
 }
 
 // Warp roles of MM1: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer, warps 2..5 = epilogue (TMEM lane quarter = warp%4);
-// other warps fall through.  kStandalone: own kernel under PDL (requests weights, then waits for the upstream kernel);
-// otherwise the caller has already issued mm1_issue_weights() and guarantees a0 is complete.
+// other warps fall through.  The caller has already issued mm1_issue_weights().  kStandalone: own kernel under PDL, the
+// producer waits for the upstream kernel before it touches a0; otherwise the caller guarantees a0 is complete.
 template <int MT, int BN, bool kStandalone>
 __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtensorMap* tm_a, const CUtensorMap* tm_b,
                                           const CUtensorMap* tm_p, int warp, int lane, long long* tl) {
@@ -296,9 +296,8 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
       const uint32_t stage_tx = (uint32_t)(mt_valid * kTile16K + B_BYTES);
       const int pre = nkb < STAGES ? nkb : STAGES;
       if (kStandalone) {
-        mm1_issue_weights<MT, BN>(c, tm_b);  // weights first: independent of the upstream kernel
-        ptx::griddep_wait();                 // a0 is produced by the quantise kernel
-        tl_mark(tl, 3);                      // upstream complete
+        ptx::griddep_wait();  // a0 is produced by the quantise kernel (the weight tiles were requested at kernel start)
+        tl_mark(tl, 3);       // upstream complete
       }
       for (int i = 0; i < pre; ++i) {
         const uint32_t fb = ptx::smem_u32(full_bar + i);
@@ -306,7 +305,6 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
           ptx::tma_load_2d(ptx::smem_u32(smem + i * STAGE_BYTES + m * kTile16K), tm_a, fb, (kb0 + i) * kBlockKBytes,
                            m0 + m * kBlockM, ptx::kEvictLast);
       }
-      ptx::progress_mark(0, 1);
       uint32_t stage = 0, phase = 1;  // stages 0..pre-1 are in their first use; the next wrap waits for phase 0 of empty
       for (int i = pre; i < nkb; ++i) {
         ptx::mbar_wait(ptx::smem_u32(empty_bar + stage), phase ^ 1);
@@ -356,11 +354,11 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
     ptx::mbar_wait(ptx::smem_u32(done_bar), 0);   // all MMAs retired => every pipeline stage has been consumed
     __syncwarp();
     ptx::tc_fence_after();
-    if (issuer) { tl_mark(tl, 6); ptx::progress_mark(2, 40); }  // MMAs retired
+    if (issuer) tl_mark(tl, 6);  // MMAs retired
     __syncwarp();                                 // tcgen05.ld below is warp-aligned: reconverge after the one-lane branch
     for (int m = 0; m < mt_valid; ++m) {
       if (m > 0) {  // the staging tiles are re-used per token tile: the previous tile's stores must have been read
-        if (issuer) { ptx::progress_mark(2, 42); ptx::tma_store_wait_read<0>(); ptx::progress_mark(2, 43); }
+        if (issuer) ptx::tma_store_wait_read<0>();
         ptx::named_bar_sync(1, 128);
       }
 #pragma unroll 1
@@ -380,7 +378,6 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
           if (n0 + g * 32 < MLAPO_MM1_OUT)
             ptx::tma_store_3d(tm_p, ptx::smem_u32(smem + g * kTile16K), n0 + g * 32, m0 + m * kBlockM, split);
         ptx::tma_store_commit();
-        ptx::progress_mark(2, 44 + m);
       }
     }
     if (issuer) { tl_mark(tl, 7); ptx::tma_store_wait_read<0>(); tl_mark(tl, 8); }
@@ -402,17 +399,15 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
   c.set_work(blockIdx.x, blockIdx.y, gridDim.y, blockIdx.z, m_total, kb_total);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  if (warp == 0 && lane == 0) {
-    ptx::prefetch_tmap(&tm_a);
+  if (warp == 0 && lane == 0) {  // barriers + the first weight tiles before anything else: they depend on nothing
     ptx::prefetch_tmap(&tm_b);
+    mm1_init_barriers<MT, BN>(c.bars);
+    ptx::fence_mbar_init();
+    mm1_issue_weights<MT, BN>(c, &tm_b);
+    ptx::prefetch_tmap(&tm_a);
     ptx::prefetch_tmap(&tm_p);
   }
   if (warp == 1) {
-    if (lane == 0) {
-      mm1_init_barriers<MT, BN>(c.bars);
-      ptx::fence_mbar_init();
-    }
-    __syncwarp();
     ptx::tmem_alloc(ptx::smem_u32(tmem_slot), C::TMEM_COLS);
     ptx::tmem_relinquish();
   }
@@ -694,11 +689,11 @@ struct QArgs {
 // Where one CTA's q-path work item lives.
 struct QCtx {
   uint8_t* smem;     // 224 KB pipeline / overlay region, 1024-byte aligned
-  uint64_t* bars;    // full[4] empty[4] mm2_done wuk_full[4] qn_ready[2] unit_full[4] buf_empty[4]
+  uint64_t* bars;    // full[4] empty[4] mm2_done wuk_full[4] qn_ready[2] unit_full[4] buf_empty[4] rope_done[2]
   int2* s_cst;       // per column {bias, descale bits}
   uint32_t tmem;     // base of a 512-column TMEM allocation
   int head, tok0, num_mt, load_mt;
-  static constexpr int NUM_BARS = 23;
+  static constexpr int NUM_BARS = 25;
 
   __device__ void set_work(int head_, int tok_tile, const QArgs& qa) {
     head = head_;
@@ -716,6 +711,8 @@ __device__ __forceinline__ void q_init_barriers(uint64_t* bars) {  // one thread
     ptx::mbar_init(ptx::smem_u32(bars + 15 + i), 1);
     ptx::mbar_init(ptx::smem_u32(bars + 19 + i), 128);
   }
+  ptx::mbar_init(ptx::smem_u32(bars + 23), 128);
+  ptx::mbar_init(ptx::smem_u32(bars + 24), 128);
 }
 
 // One thread: arm the four MM2 stages and request their W_UQ k-blocks (which depend on nothing upstream).
@@ -730,7 +727,8 @@ __device__ __forceinline__ void q_issue_weights(const QCtx& c, const CUtensorMap
 }
 
 // Warp roles of the q path: warp 0 = TMA producer, warp 1 = MMA issuer, warps 2..5 / 6..9 = epilogue groups of token tile 0 / 1.
-// kStandalone: own kernel under PDL; otherwise the caller has issued q_issue_weights() and guarantees a1 is complete.
+// The caller has already issued q_issue_weights().  kStandalone: own kernel under PDL (waits for the upstream kernel
+// before touching a1 / the per-token scales); otherwise the caller guarantees they are complete.
 template <class T, bool kInt8Out, bool kStandalone>
 __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1, const CUtensorMap* tm_wuq, const CUtensorMap* tm_wuk,
                                         const CUtensorMap* tm_out0, const CUtensorMap* tm_out1, const QArgs& qa, int warp, int lane,
@@ -743,6 +741,7 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
   uint64_t* const qn_ready = c.bars + 13;   // [2]  epilogue group m -> MMA: q_nope tile m in smem and acc2[m] drained
   uint64_t* const unit_full = c.bars + 15;  // [4]  (m*2 + buffer) MMA -> epilogue
   uint64_t* const buf_empty = c.bars + 19;  // [4]  (m*2 + buffer) epilogue -> MMA
+  uint64_t* const rope_done = c.bars + 23;  // [2]  epilogue group m -> MMA: acc2[m] columns 128..191 drained as well
   int2* const s_cst = c.s_cst;
   const uint32_t tmem = c.tmem;
   const int head = c.head, tok0 = c.tok0, num_mt = c.num_mt, load_mt = c.load_mt;
@@ -761,8 +760,7 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
                          ptx::kEvictLast);
       };
       if (kStandalone) {
-        q_issue_weights(c, tm_wuq);  // weights first: independent of the upstream kernel
-        ptx::griddep_wait();         // a1 is produced by the norm kernel
+        ptx::griddep_wait();  // a1 is produced by the norm kernel (the first W_UQ k-blocks were requested at kernel start)
         tl_mark(tl, 3);
       }
       for (int kb = 0; kb < kQStages; ++kb) load_a(kb);
@@ -822,7 +820,8 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
     for (int c = 0; c < 4; ++c) {
       for (int m = 0; m < num_mt; ++m) {
         const int ub = m * 2 + (c & 1);
-        if (c == 0) ptx::mbar_wait(ptx::smem_u32(qn_ready + m), 0);
+        if (c == 0) ptx::mbar_wait(ptx::smem_u32(qn_ready + m), 0);   // buffer 0 = acc2[m] columns 0..127 (nope, drained)
+        if (c == 1) ptx::mbar_wait(ptx::smem_u32(rope_done + m), 0);  // buffer 1 overlaps acc2[m] columns 128..191 (rope)
         if (c >= 2) ptx::mbar_wait(ptx::smem_u32(buf_empty + ub), 0);
         if (m == 0) ptx::mbar_wait(ptx::smem_u32(wuk_full + c), 0);
         __syncwarp();
@@ -899,12 +898,9 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
       if (issuer && g == 0) tl_mark(tl, 6);  // MM2 retired
 
       const uint32_t acc2 = lane_base + m * 256;
-      // nope slice -> swizzled A-operand tiles (kb = c0/64)
-#pragma unroll 1
-      for (int c0 = 0; c0 < 128; c0 += 32) {
-        uint32_t r[32];
-        ptx::tmem_ld_32x32b_x32(acc2 + c0, r);
-        ptx::tmem_ld_wait();
+      // nope slice -> swizzled A-operand tiles (kb = c0/64).  The TMEM load of the next 32 columns is in flight while the
+      // current 32 are dequantised (tcgen05.wait::ld covers every outstanding load, so exactly one is kept outstanding).
+      auto nope_chunk = [&](const uint32_t (&r)[32], int c0) {
         const uint32_t tile = ptx::smem_u32(smem + kQNopeOff + (m * 2 + (c0 >> 6)) * kTile16K);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -913,24 +909,38 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
           for (int u = 0; u < 4; ++u) w[u] = Act<T>::pack(deq(r[8 * j + 2 * u], c0 + 8 * j + 2 * u), deq(r[8 * j + 2 * u + 1], c0 + 8 * j + 2 * u + 1));
           ptx::st_shared_v4(tile + ptx::sw128_offset(row, ((c0 & 63) >> 3) + j), w[0], w[1], w[2], w[3]);
         }
-      }
-      // rope slice: columns 128..191
+      };
       float x[64];
       {
-        uint32_t r[32];
-        ptx::tmem_ld_32x32b_x32(acc2 + 128, r);
+        uint32_t ra[32], rb[32];
+        ptx::tmem_ld_32x32b_x32(acc2 + 0, ra);
         ptx::tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) x[j] = Act<T>::round(deq(r[j], 128 + j));
-        ptx::tmem_ld_32x32b_x32(acc2 + 160, r);
+        ptx::tmem_ld_32x32b_x32(acc2 + 32, rb);
+        nope_chunk(ra, 0);
         ptx::tmem_ld_wait();
+        ptx::tmem_ld_32x32b_x32(acc2 + 64, ra);
+        nope_chunk(rb, 32);
+        ptx::tmem_ld_wait();
+        ptx::tmem_ld_32x32b_x32(acc2 + 96, rb);
+        nope_chunk(ra, 64);
+        ptx::tmem_ld_wait();
+        ptx::tmem_ld_32x32b_x32(acc2 + 128, ra);  // rope slice: columns 128..191
+        nope_chunk(rb, 96);
+        // q_nope rows written and acc2[m] columns 0..127 read: the first absorb unit of this token tile may start
+        ptx::fence_proxy_async_smem();
+        ptx::tmem_ld_wait();
+        ptx::tmem_ld_32x32b_x32(acc2 + 160, rb);
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(ptx::smem_u32(qn_ready + m));
 #pragma unroll
-        for (int j = 0; j < 32; ++j) x[32 + j] = Act<T>::round(deq(r[j], 160 + j));
+        for (int j = 0; j < 32; ++j) x[j] = Act<T>::round(deq(ra[j], 128 + j));
+        ptx::tmem_ld_wait();
+        // acc2[m] fully read: the absorb buffer that overlaps the rope columns is free too
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(ptx::smem_u32(rope_done + m));
+#pragma unroll
+        for (int j = 0; j < 32; ++j) x[32 + j] = Act<T>::round(deq(rb[j], 160 + j));
       }
-      // acc2[m] fully read + q_nope rows written: release to the MMA warp
-      ptx::fence_proxy_async_smem();
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(ptx::smem_u32(qn_ready + m));
 
       stage_acquire();
 #pragma unroll
@@ -1052,24 +1062,22 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
   QCtx c;
   c.smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   c.bars = reinterpret_cast<uint64_t*>(c.smem + kQBarOff);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(c.bars + 24);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(c.bars + 26);
   c.s_cst = reinterpret_cast<int2*>(c.smem + kQBarOff + 256);
   c.set_work(blockIdx.x, blockIdx.y, qa);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  if (warp == 0 && lane == 0) {
-    ptx::prefetch_tmap(&tm_a1);
+  if (warp == 0 && lane == 0) {  // barriers + the first W_UQ k-blocks before anything else: they depend on nothing
     ptx::prefetch_tmap(&tm_wuq);
+    q_init_barriers(c.bars);
+    ptx::fence_mbar_init();
+    q_issue_weights(c, &tm_wuq);
+    ptx::prefetch_tmap(&tm_a1);
     ptx::prefetch_tmap(&tm_wuk);
     ptx::prefetch_tmap(&tm_out0);
     ptx::prefetch_tmap(&tm_out1);
   }
   if (warp == 1) {
-    if (lane == 0) {
-      q_init_barriers(c.bars);
-      ptx::fence_mbar_init();
-    }
-    __syncwarp();
     ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
     ptx::tmem_relinquish();
   }
@@ -1173,7 +1181,7 @@ mla_decode_persistent_kernel(const __grid_constant__ CUtensorMap tm_a0, const __
   QCtx qc;
   qc.smem = smem;
   qc.bars = reinterpret_cast<uint64_t*>(smem + kQBarOff);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(qc.bars + 24);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(qc.bars + 26);
   qc.s_cst = reinterpret_cast<int2*>(smem + kQBarOff + 256);
   M1 mc;
   mc.smem = smem;
@@ -1230,11 +1238,10 @@ mla_decode_persistent_kernel(const __grid_constant__ CUtensorMap tm_a0, const __
     if (has_mm1 && warp == 1) for (int i = 0; i < (mc.nkb < M1::STAGES ? mc.nkb : M1::STAGES); ++i) (void)i;
   }
   if (has_mm1 && da.stop_after != 1) mm1_roles<MT, kMm1BlockN, false>(mc, &tm_a0, &tm_wdqkv, &tm_part, warp, lane, da.tl_mm1);
-  if (threadIdx.x == 64 && has_mm1) { ptx::progress_mark(2, 50); ptx::tma_store_wait<0>(); ptx::progress_mark(2, 51); }  // partial tiles fully written, not just read out of smem
+  if (threadIdx.x == 64 && has_mm1) ptx::tma_store_wait<0>();  // partial tiles fully written, not just read out of smem
   ptx::tc_fence_before();
   __syncthreads();                                              // the MM1 pipeline bytes are free again
   ptx::tc_fence_after();
-  if (threadIdx.x == 0) ptx::progress_mark(3, 60);
   if (threadIdx.x == 32) tl_mark(da.tl_mm1, 9);
   // first W_UQ k-blocks of this CTA's head: requested now, they land while the norm phase runs
   if (warp == 0 && lane == 0 && has_q && (da.stop_after == 0 || da.stop_after > 3)) q_issue_weights(qc, &tm_wuq);

@@ -64,14 +64,6 @@ __device__ __forceinline__ void wait_timeout(unsigned a, unsigned b, unsigned c,
   }
   __trap();
 }
-// Debug progress marks into the same host-mapped buffer: word 256 + 4*cta + role.
-__device__ __forceinline__ void progress_mark(int role, unsigned val) {
-  unsigned* log = g_wait_log;
-  if (log) {
-    const unsigned cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
-    if (cta < 160) { log[256 + 4 * cta + role] = val; __threadfence_system(); }
-  }
-}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
