@@ -1230,6 +1230,7 @@ mla_decode_persistent_kernel(const __grid_constant__ CUtensorMap tm_a0, const __
     quant_vectors<T, 4>(reinterpret_cast<const T*>(da.hidden), da.a0, qs, (long long)da.n_tokens * da.hidden_dim / 8,
                         (long long)cta * blockDim.x + threadIdx.x, (long long)nblocks * blockDim.x);
   }
+  if (threadIdx.x == 0) tl_mark(da.tl_mm1, 10);  // quant done, entering barrier 1
   grid_sync(nblocks);
 
   // ---- phase 2: MM1 split-K partial sums
@@ -1246,6 +1247,7 @@ mla_decode_persistent_kernel(const __grid_constant__ CUtensorMap tm_a0, const __
   // first W_UQ k-blocks of this CTA's head: requested now, they land while the norm phase runs
   if (warp == 0 && lane == 0 && has_q && (da.stop_after == 0 || da.stop_after > 3)) q_issue_weights(qc, &tm_wuq);
   grid_sync(nblocks);
+  if (threadIdx.x == 0) tl_mark(da.tl_mm1, 11);  // barrier 2 passed
   const bool run3 = da.stop_after == 0 || da.stop_after >= 3;
 
   // ---- phase 3: norms, quant, RoPE, cache scatter (one token at a time per CTA)
@@ -1253,6 +1255,7 @@ mla_decode_persistent_kernel(const __grid_constant__ CUtensorMap tm_a0, const __
     norm_token<T, 8>(da.norm, t, threadIdx.x);
     __syncthreads();  // the reduction scratch is re-used by the next token
   }
+  if (threadIdx.x == 0) tl_mark(da.tl_mm1, 12);  // norm done, entering barrier 3
   grid_sync(nblocks);
 
   // ---- phase 4: per-head q path

@@ -10,7 +10,8 @@ import torch
 import bench
 from sgl_kernel_npu import cabi
 
-MM1 = ["gtimer", "start", "prologue/phase2", "upstream", "first_full", "last_full", "mma_done", "epi_issued", "stores_read", "end/mm1-phase-done"]
+MM1 = ["gtimer", "start", "prologue/phase2", "upstream", "first_full", "last_full", "mma_done", "epi_issued", "stores_read", "end/mm1-phase-done",
+       "P:quant_done", "P:barrier2_passed", "P:norm_done"]
 QF = ["gtimer", "start", "prologue", "upstream", "first_full", "last_full", "mm2_done", "epi2_done", "unit0", "unit4", "drain_issued",
       "stores_read", "end"]
 
