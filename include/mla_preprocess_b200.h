@@ -179,6 +179,7 @@ int mlapo_launches_per_call(const MlapoParams* p);
  * CMakeLists.txt:48-53).  flags: bit0 = synchronise and check after every kernel (errors name the kernel),
  * bit1 = also write the dequantised MM1 rows y0 (act [N,2112]) after the last workspace region,
  * bit2 = record CUDA events around every kernel of the next launches, bit3 = per-CTA clock marks (timeline region),
+ * bit6 = keep the one-CTA-per-unit q-path kernel where the streaming form would be used,
  * bit5 = run decode-sized calls (<= 256 tokens) as the single persistent cooperative kernel instead of four chained kernels,
  * bits 8-10 = leave the persistent kernel after that phase, bit11 = log stuck barrier waits to a host-mapped buffer before trapping.
  * Returns the previous flags.

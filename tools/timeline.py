@@ -62,7 +62,9 @@ def main(workload="c2", pdl=False, persistent=False):
         for name, (a0, am, a1, w) in spans.items():
             extra = f"  upstream-wait passed by {(w - t0) / 1e3:7.2f}" if w else ""
             print(f"   {name:16s} {(a0 - t0) / 1e3:7.2f} {(am - t0) / 1e3:7.2f} {(a1 - t0) / 1e3:7.2f}{extra}")
-    for k, (name, labels) in enumerate([("mm1_splitk", MM1), ("q_fused", QF)]):
+    QS = ["gtimer", "start"] + [f"u{i}:{w}" for i in range(4) for w in ("mm2_done", "acc2_released", "drained")]
+    stream = n > 256 and h * ((n + 255) // 256) > 148
+    for k, (name, labels) in enumerate([("mm1_splitk", MM1), ("q_stream" if stream else "q_fused", QS if stream else QF)]):
         a = tl[k]
         used = a[:, 1] != 0
         a = a[used]
