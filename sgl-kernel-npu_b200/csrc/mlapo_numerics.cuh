@@ -1,0 +1,77 @@
+// Numeric contract of mla_preprocess (activation types, the fp32->fp16->int8 saturating quantiser, vector pack/unpack) and the debug timeline marks.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <type_traits>
+
+#include "../../include/mla_preprocess_b200.h"
+#include "sm100_ptx.cuh"
+
+namespace mlapo {
+
+// ============================================================================================ numerics
+template <class T> struct Act;
+template <> struct Act<__nv_bfloat16> {
+  static __device__ __forceinline__ float to_f(__nv_bfloat16 v) { return __bfloat162float(v); }
+  static __device__ __forceinline__ __nv_bfloat16 from_f(float f) { return __float2bfloat16_rn(f); }
+  static __device__ __forceinline__ float lo(uint32_t w) { return __uint_as_float(w << 16); }
+  static __device__ __forceinline__ float hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
+  static __device__ __forceinline__ uint32_t pack(float a, float b) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+  }
+  static __device__ __forceinline__ float round(float f) { return __bfloat162float(__float2bfloat16_rn(f)); }
+};
+template <> struct Act<__half> {
+  static __device__ __forceinline__ float to_f(__half v) { return __half2float(v); }
+  static __device__ __forceinline__ __half from_f(float f) { return __float2half_rn(f); }
+  static __device__ __forceinline__ float lo(uint32_t w) { return __half2float(__ushort_as_half((unsigned short)(w & 0xFFFF))); }
+  static __device__ __forceinline__ float hi(uint32_t w) { return __half2float(__ushort_as_half((unsigned short)(w >> 16))); }
+  static __device__ __forceinline__ uint32_t pack(float a, float b) {
+    __half2 v = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+  }
+  static __device__ __forceinline__ float round(float f) { return __half2float(__float2half_rn(f)); }
+};
+
+// fp32 -> fp16 (RNE) -> clamp [-128,127] -> round-half-even -> int8   (golden: test_mla:81-83)
+__device__ __forceinline__ int sat_i8(float f) {
+  float h = __half2float(__float2half_rn(f));
+  h = fminf(fmaxf(h, -128.f), 127.f);
+  return __float2int_rn(h);
+}
+__device__ __forceinline__ uint32_t pack4_i8(int a, int b, int c, int d) {
+  return (uint32_t)(a & 0xFF) | ((uint32_t)(b & 0xFF) << 8) | ((uint32_t)(c & 0xFF) << 16) | ((uint32_t)(d & 0xFF) << 24);
+}
+template <class T>
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  f[0] = Act<T>::lo(v.x); f[1] = Act<T>::hi(v.x); f[2] = Act<T>::lo(v.y); f[3] = Act<T>::hi(v.y);
+  f[4] = Act<T>::lo(v.z); f[5] = Act<T>::hi(v.z); f[6] = Act<T>::lo(v.w); f[7] = Act<T>::hi(v.w);
+}
+__device__ __forceinline__ float load_descale(const void* p, int is_i64, int i) {
+  if (is_i64) return __int_as_float((int)(reinterpret_cast<const long long*>(p)[i] & 0xFFFFFFFFll));
+  return reinterpret_cast<const float*>(p)[i];
+}
+
+// Debug timeline (flag bit3): per-CTA clock64 marks, 16 slots per CTA, written only when the pointer is non-null.
+__device__ __forceinline__ void tl_mark(long long* tl, int slot) {
+  if (tl) {
+    const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+    tl[cta * 16 + slot] = clock64();
+  }
+}
+__device__ __forceinline__ void tl_mark_global(long long* tl, int slot) {
+  if (tl) {
+    const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    tl[cta * 16 + slot] = (long long)t;
+  }
+}
+
+
+}  // namespace mlapo

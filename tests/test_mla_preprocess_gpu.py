@@ -28,6 +28,10 @@ CASES = [
     (300, 8, 7168, "bf16", "int8_nzcache", PT, 0.1),
     (64, 4, 7168, "bf16", "krope_ctkv", TOK, 0.1),
     (33, 4, 6144, "fp16", "nzcache", TOK, 0.0),
+    # tile-boundary sizes and the ends of the reference's hiddenSize range [2048, 8192] (csrc/mla_preprocess/README.md:8)
+    (128, 3, 2048, "bf16", "krope_ctkv", PT, 0.0),
+    (257, 5, 8192, "bf16", "int8_nzcache", PT, 0.02),
+    (256, 1, 7168, "fp16", "nzcache", PT, 0.0),
     # prefill-sized: no split-K, 256-wide MM1 tiles, many token super-tiles (the reference stops at 1024 tokens)
     (2400, 2, 7168, "bf16", "krope_ctkv", PT, 0.05),
     # more (head, 256-token) units than SMs: the q path runs in its streaming form (persistent CTAs, overlapped units)
