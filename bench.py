@@ -104,11 +104,13 @@ def algorithmic_bytes(n, h, d, cache_mode):
 def kernel_algorithmic_bytes(name, n, h, d, cache_mode):
     """Per-kernel compulsory bytes (each kernel's own inputs + outputs), stated in DESIGN.md §4."""
     q0 = 1 if cache_mode == "int8_nzcache" else 2
+    qb = 1536 * 192 * h + 2 * 128 * 512 * h + n * 1536 + n * h * 64 * 2 + n * h * 512 * q0 + 8 * 192 * h + n * 256
     return {
         "quant_hidden": n * d * 2 + n * d,
         "mm1_splitk": 2112 * d + n * d + n * 2112 * 4,
         "norm_rope_cache": n * 2112 * 4 + n * 1536 + n * (512 * q0 + 128) + n * 260 + 8 * 2112 + 4 * 1536 + 1024,
-        "q_fused": 1536 * 192 * h + 2 * 128 * 512 * h + n * 1536 + n * h * 64 * 2 + n * h * 512 * q0 + 8 * 192 * h + n * 256,
+        "q_fused": qb,
+        "q_stream": qb,
     }.get(name, 0)
 
 
