@@ -251,8 +251,9 @@ def run_ours(args):
                                  w["quant_scale1"], w["quant_offset1"], w["bias1"], w["ctkv_scale"], w["q_nope_scale"],
                                  cache_mode, quant_mode, outs[i][0], outs[i][1])
 
-    if args.persistent:
-        cabi.set_debug_flags(32)
+    dbg = (32 if args.persistent else 0) | args.debug_flags
+    if dbg:
+        cabi.set_debug_flags(dbg)
     plist = [params_for(i) for i in range(n_sets)]
     lay = cabi.workspace_layout(plist[0])
     ws = torch.empty(lay.total_bytes, dtype=torch.uint8, device=dev)
@@ -350,7 +351,7 @@ def run_ours(args):
 
     # ---- per-kernel durations (separate eager pass, CUDA events recorded by the library around each kernel)
     import ctypes
-    cabi.set_debug_flags(4 | (32 if args.persistent else 0))
+    cabi.set_debug_flags(4 | dbg)
     ksum, kcount = None, 0
     for i in range(40):
         step(i)
@@ -360,7 +361,7 @@ def run_ours(args):
             vals = [buf[j] for j in range(cnt)]
             ksum = vals if ksum is None else [a + b for a, b in zip(ksum, vals)]
             kcount += 1
-    cabi.set_debug_flags(32 if args.persistent else 0)
+    cabi.set_debug_flags(dbg)
     cabi.lib.mlapo_kernel_name.restype = ctypes.c_char_p
     kernels = {}
     if ksum:
@@ -497,6 +498,7 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph of one weight rotation")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--debug-flags", type=int, default=0, help="A/B: extra mlapo_set_debug_flags bits (64/128 older q kernels, 4096 no L2 weight prefetch)")
     ap.add_argument("--persistent", action="store_true",
                     help="A/B: run eligible calls (<= 256 tokens) as the opt-in single persistent cooperative kernel")
     args = ap.parse_args()

@@ -36,6 +36,7 @@
 #include "mlapo_quant_norm.cuh"
 #include "mlapo_mm1.cuh"
 #include "mlapo_q.cuh"
+#include "mlapo_q_pair.cuh"
 #include "mlapo_decode_persistent.cuh"
 
 namespace mlapo {
@@ -321,22 +322,34 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   }
   g_kernel_names[0] = "quant_hidden";
 
-  // ---- k1: quantise hiddenState
+  // ---- k1: quantise hiddenState (bit12 of the debug flags: also ask for the call's weights in L2 — measured slower, see profiles/README.md)
+  WeightPrefetch wp{};
+  if (g_debug_flags & 4096) {
+    wp.ptr[0] = reinterpret_cast<const char*>(p->wdqkv_km); wp.lines[0] = (long long)MLAPO_MM1_OUT * d / 128;
+    wp.ptr[1] = reinterpret_cast<const char*>(p->wuq_km);   wp.lines[1] = (long long)h * MLAPO_Q_HEAD * MLAPO_Q_LORA / 128;
+    wp.ptr[2] = reinterpret_cast<const char*>(p->wuk);      wp.lines[2] = (long long)h * MLAPO_Q_NOPE * MLAPO_KV_LORA * 2 / 128;
+  }
   record_event(0, st);
   if (per_token) {
     e__ = launch_k(quant_hidden_per_token_kernel<T>, dim3(n), dim3(256), 0, st, pdl, reinterpret_cast<const T*>(p->hidden_state), a0,
-                   tok_scale, d);
+                   tok_scale, d, wp);
   } else {
     const long long nvec = (long long)n * d / 8;
-    const long long one_wave = (long long)num_sms() * 8 * 256;  // threads of one full wave (8 blocks of 256 per SM)
-    if (nvec <= one_wave) {  // one 16-byte vector per thread
+    // The whole grid must be resident at once, otherwise its last blocks start late and the programmatic launch of MM1
+    // (which wants to fetch weights meanwhile) waits for them: 4 blocks of 256 threads per SM is always resident.
+    const long long wave = (long long)num_sms() * 4 * 256;
+    if (nvec <= wave) {  // one 16-byte vector per thread
       e__ = launch_k(quant_hidden_kernel<T, 1>, dim3((unsigned)((nvec + 255) / 256)), dim3(256), 0, st, pdl,
                      reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
-                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, tl0);
+                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0);
+    } else if (nvec <= 2 * wave) {  // two vectors per thread, both loads in flight
+      e__ = launch_k(quant_hidden_kernel<T, 2>, dim3((unsigned)((nvec + 511) / 512)), dim3(256), 0, st, pdl,
+                     reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
+                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0);
     } else {                 // prefill sizes: grid-stride, 4 independent loads in flight per thread
       e__ = launch_k(quant_hidden_kernel<T, 4>, dim3(num_sms() * 8), dim3(256), 0, st, pdl,
                      reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
-                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, tl0);
+                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0);
     }
   }
   MLAPO_CHECK_LAUNCH("quant_hidden");
@@ -374,7 +387,30 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   // ---- k4 / k6: fused MM2 + dequant + RoPE + W_UK absorb.  One CTA per (head, token super-tile) while those fit one wave;
   //      beyond that, persistent CTAs stream the units so that consecutive units overlap.
   const int q_units = h * ((n + 255) / 256);
-  if (n > 256 && q_units > num_sms() && !(g_debug_flags & 64)) {  // bit6: keep k4 for A/B comparisons
+  // k7 wins where a pair has many units to stream (C3: 494 vs 558 us for the q path); with one or two units per pair (decode)
+  // its longer dependency chain loses to k4 (C2: 33 vs 27 us), so it takes over k6's range only.  bit13 forces it for n > 128.
+  const bool many_units = n > 256 && q_units > num_sms();
+  if (((many_units && !(g_debug_flags & 128)) || ((g_debug_flags & 8192) && n > kBlockM))) {  // bit7: keep k6 for A/B comparisons
+    // ---- k7: CTA pairs.  Each CTA of a pair owns one 128-token tile and half of the head's weight rows.
+    int rcx;
+    CUtensorMap tm_a1p, tm_wuqp;
+    if ((rcx = make_tmap(&tm_a1p, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a1, n, MLAPO_Q_LORA, MLAPO_Q_LORA, kBlockM, 128))) return rcx;
+    if ((rcx = make_tmap(&tm_wuqp, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wuq_km, (uint64_t)h * MLAPO_Q_HEAD, MLAPO_Q_LORA, MLAPO_Q_LORA,
+                         kPHalfB, 128))) return rcx;
+    const int max_pairs = num_sms() / 2;
+    dim3 grid(2 * (q_units < max_pairs ? q_units : max_pairs));
+    if (int8_out) {
+      static bool done[64] = {};
+      if ((rc = set_smem_attr(q_pair_kernel<T, true>, kPSmemBytes, &done[dev], "q_pair<int8>"))) return rc;
+      e__ = launch_k(q_pair_kernel<T, true>, grid, dim3(kPThreads), kPSmemBytes, st, pdl, tm_a1p, tm_wuqp, tm_wuk, tm_o0, qa, p->q_out1, q_units, tl4);
+    } else {
+      static bool done[64] = {};
+      if ((rc = set_smem_attr(q_pair_kernel<T, false>, kPSmemBytes, &done[dev], "q_pair"))) return rc;
+      e__ = launch_k(q_pair_kernel<T, false>, grid, dim3(kPThreads), kPSmemBytes, st, pdl, tm_a1p, tm_wuqp, tm_wuk, tm_o0, qa, p->q_out1, q_units, tl4);
+    }
+    MLAPO_CHECK_LAUNCH("q_pair");
+    g_kernel_names[3] = "q_pair";
+  } else if (n > 256 && q_units > num_sms() && !(g_debug_flags & 64)) {  // bit6: keep k4 for A/B comparisons
     int rcx;
     CUtensorMap tm_a1s;  // the streaming kernel always fetches both token tiles of a unit in one box
     if ((rcx = make_tmap(&tm_a1s, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a1, n, MLAPO_Q_LORA, MLAPO_Q_LORA, 2 * kBlockM, 128))) return rcx;

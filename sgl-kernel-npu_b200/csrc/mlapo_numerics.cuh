@@ -64,6 +64,10 @@ __device__ __forceinline__ void tl_mark(long long* tl, int slot) {
     tl[cta * 16 + slot] = clock64();
   }
 }
+// Fine-grained trace of ONE thread of CTA 0 (rows 1024.. of the kernel's timeline table): entry idx <- clock64
+__device__ __forceinline__ void tl_trace(long long* tl, bool who, int idx) {
+  if (tl && who && blockIdx.x == 0 && idx < 2048) tl[1024 * 16 + idx] = clock64();
+}
 __device__ __forceinline__ void tl_mark_global(long long* tl, int slot) {
   if (tl) {
     const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);

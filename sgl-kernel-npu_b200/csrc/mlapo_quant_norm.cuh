@@ -76,11 +76,26 @@ __device__ __forceinline__ void quant_vectors(const T* __restrict__ x, int8_t* _
   }
 }
 
+// The call's three weight tensors (70 MB at 128 heads) fit the 126 MB L2.  The first kernel of the call asks for all of them
+// before it waits for its predecessor, so HBM streams weights while quant / MM1 / norm — which move little data — run,
+// and the weight loads of MM1 and of the q path find L2 lines (or fills already in flight) instead of starting at DRAM.
+struct WeightPrefetch {
+  const char* ptr[3];      // W_DQKV, W_UQ, W_UK in the order the call consumes them
+  long long lines[3];      // 128-byte lines each
+};
+__device__ __forceinline__ void prefetch_weights_l2(const WeightPrefetch& wp) {
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+    for (long long i = tid; i < wp.lines[r]; i += nth) asm volatile("prefetch.global.L2 [%0];" ::"l"(wp.ptr[r] + i * 128));
+}
+
 template <class T, int U>
 __global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict__ q, const T* __restrict__ scale,
-                                    const int8_t* __restrict__ offset, long long n_vec8, long long* tl) {
+                                    const int8_t* __restrict__ offset, long long n_vec8, WeightPrefetch wp, long long* tl) {
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 0);
   ptx::griddep_launch_dependents();
+  prefetch_weights_l2(wp);
   QuantScale qs;
   qs.load(scale, offset);
   ptx::griddep_wait();  // a0 may still be read by the previous call's MM1 until its successors have completed
@@ -123,8 +138,9 @@ __device__ __forceinline__ void quant_row_per_token(const T* __restrict__ x, int
 
 template <class T>
 __global__ void __launch_bounds__(256) quant_hidden_per_token_kernel(const T* __restrict__ x, int8_t* __restrict__ q,
-                                                                      float* __restrict__ tok_scale, int d) {
+                                                                      float* __restrict__ tok_scale, int d, WeightPrefetch wp) {
   ptx::griddep_launch_dependents();
+  prefetch_weights_l2(wp);
   ptx::griddep_wait();
   quant_row_per_token<T>(x, q, tok_scale, d, blockIdx.x);
 }

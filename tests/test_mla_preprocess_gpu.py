@@ -58,18 +58,29 @@ def check(res, case, quant_mode, q0_close):
         assert res["q_out0"][0] <= 2e-3 * res["q_out0"][1], res["q_out0"]  # and almost always bit-identical
 
 
-@pytest.mark.parametrize("persistent", [False, True], ids=["chained", "persistent"])
+VARIANTS = {"chained": (False, 0), "persistent": (True, 0), "single_cta_q": (False, 128), "pair_q": (False, 8192)}
+
+
+@pytest.mark.parametrize("variant", list(VARIANTS))
 @pytest.mark.parametrize("cfg", CASES, ids=[f"N{c[0]}-H{c[1]}-D{c[2]}-{c[3]}-{c[4]}-{c[5][:9]}" for c in CASES])
-def test_parity_vs_oracle(cfg, persistent, cuda_device):
-    """`chained` = the default launch shape (four PDL-chained kernels); `persistent` = the opt-in single cooperative kernel
-    for calls of <= 256 tokens.  Both meet the same bars."""
+def test_parity_vs_oracle(cfg, variant, cuda_device):
+    """`chained` = the default launch shape (four PDL-chained kernels; the q path is the per-head kernel, or the CTA-pair
+    kernel when there are more (head, 256-token) units than SMs); `persistent` = the opt-in single cooperative kernel for
+    calls of <= 256 tokens; `single_cta_q` = the streaming q kernel the pair kernel replaced; `pair_q` = the pair kernel
+    forced on every call of more than 128 tokens.  All meet the same bars."""
     n, h, d, dt, mode, qm, neg = cfg
+    persistent, extra = VARIANTS[variant]
     if persistent and n > 256:
         pytest.skip("the persistent decode kernel covers <= 256 tokens")
+    many_units = n > 256 and h * ((n + 255) // 256) > torch.cuda.get_device_properties(cuda_device).multi_processor_count
+    if variant == "single_cta_q" and not many_units:
+        pytest.skip("same kernels as `chained` for this shape")
+    if variant == "pair_q" and (n <= 128 or many_units):
+        pytest.skip("same kernels as `chained` for this shape")
     case = orc.gen_case(N=n, H=h, D=d, dtype=DT[dt], cache_mode=mode, seed=42, num_blocks=max(12, n // 64), neg_slot_frac=neg)
     case.t["kv_cache"].fill_(5)
     case.t["kv_cache_rope"].fill_(5)
-    g, taps = hz.run_cuda(case, cuda_device, quant_mode=qm, persistent=persistent)
+    g, taps = hz.run_cuda(case, cuda_device, quant_mode=qm, persistent=persistent, extra_flags=extra)
     res, ocase, _ = hz.compare(case, qm, g, taps)
     q0_close = mode == "int8_nzcache" or torch.allclose(g["q_out0"].cpu().float(), ocase.t["q_out0"].float(), rtol=1e-2, atol=1e-3)
     check(res, case, qm, q0_close)

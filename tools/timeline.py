@@ -16,7 +16,7 @@ QF = ["gtimer", "start", "prologue", "upstream", "first_full", "last_full", "mm2
       "stores_read", "end"]
 
 
-def main(workload="c2", pdl=False, persistent=False):
+def main(workload="c2", pdl=False, persistent=False, legacy=False):
     n, h, d, cache_mode, _ = bench.WORKLOADS[workload]
     dev = torch.device("cuda:0")
     gen = torch.Generator(device=dev).manual_seed(1)
@@ -26,7 +26,7 @@ def main(workload="c2", pdl=False, persistent=False):
     kv, kvr = bench.cache_tensors(torch, cache_mode, 64, dev)
     q0 = torch.zeros((n, h, 512), dtype=torch.int8 if cache_mode == "int8_nzcache" else torch.bfloat16, device=dev)
     q1 = torch.zeros((n, h, 64), dtype=torch.bfloat16, device=dev)
-    cabi.set_debug_flags(8 | (0 if pdl else 1) | (32 if persistent else 0))
+    cabi.set_debug_flags(8 | (0 if pdl else 1) | (32 if persistent else 0) | (128 if legacy else 0))
     ps = []
     for w in sets:
         ps.append(cabi.build_params(hid, w["wdqkv_km"], w["descale0"], w["gamma1"], w["beta1"], w["wuq_km"], w["descale1"], w["gamma2"],
@@ -63,8 +63,12 @@ def main(workload="c2", pdl=False, persistent=False):
             extra = f"  upstream-wait passed by {(w - t0) / 1e3:7.2f}" if w else ""
             print(f"   {name:16s} {(a0 - t0) / 1e3:7.2f} {(am - t0) / 1e3:7.2f} {(a1 - t0) / 1e3:7.2f}{extra}")
     QS = ["gtimer", "start"] + [f"u{i}:{w}" for i in range(4) for w in ("mm2_done", "acc2_released", "drained")]
+    QP = ["gtimer", "start", "prologue", "upstream", "first_full"] + [f"u{i}:{w}" for i in range(3) for w in ("mm2_done", "acc_read", "drained")] + ["end"]
     stream = n > 256 and h * ((n + 255) // 256) > 148
-    for k, (name, labels) in enumerate([("mm1_splitk", MM1), ("q_stream" if stream else "q_fused", QS if stream else QF)]):
+    qname, qlabels = ("q_stream", QS) if stream else ("q_fused", QF)
+    if stream and not legacy:
+        qname, qlabels = "q_pair", QP
+    for k, (name, labels) in enumerate([("mm1_splitk", MM1), (qname, qlabels)]):
         a = tl[k]
         used = a[:, 1] != 0
         a = a[used]
@@ -80,5 +84,5 @@ def main(workload="c2", pdl=False, persistent=False):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1] if len(sys.argv) > 1 else "c2", pdl=len(sys.argv) > 2 and sys.argv[2] in ("pdl", "persistent"),
-         persistent=len(sys.argv) > 2 and sys.argv[2] == "persistent")
+    main(sys.argv[1] if len(sys.argv) > 1 else "c2", pdl=len(sys.argv) > 2 and ("pdl" in sys.argv[2:] or "persistent" in sys.argv[2:]),
+         persistent=len(sys.argv) > 2 and sys.argv[2] == "persistent", legacy="legacy" in sys.argv[2:])
