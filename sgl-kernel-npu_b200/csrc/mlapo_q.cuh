@@ -451,6 +451,11 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
   c.tmem = *tmem_slot;
   ptx::griddep_launch_dependents();
   if (threadIdx.x == 0) tl_mark(tl, 2);  // prologue done
+  if (threadIdx.x == 0 && tl) {  // which SM ran this CTA (timeline analysis only)
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    tl[(blockIdx.x + gridDim.x * blockIdx.y) * 16 + 13] = smid;
+  }
 
   q_roles<T, kInt8Out, true>(c, &tm_a1, &tm_wuq, &tm_wuk, &tm_out0, &tm_out1, qa, warp, lane, tl);
 

@@ -99,6 +99,7 @@ __global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict_
   QuantScale qs;
   qs.load(scale, offset);
   ptx::griddep_wait();  // a0 may still be read by the previous call's MM1 until its successors have completed
+  if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 14);
   quant_vectors<T, U>(x, q, qs, n_vec8, blockIdx.x * (long long)blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 15);
 }

@@ -46,8 +46,13 @@ def main(workload="c2", pdl=False, persistent=False, legacy=False):
                 for i in range(6):
                     cabi.launch(ps[i % 3], ws, gs.cuda_stream)
             gr.replay()
-            gr.replay()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(gs)
+            for _ in range(20):
+                gr.replay()
+            e1.record(gs)
         torch.cuda.synchronize()
+        print(f"period with the timeline marks on: {e0.elapsed_time(e1) * 1e3 / 120:.2f} us per call")
     tl = ws[lay.timeline:lay.timeline + 4 * 4096 * 16 * 8].view(torch.int64).reshape(4, 4096, 16).cpu().numpy()
     # whole-call picture from the global timer: [kernel] first CTA start .. last CTA end, relative to the quant kernel's start
     spans = {}
@@ -55,12 +60,12 @@ def main(workload="c2", pdl=False, persistent=False, legacy=False):
         a = tl[k]
         a = a[a[:, 0] != 0]
         if a.shape[0]:
-            spans[name] = (a[:, 0].min(), np.median(a[:, 0]), a[:, 15].max(), a[:, 14].max() if k == 3 else 0)
+            spans[name] = (a[:, 0].min(), np.median(a[:, 0]), a[:, 15].max(), a[:, 14].max() if k in (2, 3) else 0, np.median(a[:, 14]) if k in (2, 3) else 0, np.median(a[:, 15]))
     if spans:
         t0 = spans["quant_hidden"][0] if "quant_hidden" in spans else min(v[0] for v in spans.values())
         print("call timeline (us from quant start): kernel first-CTA-start / median-CTA-start / last-CTA-end")
-        for name, (a0, am, a1, w) in spans.items():
-            extra = f"  upstream-wait passed by {(w - t0) / 1e3:7.2f}" if w else ""
+        for name, (a0, am, a1, w, wm, em) in spans.items():
+            extra = f"  upstream-wait passed: median {(wm - t0) / 1e3:7.2f} last {(w - t0) / 1e3:7.2f}; median CTA end {(em - t0) / 1e3:7.2f}" if w else ""
             print(f"   {name:16s} {(a0 - t0) / 1e3:7.2f} {(am - t0) / 1e3:7.2f} {(a1 - t0) / 1e3:7.2f}{extra}")
     QS = ["gtimer", "start"] + [f"u{i}:{w}" for i in range(4) for w in ("mm2_done", "acc2_released", "drained")]
     QP = ["gtimer", "start", "prologue", "upstream", "first_full"] + [f"u{i}:{w}" for i in range(3) for w in ("mm2_done", "acc_read", "drained")] + ["end"]
@@ -78,6 +83,21 @@ def main(workload="c2", pdl=False, persistent=False, legacy=False):
             dlt = dlt[a[:, j] != 0]
             if dlt.size:
                 print(f"   {labels[j]:14s} {np.median(dlt):9.0f} {np.percentile(dlt, 10):9.0f} {np.percentile(dlt, 90):9.0f} {dlt.max():9.0f}")
+        if name == "q_fused" and a[:, 13].max() > 0:
+            order = np.argsort(a[:, 13])
+            print("   per SM (smid: last_full, end since CTA start, CTA start offset ns):")
+            slow = [i for i in order if a[i, 5] - a[i, 1] > 1.15 * np.median(a[:, 5] - a[:, 1])]
+            print("   slow CTAs (smid:cta:last_full): " + " ".join(f"{int(a[i, 13])}:{i}:{int(a[i, 5] - a[i, 1])}" for i in slow))
+            absf = (a[:, 0] - a[:, 0].min()) * 1.965 + (a[:, 5] - a[:, 1])
+            print("   last_full by CTA id (k-cycles since the first CTA start): " + " ".join(f"{v / 1e3:.0f}" for v in absf))
+            abse = (a[:, 0] - a[:, 0].min()) * 1.965 + (a[:, 12] - a[:, 1])
+            print("   end by CTA id: " + " ".join(f"{v / 1e3:.0f}" for v in abse))
+            print("   idle SMs: " + " ".join(str(x) for x in sorted(set(range(148)) - set(int(v) for v in a[:, 13]))))
+        if a[:, 15].max() > 0:
+            e = (a[:, 15] - a[:, 0].min()) / 1e3
+            st = (a[:, 0] - a[:, 0].min()) / 1e3
+            print(f"   absolute (us since the kernel's first CTA start): CTA start p10/p50/p90/max {np.percentile(st, 10):.2f} {np.median(st):.2f} {np.percentile(st, 90):.2f} {st.max():.2f};"
+                  f" CTA end p10/p50/p90/max {np.percentile(e, 10):.2f} {np.median(e):.2f} {np.percentile(e, 90):.2f} {e.max():.2f}")
         g = a[:, 0]
         print(f"   CTA start skew (globaltimer ns): p50-min {np.median(g) - g.min():.0f}  max-min {g.max() - g.min():.0f}")
     cabi.set_debug_flags(0)
