@@ -26,7 +26,7 @@ def main(workload="c2", pdl=False, persistent=False, legacy=False):
     kv, kvr = bench.cache_tensors(torch, cache_mode, 64, dev)
     q0 = torch.zeros((n, h, 512), dtype=torch.int8 if cache_mode == "int8_nzcache" else torch.bfloat16, device=dev)
     q1 = torch.zeros((n, h, 64), dtype=torch.bfloat16, device=dev)
-    cabi.set_debug_flags(8 | (0 if pdl else 1) | (32 if persistent else 0) | (128 if legacy else 0))
+    cabi.set_debug_flags(8 | (0 if pdl else 1) | (32 if persistent else 0) | (128 if legacy else 0) | int(os.environ.get("MLAPO_EXTRA_FLAGS", "0")))
     ps = []
     for w in sets:
         ps.append(cabi.build_params(hid, w["wdqkv_km"], w["descale0"], w["gamma1"], w["beta1"], w["wuq_km"], w["descale1"], w["gamma2"],
