@@ -133,6 +133,33 @@ int mlapo_get_workspace_layout(const MlapoParams* p, MlapoWorkspaceLayout* layou
 int mlapo_repack_nz_weight(const void* w_nz, void* w_km, int32_t k, int32_t n_out, void* stream);
 
 /*
+ * batch_matmul_transpose: C[m, batch, n] = sum_k A[m, batch, k] * B[batch, k, n], the W_UV half of MLA weight
+ * absorption.  Replaces sglang::npu_kernel::batch_matmul_transpose (csrc/batch_matmul_transpose/op_host/batch_matmul_transpose.cpp:46-114,
+ * declared include/sgl_kenel_npu_ops.h:121-124, schema csrc/pytorch_extensions.cpp:117-119).  a [m, batch, k], c [m, batch, n],
+ * b ND [batch, k, n] or NZ [batch, n/16, k, 16] (k, n multiples of 16); act_dtype MLAPO_ACT_*; fp32 accumulation, one rounding.
+ * No limit on m (the reference stops at 1024).  ND weights with k % 64 == 0 and n % 64 == 0 run on the tensor cores.
+ */
+#define MLAPO_FORMAT_ND 0
+#define MLAPO_FORMAT_NZ 1
+int batch_matmul_transpose_launch(const void* a, const void* b, void* c, int64_t m, int64_t batch, int64_t k, int64_t n,
+                                  int32_t act_dtype, int32_t b_format, void* stream);
+
+/*
+ * Format tools.  The reference has them only as test helpers; they are exported so that Ascend-format
+ * checkpoints and caches can be prepared and read on the device.  All asynchronous on `stream`, device pointers.
+ *  - mlapo_transdata_nd_to_nz: ND [rows, cols] -> FRACTAL_NZ [1, ceil(cols/c0), ceil16(rows), c0], zero padded; int8 weights
+ *    use c0 = 32, 16-bit tensors c0 = 16.  Replaces transdata() (tests/python/sgl_kernel_npu/test_mla_preprocess.py:38-54).
+ *  - mlapo_pack_descale_int64: fp32 descale -> the int64 carrier of the fp16 path, (bits & 0xFFFFE000) | 1 << 46.
+ *    Replaces trans_descale_param() (test_mla_preprocess.py:110-119).
+ *  - mlapo_gather_nz_cache_rows: rows named by `slots` out of a paged NZ cache [blocks, width/c0, 128, c0] -> dense [n, width]
+ *    (slot -1 or out of range -> zeros).  Replaces extract_from_nzcache() (test_mla_preprocess.py:122-135).
+ */
+int mlapo_transdata_nd_to_nz(const void* nd, void* nz, int64_t rows, int64_t cols, int32_t c0, int32_t elem_bytes, void* stream);
+int mlapo_pack_descale_int64(const void* descale_f32, void* descale_i64, int64_t n, void* stream);
+int mlapo_gather_nz_cache_rows(const void* cache, const int32_t* slots, void* rows_out, int64_t n, int32_t width, int32_t c0,
+                               int32_t elem_bytes, int64_t num_blocks, void* stream);
+
+/*
  * The operator.  Enqueues the whole prologue on `stream`:
  *   quant -> W_DQKV int8 GEMM -> dequant -> { q_a RMSNorm+quant -> W_UQ int8 GEMM -> dequant -> RoPE | W_UK absorb }
  *                                        -> { latent RMSNorm(512), RoPE(64) -> paged-cache scatter by slot_mapping }.

@@ -116,5 +116,36 @@ def main():
         print("wrote", name, {k: v.shape for k, v in rec.items() if hasattr(v, "shape") and v.ndim > 0})
 
 
+def format_fixtures(ref):
+    """Known answers of the reference's own format helpers (test_mla:38-54, 110-135) on small seeded inputs."""
+    g = torch.Generator().manual_seed(7)
+    rec = {}
+    # aligned shapes only: the reference helper hands F.pad its row/column paddings in swapped order (test_mla:42-43),
+    # so it fails on ragged inputs; padding is checked against oracle.nz_pack instead
+    w8 = torch.randint(-128, 128, (64, 128), dtype=torch.int8, generator=g)
+    rec["td_i8_in"] = w8.numpy()
+    rec["td_i8_out"] = ref.transdata(w8, (16, 32)).numpy()
+    w16 = torch.randint(-2 ** 15, 2 ** 15, (32, 48), dtype=torch.int16, generator=g)  # 16-bit payload, block (16, 16)
+    rec["td_16_in"] = w16.numpy()
+    rec["td_16_out"] = ref.transdata(w16, (16, 16)).numpy()
+    d = (torch.rand(257, generator=g) / 1000).numpy().astype(np.float32)
+    rec["descale_in"] = d.copy()
+    rec["descale_out"] = ref.trans_descale_param(d.copy()).numpy()
+    cache = torch.randint(-2 ** 15, 2 ** 15, (3, 64 // 16, 128, 16), dtype=torch.int16, generator=g)  # rope-cache geometry
+    slots = np.array([0, 1, 127, 128, 200, 383], dtype=np.int32)
+    rows = [ref.extract_from_nzcache(cache.view(3, -1, 1, 64), int(s) // 128, int(s) % 128)[0].numpy() for s in slots]
+    rec["nz_cache"] = cache.numpy()
+    rec["nz_slots"] = slots
+    rec["nz_rows"] = np.stack(rows)
+    cache8 = torch.randint(-128, 128, (2, 64 // 32, 128, 32), dtype=torch.int8, generator=g)
+    rows8 = [ref.extract_from_nzcache(cache8.view(2, -1, 1, 64), int(s) // 128, int(s) % 128, 32)[0].numpy() for s in slots[:5]]
+    rec["nz_cache8"] = cache8.numpy()
+    rec["nz_rows8"] = np.stack(rows8)
+    np.savez_compressed(os.path.join(OUT_DIR, "format_tools.npz"), **rec)
+    print("wrote format_tools.npz")
+
+
 if __name__ == "__main__":
-    main()
+    if "--formats-only" not in sys.argv:
+        main()
+    format_fixtures(load_reference_test())

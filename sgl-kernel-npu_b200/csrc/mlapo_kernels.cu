@@ -38,6 +38,8 @@
 #include "mlapo_q.cuh"
 #include "mlapo_q_pair.cuh"
 #include "mlapo_decode_persistent.cuh"
+#include "mlapo_format.cuh"
+#include "mlapo_bmt.cuh"
 
 namespace mlapo {
 
@@ -444,6 +446,43 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   return MLAPO_OK;
 }
 
+template <class T>
+static int bmt_launch_impl(const void* a, const void* b, void* c, int64_t m, int64_t batch, int64_t k, int64_t n, int b_is_nz,
+                           cudaStream_t st) {
+  const CUtensorMapDataType dt = std::is_same<T, __nv_bfloat16>::value ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  cudaError_t e;
+  const bool tc = !b_is_nz && k % 64 == 0 && n % 64 == 0 && m < (1ll << 31) && batch <= 65535 &&
+                  ((uintptr_t)a % 16 == 0) && ((uintptr_t)b % 16 == 0) && ((uintptr_t)c % 16 == 0);
+  if (tc) {
+    int rc, dev = 0;
+    cudaGetDevice(&dev);
+    dev &= 63;
+    CUtensorMap tm_a, tm_b, tm_c;  // coordinates (inner, rows, batch); the op's "transposes" are just these stride orders
+    if ((rc = make_tmap(&tm_a, dt, 2, a, (uint64_t)m, (uint64_t)k, (uint64_t)batch * k * 2, kBlockM, 64, (uint64_t)batch, (uint64_t)k * 2))) return rc;
+    if ((rc = make_tmap(&tm_b, dt, 2, b, (uint64_t)k, (uint64_t)n, (uint64_t)n * 2, 64, 64, (uint64_t)batch, (uint64_t)k * n * 2))) return rc;
+    if ((rc = make_tmap(&tm_c, dt, 2, c, (uint64_t)m, (uint64_t)n, (uint64_t)batch * n * 2, kBlockM, 64, (uint64_t)batch, (uint64_t)n * 2))) return rc;
+    const unsigned m_tiles = (unsigned)((m + 2 * kBlockM - 1) / (2 * kBlockM));
+    if (n % 128 == 0) {
+      static bool done[64] = {};
+      if ((rc = set_smem_attr(bmt_tc_kernel<T, 128>, bmt_smem_bytes<128>(), &done[dev], "bmt<128>"))) return rc;
+      e = launch_k(bmt_tc_kernel<T, 128>, dim3((unsigned)(n / 128), m_tiles, (unsigned)batch), dim3(kBmtThreads), bmt_smem_bytes<128>(), st, false,
+                   tm_a, tm_b, tm_c, (int)m, (int)k);
+    } else {
+      static bool done[64] = {};
+      if ((rc = set_smem_attr(bmt_tc_kernel<T, 64>, bmt_smem_bytes<64>(), &done[dev], "bmt<64>"))) return rc;
+      e = launch_k(bmt_tc_kernel<T, 64>, dim3((unsigned)(n / 64), m_tiles, (unsigned)batch), dim3(kBmtThreads), bmt_smem_bytes<64>(), st, false,
+                   tm_a, tm_b, tm_c, (int)m, (int)k);
+    }
+  } else {
+    long long blocks = (m * batch * n + 255) / 256;
+    if (blocks > 148 * 64) blocks = 148 * 64;
+    bmt_generic_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(reinterpret_cast<const T*>(a), reinterpret_cast<const T*>(b), reinterpret_cast<T*>(c),
+                                                           m, batch, k, n, b_is_nz);
+    e = cudaGetLastError();
+  }
+  return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "batch_matmul_transpose launch: %s", cudaGetErrorString(e));
+}
+
 }  // namespace mlapo
 
 // ============================================================================================ C ABI
@@ -510,6 +549,56 @@ int mlapo_get_workspace_size(const MlapoParams* p, size_t* bytes) {
 int mlapo_launches_per_call(const MlapoParams* p) {
   if (check_params(p)) return 0;
   return decode_persistent_eligible(p, choose_splits0(p->num_tokens, p->hidden_dim)) ? 1 : 4;
+}
+
+int batch_matmul_transpose_launch(const void* a, const void* b, void* c, int64_t m, int64_t batch, int64_t k, int64_t n,
+                                  int32_t act_dtype, int32_t b_format, void* stream) {
+  if (!a || !b || !c) return fail(MLAPO_ERR_INVALID_ARG, "batch_matmul_transpose: null pointer");
+  if (m <= 0 || batch <= 0 || k <= 0 || n <= 0) return fail(MLAPO_ERR_INVALID_ARG, "batch_matmul_transpose: m=%lld batch=%lld k=%lld n=%lld",
+                                                          (long long)m, (long long)batch, (long long)k, (long long)n);
+  if (b_format != MLAPO_FORMAT_ND && b_format != MLAPO_FORMAT_NZ) return fail(MLAPO_ERR_INVALID_ARG, "batch_matmul_transpose: format %d", b_format);
+  if (b_format == MLAPO_FORMAT_NZ && (k % 16 || n % 16))
+    return fail(MLAPO_ERR_INVALID_ARG, "batch_matmul_transpose: NZ weights need k and n to be multiples of 16 (k=%lld n=%lld)", (long long)k, (long long)n);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (act_dtype == MLAPO_ACT_BF16) return bmt_launch_impl<__nv_bfloat16>(a, b, c, m, batch, k, n, b_format == MLAPO_FORMAT_NZ, st);
+  if (act_dtype == MLAPO_ACT_FP16) return bmt_launch_impl<__half>(a, b, c, m, batch, k, n, b_format == MLAPO_FORMAT_NZ, st);
+  return fail(MLAPO_ERR_INVALID_ARG, "batch_matmul_transpose: tensors must be fp16 or bf16");
+}
+
+static unsigned grid_for(long long work) {
+  long long b = (work + 255) / 256;
+  return (unsigned)(b < 1 ? 1 : b > 65535 ? 65535 : b);
+}
+
+int mlapo_transdata_nd_to_nz(const void* nd, void* nz, int64_t rows, int64_t cols, int32_t c0, int32_t elem_bytes, void* stream) {
+  if (!nd || !nz) return fail(MLAPO_ERR_INVALID_ARG, "transdata: null pointer");
+  if (rows <= 0 || cols <= 0 || c0 <= 0 || (elem_bytes != 1 && elem_bytes != 2 && elem_bytes != 4))
+    return fail(MLAPO_ERR_INVALID_ARG, "transdata: rows=%lld cols=%lld c0=%d elem_bytes=%d", (long long)rows, (long long)cols, c0, elem_bytes);
+  const long long rp = (rows + 15) / 16 * 16, cp = (cols + c0 - 1) / c0 * c0;
+  transdata_nd_to_nz_kernel<<<grid_for(rp * cp), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const uint8_t*>(nd), reinterpret_cast<uint8_t*>(nz), rows, cols, rp, cp, c0, elem_bytes);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "transdata launch: %s", cudaGetErrorString(e));
+}
+
+int mlapo_pack_descale_int64(const void* descale_f32, void* descale_i64, int64_t n, void* stream) {
+  if (!descale_f32 || !descale_i64 || n <= 0) return fail(MLAPO_ERR_INVALID_ARG, "pack_descale: bad argument");
+  pack_descale_kernel<<<grid_for(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<const uint32_t*>(descale_f32),
+                                                                                 reinterpret_cast<unsigned long long*>(descale_i64), n);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "pack_descale launch: %s", cudaGetErrorString(e));
+}
+
+int mlapo_gather_nz_cache_rows(const void* cache, const int32_t* slots, void* rows_out, int64_t n, int32_t width, int32_t c0,
+                               int32_t elem_bytes, int64_t num_blocks, void* stream) {
+  if (!cache || !slots || !rows_out) return fail(MLAPO_ERR_INVALID_ARG, "gather_nz_cache_rows: null pointer");
+  if (n <= 0 || width <= 0 || c0 <= 0 || width % c0 || (elem_bytes != 1 && elem_bytes != 2) || num_blocks <= 0)
+    return fail(MLAPO_ERR_INVALID_ARG, "gather_nz_cache_rows: n=%lld width=%d c0=%d elem_bytes=%d blocks=%lld", (long long)n, width, c0,
+                elem_bytes, (long long)num_blocks);
+  gather_nz_rows_kernel<<<grid_for(n * width), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const uint8_t*>(cache), slots, reinterpret_cast<uint8_t*>(rows_out), n, width, c0, elem_bytes, num_blocks);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "gather_nz_cache_rows launch: %s", cudaGetErrorString(e));
 }
 
 int mlapo_repack_nz_weight(const void* w_nz, void* w_km, int32_t k, int32_t n_out, void* stream) {

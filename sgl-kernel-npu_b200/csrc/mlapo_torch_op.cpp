@@ -238,6 +238,39 @@ at::Tensor mla_preprocess_repack_weight(const at::Tensor& w_nz) {
   return repack_nz(w_nz, at::cuda::getCurrentCUDAStream());
 }
 
+// csrc/batch_matmul_transpose/op_host/batch_matmul_transpose.cpp:46-114 (same signature as include/sgl_kenel_npu_ops.h:121-124):
+// tensor_c[m, batch, :] = tensor_a[m, batch, :] . tensor_b[batch]; the mode strings and their defaults are the reference's
+// (:16-25, 65-67); quant_mode is validated and, as in the reference's fp16/bf16 kernel, does not change the arithmetic.
+void batch_matmul_transpose(const at::Tensor& tensor_a, const at::Tensor& tensor_b, at::Tensor& tensor_c,
+                            c10::optional<c10::string_view> format_mode, c10::optional<c10::string_view> quant_mode) {
+  const std::string fmt(format_mode.value_or("ND")), qm(quant_mode.value_or("per_channel_symm"));
+  TORCH_CHECK(fmt == "ND" || fmt == "NZ", "format_mode: Unsupported mode value ", fmt);
+  TORCH_CHECK(qm == "per_channel_symm" || qm == "per_channel_asymm" || qm == "per_token_symm", "quant_mode: Unsupported mode value ", qm);
+  TORCH_CHECK(tensor_a.scalar_type() == tensor_b.scalar_type() && tensor_b.scalar_type() == tensor_c.scalar_type(), "tensor type is not the same");
+  TORCH_CHECK(tensor_a.scalar_type() == at::kBFloat16 || tensor_a.scalar_type() == at::kHalf, "tensor type only support half or bf16");
+  TORCH_CHECK(tensor_a.is_cuda() && tensor_b.is_cuda() && tensor_c.is_cuda(), "batch_matmul_transpose: tensors must be CUDA tensors");
+  TORCH_CHECK(tensor_a.is_contiguous() && tensor_b.is_contiguous() && tensor_c.is_contiguous(), "batch_matmul_transpose: tensors must be contiguous");
+  TORCH_CHECK(tensor_a.dim() == 3, "batch size is not same between srcTensor and dstTensor");
+  int64_t n;
+  if (fmt == "ND") {
+    TORCH_CHECK(tensor_b.dim() == 3, "tensor shape should be dim3 in ND format");
+    TORCH_CHECK(tensor_a.size(2) == tensor_b.size(1), "tensor shape is wrong");
+    n = tensor_b.size(2);
+  } else {
+    TORCH_CHECK(tensor_b.dim() == 4, "tensor shape should be dim4 in nz format");
+    TORCH_CHECK(tensor_a.size(2) == tensor_b.size(2), "tensor shape is wrong");
+    n = tensor_b.size(1) * tensor_b.size(3);
+  }
+  TORCH_CHECK(tensor_a.size(1) == tensor_b.size(0), "tensor shape is wrong");
+  TORCH_CHECK(tensor_c.numel() == tensor_a.size(0) * tensor_a.size(1) * n, "tensor_c must hold [m, batch, n] elements");
+  if (tensor_c.numel() == 0) return;
+  const c10::cuda::CUDAGuard guard(tensor_a.device());
+  check_cabi(batch_matmul_transpose_launch(tensor_a.data_ptr(), tensor_b.data_ptr(), tensor_c.data_ptr(), tensor_a.size(0), tensor_a.size(1),
+                                           tensor_a.size(2), n, tensor_a.scalar_type() == at::kBFloat16 ? MLAPO_ACT_BF16 : MLAPO_ACT_FP16,
+                                           fmt == "NZ" ? MLAPO_FORMAT_NZ : MLAPO_FORMAT_ND, at::cuda::getCurrentCUDAStream()),
+             "batch_matmul_transpose_launch");
+}
+
 std::string sgl_kernel_npu_version() { return std::string(mlapo_version()); }
 void sgl_kernel_npu_print_version() { std::printf("%s\n", mlapo_version()); }
 
@@ -260,10 +293,14 @@ TORCH_LIBRARY_FRAGMENT(npu, m) {
       "Tensor(a!) q_out0, Tensor(b!) kv_cache_out0, Tensor(c!) q_out1, Tensor(d!) kv_cache_out1) "
       "-> (Tensor(a!), Tensor(b!), Tensor(c!), Tensor(d!))");
   m.def("mla_preprocess_repack_weight(Tensor w_nz) -> Tensor");
+  m.def(  // csrc/pytorch_extensions.cpp:117-119, verbatim
+      "batch_matmul_transpose(Tensor tensor_a, Tensor tensor_b, Tensor(a!) tensor_c, "
+      "str? format_mode=None, str? quant_mode=None) -> ()");
 }
 
 // csrc/pytorch_extensions.cpp:205, 268 register under PrivateUse1 (the NPU); here the device is CUDA.
 TORCH_LIBRARY_IMPL(npu, CUDA, m) {
   m.impl("mla_preprocess", TORCH_FN(sglang::npu_kernel::mla_preprocess));
   m.impl("mla_preprocess_repack_weight", TORCH_FN(sglang::npu_kernel::mla_preprocess_repack_weight));
+  m.impl("batch_matmul_transpose", TORCH_FN(sglang::npu_kernel::batch_matmul_transpose));
 }

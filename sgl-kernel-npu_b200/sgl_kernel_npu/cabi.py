@@ -50,6 +50,13 @@ def _load():
     lib.mlapo_get_workspace_size.argtypes = [ctypes.POINTER(MlapoParams), ctypes.POINTER(ctypes.c_size_t)]
     lib.mlapo_get_workspace_layout.argtypes = [ctypes.POINTER(MlapoParams), ctypes.POINTER(MlapoWorkspaceLayout)]
     lib.mlapo_repack_nz_weight.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+    lib.mlapo_transdata_nd_to_nz.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64, ctypes.c_int32,
+                                             ctypes.c_int32, ctypes.c_void_p]
+    lib.mlapo_pack_descale_int64.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]
+    lib.mlapo_gather_nz_cache_rows.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32,
+                                               ctypes.c_int32, ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p]
+    lib.batch_matmul_transpose_launch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64,
+                                                  ctypes.c_int64, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
     lib.mla_preprocess_launch.argtypes = [ctypes.POINTER(MlapoParams), ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
     lib.mla_preprocess_launch_static.argtypes = [ctypes.POINTER(MlapoParams), ctypes.c_void_p]
     lib.mlapo_launches_per_call.argtypes = [ctypes.POINTER(MlapoParams)]
@@ -93,6 +100,104 @@ def repack_nz_weight(w_nz: torch.Tensor) -> torch.Tensor:
     with torch.cuda.device(w_nz.device):
         _check(lib.mlapo_repack_nz_weight(w_nz.data_ptr(), out.data_ptr(), k, n_out, _stream_ptr(w_nz)), "mlapo_repack_nz_weight")
     return out
+
+
+def _need_cuda(t, what):
+    if not t.is_cuda or not t.is_contiguous():
+        raise ValueError(f"{what} must be a contiguous CUDA tensor")
+
+
+def transdata_nd_to_nz(nd: torch.Tensor, c0: int = None) -> torch.Tensor:
+    """ND [rows, cols] -> FRACTAL_NZ [1, ceil(cols/c0), ceil16(rows), c0], zero padded (reference test helper `transdata`,
+    tests/python/sgl_kernel_npu/test_mla_preprocess.py:38-54).  c0 defaults to 32 for 1-byte and 16 for 2-byte elements."""
+    if nd.dim() != 2:
+        raise ValueError(f"expected a 2-D tensor, got {tuple(nd.shape)}")
+    _need_cuda(nd, "nd")
+    eb = nd.element_size()
+    c0 = (32 if eb == 1 else 16) if c0 is None else c0
+    rows, cols = nd.shape
+    out = torch.empty((1, -(-cols // c0), -(-rows // 16) * 16, c0), dtype=nd.dtype, device=nd.device)
+    with torch.cuda.device(nd.device):
+        _check(lib.mlapo_transdata_nd_to_nz(nd.data_ptr(), out.data_ptr(), rows, cols, c0, eb, _stream_ptr(nd)), "mlapo_transdata_nd_to_nz")
+    return out
+
+
+def pack_descale_int64(descale_f32: torch.Tensor) -> torch.Tensor:
+    """fp32 descale -> the int64 carrier the fp16 path expects: (bits & 0xFFFFE000) | 1 << 46 (`trans_descale_param`,
+    test_mla_preprocess.py:110-119)."""
+    if descale_f32.dtype != torch.float32:
+        raise ValueError("descale must be float32")
+    _need_cuda(descale_f32, "descale")
+    out = torch.empty(descale_f32.shape, dtype=torch.int64, device=descale_f32.device)
+    with torch.cuda.device(descale_f32.device):
+        _check(lib.mlapo_pack_descale_int64(descale_f32.data_ptr(), out.data_ptr(), descale_f32.numel(), _stream_ptr(descale_f32)),
+               "mlapo_pack_descale_int64")
+    return out
+
+
+def gather_nz_cache_rows(cache: torch.Tensor, slots: torch.Tensor) -> torch.Tensor:
+    """Rows of a paged NZ cache [blocks, width/c0, 128, c0] named by `slots` (int32) -> dense [n, width]; slot -1 -> zeros
+    (`extract_from_nzcache`, test_mla_preprocess.py:122-135)."""
+    if cache.dim() != 4 or cache.shape[2] != 128:
+        raise ValueError(f"expected an NZ cache [blocks, width/c0, 128, c0], got {tuple(cache.shape)}")
+    if slots.dtype != torch.int32 or slots.dim() != 1:
+        raise ValueError("slots must be a 1-D int32 tensor")
+    _need_cuda(cache, "cache")
+    _need_cuda(slots, "slots")
+    blocks, groups, _, c0 = cache.shape
+    width = groups * c0
+    out = torch.empty((slots.numel(), width), dtype=cache.dtype, device=cache.device)
+    if slots.numel():
+        with torch.cuda.device(cache.device):
+            _check(lib.mlapo_gather_nz_cache_rows(cache.data_ptr(), slots.data_ptr(), out.data_ptr(), slots.numel(), width, c0,
+                                                  cache.element_size(), blocks, _stream_ptr(cache)), "mlapo_gather_nz_cache_rows")
+    return out
+
+
+BMT_FORMAT_MAP = {"ND": 0, "NZ": 1}                                                      # batch_matmul_transpose.cpp:22-25
+BMT_QUANT_MODES = ("per_channel_symm", "per_channel_asymm", "per_token_symm")             # :16-20
+
+
+def batch_matmul_transpose(tensor_a, tensor_b, tensor_c, format_mode=None, quant_mode=None) -> None:
+    """tensor_c[m, batch, :] = tensor_a[m, batch, :] @ tensor_b[batch] through the C ABI; argument meaning, mode strings, defaults
+    and checks of csrc/batch_matmul_transpose/op_host/batch_matmul_transpose.cpp:46-80."""
+    fmt = "ND" if format_mode is None else format_mode
+    qm = "per_channel_symm" if quant_mode is None else quant_mode
+    if fmt not in BMT_FORMAT_MAP:
+        raise RuntimeError(f"format_mode: Unsupported mode value {fmt}")
+    if qm not in BMT_QUANT_MODES:
+        raise RuntimeError(f"quant_mode: Unsupported mode value {qm}")
+    if not (tensor_a.dtype == tensor_b.dtype == tensor_c.dtype):
+        raise RuntimeError("tensor type is not the same")
+    if tensor_a.dtype not in (torch.float16, torch.bfloat16):
+        raise RuntimeError("tensor type only support half or bf16")
+    for t, nm in ((tensor_a, "tensor_a"), (tensor_b, "tensor_b"), (tensor_c, "tensor_c")):
+        _need_cuda(t, nm)
+    if tensor_a.dim() != 3:
+        raise RuntimeError("batch size is not same between srcTensor and dstTensor")
+    if fmt == "ND":
+        if tensor_b.dim() != 3:
+            raise RuntimeError("tensor shape should be dim3 in ND format")
+        if tensor_a.shape[2] != tensor_b.shape[1]:
+            raise RuntimeError("tensor shape is wrong")
+        n = tensor_b.shape[2]
+    else:
+        if tensor_b.dim() != 4:
+            raise RuntimeError("tensor shape should be dim4 in nz format")
+        if tensor_a.shape[2] != tensor_b.shape[2]:
+            raise RuntimeError("tensor shape is wrong")
+        n = tensor_b.shape[1] * tensor_b.shape[3]
+    if tensor_a.shape[1] != tensor_b.shape[0]:
+        raise RuntimeError("tensor shape is wrong")
+    m, batch, k = tensor_a.shape
+    if tensor_c.numel() != m * batch * n:
+        raise RuntimeError("tensor_c must hold [m, batch, n] elements")
+    if tensor_c.numel() == 0:
+        return
+    with torch.cuda.device(tensor_a.device):
+        _check(lib.batch_matmul_transpose_launch(tensor_a.data_ptr(), tensor_b.data_ptr(), tensor_c.data_ptr(), m, batch, k, n,
+                                                 (0 if tensor_a.dtype == torch.bfloat16 else 1), BMT_FORMAT_MAP[fmt], _stream_ptr(tensor_a)),
+               "batch_matmul_transpose_launch")
 
 
 def _ptr(t):
