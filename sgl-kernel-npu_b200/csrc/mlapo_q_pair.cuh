@@ -29,8 +29,8 @@ constexpr int kPWukSlots = 3;
 constexpr int kPWukOff = kPNopeOff + 2 * kTile16K;                   // 147456: 3 x 16 KB ([128 k x 64 n] per slot)
 constexpr int kPStageOff = kPWukOff + kPWukSlots * kTile16K;         // 196608: 2 x 16 KB output staging (one per team)
 constexpr int kPBarOff = kPStageOff + 2 * kTile16K;                  // 229376
-constexpr int kPCstPerGroup = 48;
-constexpr int kPSmemBytes = kPBarOff + 256 + 4 * kPCstPerGroup * 8 + 1024;  // 232192
+constexpr int kPCstPerGroup = 96;
+constexpr int kPSmemBytes = kPBarOff + 256 + 2 * kPCstPerGroup * 8 + 1024;  // 232192
 static_assert(kPStageBytes % 1024 == 0 && kPNopeOff % 1024 == 0, "swizzled tiles need 1024-byte alignment");
 static_assert(kPSmemBytes <= 232448, "q_pair smem");
 
@@ -47,7 +47,7 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
   uint64_t* empty_bar = bars + 4;       // [4] MM2 commit (both CTAs) -> TMA
   uint64_t* mm2_done = bars + 8;        // [2] per TMEM region: MM2 commit (both) -> epilogue
   uint64_t* region_free = bars + 10;    // [2] leader's: remote arrives after the last two chunks -> MM2 of the unit after next
-  uint64_t* acc_read = bars + 12;       // [1] leader's: 8 remote arrives (CTA x group): acc2 read, q_nope tiles written -> absorb
+  uint64_t* acc_read = bars + 12;       // [1] leader's: 4 remote arrives (CTA x dequant group): acc2 read, q_nope tiles written -> absorb
   uint64_t* qn_free = bars + 13;        // [1] absorb commit (both) -> epilogue may overwrite the q_nope tiles
   uint64_t* wuk_full = bars + 14;       // [3] leader's: TMA of both CTAs -> absorb
   uint64_t* wuk_empty = bars + 17;      // [3] absorb commit (both) -> TMA
@@ -71,7 +71,7 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
     ptx::prefetch_tmap(&tm_wuk);
     ptx::prefetch_tmap(&tm_out0);
     for (int i = 0; i < 24; ++i) {
-      const uint32_t cnt = (i == 10 || i == 11) ? kRegionFreeCount : i == 12 ? 8u : (i == 22 || i == 23) ? kBufEmptyCount : 1u;
+      const uint32_t cnt = (i == 10 || i == 11) ? kRegionFreeCount : i == 12 ? 4u : (i == 22 || i == 23) ? kBufEmptyCount : 1u;
       ptx::mbar_init(ptx::smem_u32(bars + i), cnt);
     }
     ptx::fence_mbar_init();
@@ -197,218 +197,256 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue: thread = token row, group = column share
-    const int grp = (warp - 4) >> 2;       // 0..3
-    const int team = grp >> 1, sub = grp & 1;
+    // ------------------------------------------------------------------ epilogue warps: thread = token row
+    // Two warp sets work on DIFFERENT units at the same time: warps 4..11 dequantise unit i+1 (acc2 -> q_nope tile, RoPE)
+    // while warps 12..19 drain the absorb results of unit i.  Each set is two groups of 128 threads that split columns.
+    const int eg = (warp - 4) >> 2;        // 0,1: dequant groups; 2,3: drain groups
+    const int g = eg & 1;
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
-    const int et = threadIdx.x - 128 - grp * 128;   // 0..127 inside the group
-    const bool g_issuer = et == 0;
-    const bool t_issuer = g_issuer && sub == 0;     // one thread per team hands TMEM buffers back
-    const int g_bar = 1 + grp, t_bar = 5 + team;
+    const int et = threadIdx.x - 128 - eg * 128;   // 0..127 inside the group
+    const bool issuer = et == 0;
+    const int g_bar = 1 + eg;
     const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
     const bool per_token = qa.tok_scale1 != nullptr;
-    const uint32_t r_acc_read = ptx::mapa(ptx::smem_u32(acc_read), 0);
-    constexpr int kMagic = 0x4B400000;             // bits of 1.5 * 2^23: int v, |v| < 2^22  ->  float(v) = as_float(kMagic + v) - 1.5 * 2^23
-    constexpr float kMagicF = 12582912.f;
     ptx::griddep_wait();  // per-token scales come from the norm kernel
 
-    // Per-unit inputs are fetched one unit ahead: the column constants {bias + kMagic, descale} of the group's 48 columns go to
-    // s_cst[unit parity], this row's cos/sin of dims [8q,8q+8) and 32 + the same and its token scale stay in registers.
-    uint4 cs_lo, sn_lo, cs_hi, sn_hi;
-    float ts = 1.f;
-    int2 cst_next = make_int2(0, 0);
-    auto fetch_unit = [&](int u) {
-      const int head = u / n_tb, t = (u % n_tb) * 256 + (int)rank * kBlockM + row;
-      const int tc = t < qa.m_total ? t : qa.m_total - 1;  // clamped row for loads
-      if (et < kPCstPerGroup) {
-        const int col = et < 32 ? 32 * grp + et : et < 40 ? 128 + 8 * grp + (et - 32) : 160 + 8 * grp + (et - 40);
-        const float dsc = load_descale(qa.descale1, qa.descale_is_i64, head * MLAPO_Q_HEAD + col);
-        cst_next = make_int2((qa.bias1 ? qa.bias1[head * MLAPO_Q_HEAD + col] : 0) + kMagic, __float_as_int(dsc));
-      }
-      if (per_token) ts = qa.tok_scale1[tc];
-      const uint4* cp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(qa.cos) + (long long)tc * 64 + 8 * grp);
-      const uint4* sp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(qa.sin) + (long long)tc * 64 + 8 * grp);
-      cs_lo = ptx::ld_global_nc_v4(cp); sn_lo = ptx::ld_global_nc_v4(sp);
-      cs_hi = ptx::ld_global_nc_v4(cp + 4); sn_hi = ptx::ld_global_nc_v4(sp + 4);
-    };
-    if (pair < total_units) fetch_unit(pair);
-    int2* const s_cst = s_cst_all + grp * kPCstPerGroup;  // [0,32) nope cols 32q.., [32,40) rope dims 8q.., [40,48) 32+8q..
-    const uint32_t st_tile = ptx::smem_u32(smem + kPStageOff + team * kTile16K);
-
-    uint32_t it = 0;
-    for (int u = pair; u < total_units; u += num_pairs, ++it) {
-      const uint32_t par = it & 1;
-      const int head = u / n_tb, tok0 = (u % n_tb) * 256 + (int)rank * kBlockM;
-      const int t = tok0 + row;
-      const bool valid = t < qa.m_total;
-      if (et < kPCstPerGroup) s_cst[et] = cst_next;  // fetched one unit ago; the group's previous unit is completely done
-      const float ts_u = ts;
-      const uint4 cs_lo_u = cs_lo, sn_lo_u = sn_lo, cs_hi_u = cs_hi, sn_hi_u = sn_hi;
-      ptx::named_bar_sync(g_bar, 128);  // constants visible to the group
-
-      ptx::mbar_wait(ptx::smem_u32(mm2_done + par), (it >> 1) & 1);
-      __syncwarp();
-      ptx::tc_fence_after();
-      if (g_issuer && grp == 0 && it < 3) tl_mark(tl, 5 + 3 * it);  // MM2 of unit `it` retired (as seen by the epilogue)
-      const uint32_t acc2 = lane_base + par * 256;
-
-      // int32 -> fp32 without the quarter-rate I2F: exact while |acc + bias| < 2^22; otherwise (never seen with int8 data,
-      // but possible: |acc| can reach 1536 * 2^14) the warp redoes the batch of 8 with the converting instruction.
-      auto deq8 = [&](const uint32_t* raw, int ci, float (&f)[8]) {
-        uint32_t bad = 0;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int2 cst = s_cst[ci + j];
-          const uint32_t bits = raw[j] + (uint32_t)cst.x;
-          bad |= bits ^ 0x4B000000u;
-          const float v = __fadd_rn(__uint_as_float(bits), -kMagicF);
-          f[j] = per_token ? __fmul_rn(__fmul_rn(v, __int_as_float(cst.y)), ts_u) : __fmul_rn(v, __int_as_float(cst.y));
+    if (eg < 2) {
+      // ---------------- dequant set.  Group g: nope columns [64g, 64g+64) -> q_nope tile g (absorb A operand, k-block g);
+      //                  rope dims [16g, 16g+16) and their partners 32 + the same -> RoPE -> q_out1.
+      const uint32_t r_acc_read = ptx::mapa(ptx::smem_u32(acc_read), 0);
+      constexpr int kMagic = 0x4B400000;   // bits of 1.5 * 2^23: int v, |v| < 2^22  ->  float(v) = as_float(kMagic + v) - 1.5 * 2^23
+      constexpr float kMagicF = 12582912.f;
+      int2* const s_cst = s_cst_all + g * kPCstPerGroup;  // [0,64) nope cols 64g.., [64,80) rope dims 16g.., [80,96) 32+16g..
+      // Fetched one unit ahead: the column constants {bias + kMagic, descale} of the group's 96 columns and the token scale.
+      float ts = 1.f;
+      int bias_next = 0;
+      float dsc_next = 0.f;
+      auto fetch_unit = [&](int u) {
+        const int head = u / n_tb, t = (u % n_tb) * 256 + (int)rank * kBlockM + row;
+        const int tc = t < qa.m_total ? t : qa.m_total - 1;  // clamped row for loads
+        if (et < kPCstPerGroup) {
+          const int col = et < 64 ? 64 * g + et : et < 80 ? 128 + 16 * g + (et - 64) : 160 + 16 * g + (et - 80);
+          dsc_next = load_descale(qa.descale1, qa.descale_is_i64, head * MLAPO_Q_HEAD + col);  // consumed when the unit starts
+          bias_next = qa.bias1 ? qa.bias1[head * MLAPO_Q_HEAD + col] : 0;
         }
-        if (__any_sync(0xffffffffu, (bad & 0xFF800000u) != 0)) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const int2 cst = s_cst[ci + j];
-            const float v = __int2float_rn((int)(raw[j] + (uint32_t)cst.x) - kMagic);
-            f[j] = per_token ? __fmul_rn(__fmul_rn(v, __int_as_float(cst.y)), ts_u) : __fmul_rn(v, __int_as_float(cst.y));
-          }
-        }
+        if (per_token) ts = qa.tok_scale1[tc];
       };
-      float xl[8], xh[8];
-      uint32_t wn[16];
-      {
-        uint32_t ra[32];
-        ptx::tmem_ld_32x32b_x32(acc2 + 32 * grp, ra);
-        ptx::tmem_ld_wait();
-        uint32_t rl[8], rh[8];
-        ptx::tmem_ld_32x32b_x8(acc2 + 128 + 8 * grp, rl);
-        ptx::tmem_ld_32x32b_x8(acc2 + 160 + 8 * grp, rh);
-#pragma unroll
-        for (int b8 = 0; b8 < 4; ++b8) {
-          float f[8];
-          deq8(ra + 8 * b8, 8 * b8, f);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) wn[4 * b8 + j] = Act<T>::pack(f[2 * j], f[2 * j + 1]);
-        }
-        ptx::tmem_ld_wait();
-        deq8(rl, 32, xl);
-        deq8(rh, 40, xh);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { xl[j] = Act<T>::round(xl[j]); xh[j] = Act<T>::round(xh[j]); }
-      }
-      // this group's 64 bytes of every q_nope row (absorb A operand): free once the previous unit's absorb MMAs have retired
-      if (it > 0) ptx::mbar_wait(ptx::smem_u32(qn_free), (it - 1) & 1);
-      __syncwarp();
-      {
-        const uint32_t tile = ptx::smem_u32(smem + kPNopeOff + team * kTile16K);
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          ptx::st_shared_v4(tile + ptx::sw128_offset(row, sub * 4 + j), wn[4 * j], wn[4 * j + 1], wn[4 * j + 2], wn[4 * j + 3]);
-      }
-      ptx::fence_proxy_async_smem();
-      ptx::tc_fence_before();
-      ptx::named_bar_sync(g_bar, 128);
-      if (g_issuer) ptx::mbar_arrive_cluster(r_acc_read);  // this group's share of acc2 is read, its q_nope bytes are written
-      if (g_issuer && grp == 3 && it < 3) tl_mark(tl, 6 + 3 * it);
+      if (pair < total_units) fetch_unit(pair);
 
-      // RoPE of dims [8q,8q+8) and their partners, straight to q_out1 (test_mla:57-67)
-      if (valid) {
-        T* dst = reinterpret_cast<T*>(q_out1) + ((long long)t * qa.num_heads + head) * MLAPO_ROPE + 8 * grp;
-        float c_lo[8], s_lo[8], c_hi[8], s_hi[8];
-        unpack8<T>(cs_lo_u, c_lo);
-        unpack8<T>(sn_lo_u, s_lo);
-        unpack8<T>(cs_hi_u, c_hi);
-        unpack8<T>(sn_hi_u, s_hi);
-        uint32_t wl[4], wh[4];
-#pragma unroll
-        for (int v = 0; v < 4; ++v) {
-          const int i0 = 2 * v, i1 = i0 + 1;
-          const float a0 = __fadd_rn(__fmul_rn(xl[i0], c_lo[i0]), __fmul_rn(-xh[i0], s_lo[i0]));
-          const float a1 = __fadd_rn(__fmul_rn(xl[i1], c_lo[i1]), __fmul_rn(-xh[i1], s_lo[i1]));
-          const float b0 = __fadd_rn(__fmul_rn(xh[i0], c_hi[i0]), __fmul_rn(xl[i0], s_hi[i0]));
-          const float b1 = __fadd_rn(__fmul_rn(xh[i1], c_hi[i1]), __fmul_rn(xl[i1], s_hi[i1]));
-          wl[v] = Act<T>::pack(a0, a1);
-          wh[v] = Act<T>::pack(b0, b1);
-        }
-        ptx::st_global_v4(dst, wl[0], wl[1], wl[2], wl[3]);
-        ptx::st_global_v4(dst + 32, wh[0], wh[1], wh[2], wh[3]);
-      }
-      // next unit's inputs: their latency hides behind this unit's drains
-      if (u + num_pairs < total_units) fetch_unit(u + num_pairs);
+      uint32_t it = 0;
+      for (int u = pair; u < total_units; u += num_pairs, ++it) {
+        const uint32_t par = it & 1;
+        const int head = u / n_tb, tok0 = (u % n_tb) * 256 + (int)rank * kBlockM;
+        const int t = tok0 + row;
+        const bool valid = t < qa.m_total;
+        if (et < kPCstPerGroup) s_cst[et] = make_int2(bias_next + kMagic, __float_as_int(dsc_next));  // fetched one unit ago
+        const float ts_u = ts;  // 1 in per-tensor mode
+        // this row's cos/sin (dims [16g,16g+16) and 32 + the same), used after the hand-off to the absorb
+        const T* cos_row = reinterpret_cast<const T*>(qa.cos) + (long long)(valid ? t : qa.m_total - 1) * 64 + 16 * g;
+        const T* sin_row = reinterpret_cast<const T*>(qa.sin) + (long long)(valid ? t : qa.m_total - 1) * 64 + 16 * g;
+        ptx::named_bar_sync(g_bar, 128);  // constants visible to the group
 
-      // drains: TMEM -> registers -> swizzled staging tile of the team -> TMA store into q_out0
-      if (kInt8Out) {
-        // S9: int8( fp16( act(acc) * q_nope_scale[h] ) )   (golden test_mla:86-92, 466-470).  Team t owns TMEM buffer t:
-        // chunks c = t, t+2; group `sub` converts columns [64 sub, 64 sub + 64) = 64 bytes of the 128-byte output row.
-        const float qs = Act<T>::to_f(reinterpret_cast<const T*>(qa.q_nope_scale)[head]);
-#pragma unroll 1
-        for (int cc = 0; cc < 2; ++cc) {
-          const int c = team + 2 * cc;
-          ptx::mbar_wait(ptx::smem_u32(unit_full + team), (it * 2 + cc) & 1);
-          __syncwarp();
-          ptx::tc_fence_after();
-          const uint32_t acc3 = lane_base + par * 256 + team * 128 + sub * 64;
-          uint32_t w[16];
+        ptx::mbar_wait(ptx::smem_u32(mm2_done + par), (it >> 1) & 1);
+        __syncwarp();
+        ptx::tc_fence_after();
+        if (issuer && g == 0 && it < 3) tl_mark(tl, 5 + 3 * it);  // MM2 of unit `it` retired (as seen by the dequant set)
+        const bool tr = issuer && g == 0 && it >= 2 && it < 4;
+        const int tb = (it - 2) * 32;
+        tl_trace(tl, tr, tb + 0);
+        const uint32_t acc2 = lane_base + par * 256;
+
+        // int32 -> fp32 without the quarter-rate I2F: exact while |acc + bias| < 2^22; otherwise (never seen with int8 data,
+        // but possible: |acc| can reach 1536 * 2^14) the warp redoes the batch of 8 with the converting instruction.
+        // (x * 1.0f is exact, so the per-tensor mode simply carries a token scale of 1; its bias rides in cst.x)
+        auto deq16 = [&](const uint32_t* raw, int ci, float (&f)[16]) {
+          uint32_t bad = 0;
 #pragma unroll
-          for (int c0 = 0; c0 < 64; c0 += 32) {
-            uint32_t r[32];
-            ptx::tmem_ld_32x32b_x32(acc3 + c0, r);
-            ptx::tmem_ld_wait();
+          for (int j = 0; j < 16; j += 2) {
+            const int4 cst = *reinterpret_cast<const int4*>(s_cst + ci + j);  // two columns per shared-memory load
+            const uint32_t b0 = raw[j] + (uint32_t)cst.x, b1 = raw[j + 1] + (uint32_t)cst.z;
+            bad |= (b0 ^ 0x4B000000u) | (b1 ^ 0x4B000000u);
+            f[j] = __fmul_rn(__fmul_rn(__fadd_rn(__uint_as_float(b0), -kMagicF), __int_as_float(cst.y)), ts_u);
+            f[j + 1] = __fmul_rn(__fmul_rn(__fadd_rn(__uint_as_float(b1), -kMagicF), __int_as_float(cst.w)), ts_u);
+          }
+          if (__any_sync(0xffffffffu, (bad & 0xFF800000u) != 0)) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              int q[4];
-#pragma unroll
-              for (int v = 0; v < 4; ++v) q[v] = sat_i8(__fmul_rn(Act<T>::round(__uint_as_float(r[4 * j + v])), qs));
-              w[(c0 >> 2) + j] = pack4_i8(q[0], q[1], q[2], q[3]);
+            for (int j = 0; j < 16; ++j) {
+              const int2 cst = s_cst[ci + j];
+              f[j] = __fmul_rn(__fmul_rn(__int2float_rn((int)(raw[j] + (uint32_t)cst.x) - kMagic), __int_as_float(cst.y)), ts_u);
             }
           }
-          ptx::tc_fence_before();
-          if (t_issuer) ptx::tma_store_wait_read<0>();   // the team's previous store has finished reading the staging tile
-          ptx::named_bar_sync(t_bar, 256);               // ... and every thread of the team is past its TMEM loads of chunk c
-          if (t_issuer) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(cc == 0 ? buf_empty + team : region_free + par), 0));
+        };
+        // q_nope tile g is free once the previous unit's absorb MMAs have retired (normally long before this unit's MM2 has)
+        if (it > 0) ptx::mbar_wait(ptx::smem_u32(qn_free), (it - 1) & 1);
+        __syncwarp();
+        tl_trace(tl, tr, tb + 1);
+        const uint32_t tile = ptx::smem_u32(smem + kPNopeOff + g * kTile16K);
+        float xl[16], xh[16];
+        {
+          // 16 columns per TMEM load, the next load in flight while the current one is converted (96 registers per thread)
+          uint32_t r0[16], r1[16];
+          ptx::tmem_ld_32x32b_x16(acc2 + 64 * g, r0);
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, sub * 4 + j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
-          ptx::fence_proxy_async_smem();
-          ptx::named_bar_sync(t_bar, 256);
-          if (t_issuer) {
-            ptx::tma_store_2d(&tm_out0, st_tile, head * MLAPO_KV_LORA + c * 128, tok0);
-            ptx::tma_store_commit();
-          }
-        }
-      } else {
-        // Team t drains columns [64t, 64t+64) of every chunk; group `sub` converts 32 of them = 64 bytes of the staging row.
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          ptx::mbar_wait(ptx::smem_u32(unit_full + (c & 1)), (it * 2 + (c >> 1)) & 1);
-          __syncwarp();
-          ptx::tc_fence_after();
-          uint32_t w[16];
-          {
-            uint32_t r[32];
-            ptx::tmem_ld_32x32b_x32(lane_base + par * 256 + (c & 1) * 128 + team * 64 + sub * 32, r);
+          for (int q = 0; q < 4; ++q) {
+            uint32_t (&cur)[16] = (q & 1) ? r1 : r0;
+            uint32_t (&nxt)[16] = (q & 1) ? r0 : r1;
             ptx::tmem_ld_wait();
+            tl_trace(tl, tr, tb + 2 + 2 * q);
+            if (q < 3) ptx::tmem_ld_32x32b_x16(acc2 + 64 * g + 16 * (q + 1), nxt);
+            else ptx::tmem_ld_32x32b_x16(acc2 + 128 + 16 * g, nxt);  // rope dims 16g..: lands in r0
+            {
+              float f[16];
+              deq16(cur, 16 * q, f);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) w[j] = Act<T>::pack(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+              for (int b8 = 0; b8 < 2; ++b8)
+                ptx::st_shared_v4(tile + ptx::sw128_offset(row, 2 * q + b8), Act<T>::pack(f[8 * b8], f[8 * b8 + 1]), Act<T>::pack(f[8 * b8 + 2], f[8 * b8 + 3]),
+                                  Act<T>::pack(f[8 * b8 + 4], f[8 * b8 + 5]), Act<T>::pack(f[8 * b8 + 6], f[8 * b8 + 7]));
+            }
+            tl_trace(tl, tr, tb + 3 + 2 * q);
           }
-          ptx::tc_fence_before();
-          if (t_issuer) ptx::tma_store_wait_read<0>();
-          ptx::named_bar_sync(t_bar, 256);
-          if (t_issuer) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(c < 2 ? buf_empty + c : region_free + par), 0));
+          ptx::tmem_ld_wait();
+          ptx::tmem_ld_32x32b_x16(acc2 + 160 + 16 * g, r1);  // their partners 32 + 16g..
+          deq16(r0, 64, xl);
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, sub * 4 + j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
-          ptx::fence_proxy_async_smem();
-          ptx::named_bar_sync(t_bar, 256);
-          if (t_issuer) {
-            ptx::tma_store_2d(&tm_out0, st_tile, head * MLAPO_KV_LORA + c * 128 + team * 64, tok0);
-            ptx::tma_store_commit();
+          for (int j = 0; j < 16; ++j) xl[j] = Act<T>::round(xl[j]);
+          ptx::tmem_ld_wait();
+          deq16(r1, 80, xh);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) xh[j] = Act<T>::round(xh[j]);
+        }
+        tl_trace(tl, tr, tb + 10);
+        if (u + num_pairs < total_units) fetch_unit(u + num_pairs);  // consumed when the next unit starts
+        // cos/sin of this row: an L2 round trip is ~2.5k cycles under this load; requested here (earlier costs spills), used
+        // after the hand-off to the absorb
+        uint4 cs4[4], sn4[4];
+        {
+          const uint4* cp = reinterpret_cast<const uint4*>(cos_row);
+          const uint4* sp = reinterpret_cast<const uint4*>(sin_row);
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            cs4[j] = ptx::ld_global_nc_v4(cp + j); sn4[j] = ptx::ld_global_nc_v4(sp + j);
+            cs4[2 + j] = ptx::ld_global_nc_v4(cp + 4 + j); sn4[2 + j] = ptx::ld_global_nc_v4(sp + 4 + j);
           }
         }
+        ptx::fence_proxy_async_smem();
+        ptx::tc_fence_before();
+        tl_trace(tl, tr, tb + 11);
+        ptx::named_bar_sync(g_bar, 128);
+        tl_trace(tl, tr, tb + 12);
+        if (issuer) ptx::mbar_arrive_cluster(r_acc_read);  // this group's share of acc2 is read, its q_nope tile is written
+        tl_trace(tl, tr, tb + 13);
+        if (issuer && g == 1 && it < 3) tl_mark(tl, 6 + 3 * it);
+
+        // RoPE of dims [16g,16g+16) and their partners, 32-byte sectors straight to q_out1 (test_mla:57-67)
+        if (valid) {
+          T* dst = reinterpret_cast<T*>(q_out1) + ((long long)t * qa.num_heads + head) * MLAPO_ROPE + 16 * g;
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            float c_lo[8], s_lo[8], c_hi[8], s_hi[8];
+            unpack8<T>(cs4[j], c_lo);
+            unpack8<T>(sn4[j], s_lo);
+            unpack8<T>(cs4[2 + j], c_hi);
+            unpack8<T>(sn4[2 + j], s_hi);
+            uint32_t wl[4], wh[4];
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+              const int i0 = 8 * j + 2 * v, i1 = i0 + 1;
+              const float a0 = __fadd_rn(__fmul_rn(xl[i0], c_lo[2 * v]), __fmul_rn(-xh[i0], s_lo[2 * v]));
+              const float a1 = __fadd_rn(__fmul_rn(xl[i1], c_lo[2 * v + 1]), __fmul_rn(-xh[i1], s_lo[2 * v + 1]));
+              const float b0 = __fadd_rn(__fmul_rn(xh[i0], c_hi[2 * v]), __fmul_rn(xl[i0], s_hi[2 * v]));
+              const float b1 = __fadd_rn(__fmul_rn(xh[i1], c_hi[2 * v + 1]), __fmul_rn(xl[i1], s_hi[2 * v + 1]));
+              wl[v] = Act<T>::pack(a0, a1);
+              wh[v] = Act<T>::pack(b0, b1);
+            }
+            ptx::st_global_v4(dst + 8 * j, wl[0], wl[1], wl[2], wl[3]);
+            ptx::st_global_v4(dst + 32 + 8 * j, wh[0], wh[1], wh[2], wh[3]);
+          }
+        }
+        tl_trace(tl, tr, tb + 14);
       }
-      if (g_issuer && grp == 3 && it < 3) tl_mark(tl, 7 + 3 * it);  // unit `it` drained
+    } else {
+      // ---------------- drain set.  act out: group g drains columns [64g, 64g+64) of every chunk (one 128-byte row per token);
+      //                  int8 out: group g owns TMEM buffer g and drains whole chunks c = g, g+2 (128 int8 = one 128-byte row).
+      //                  TMEM -> registers -> this group's swizzled 16 KB staging tile -> TMA store into q_out0.
+      const uint32_t st_tile = ptx::smem_u32(smem + kPStageOff + g * kTile16K);
+      uint32_t it = 0;
+      for (int u = pair; u < total_units; u += num_pairs, ++it) {
+        const uint32_t par = it & 1;
+        const int head = u / n_tb, tok0 = (u % n_tb) * 256 + (int)rank * kBlockM;
+        if (kInt8Out) {
+          // S9: int8( fp16( act(acc) * q_nope_scale[h] ) )   (golden test_mla:86-92, 466-470)
+          const float qs = Act<T>::to_f(reinterpret_cast<const T*>(qa.q_nope_scale)[head]);
+#pragma unroll 1
+          for (int cc = 0; cc < 2; ++cc) {
+            const int c = g + 2 * cc;
+            ptx::mbar_wait(ptx::smem_u32(unit_full + g), (it * 2 + cc) & 1);
+            __syncwarp();
+            ptx::tc_fence_after();
+            const uint32_t acc3 = lane_base + par * 256 + g * 128;
+            uint32_t w[32];
+#pragma unroll
+            for (int c0 = 0; c0 < 128; c0 += 32) {
+              uint32_t r[32];
+              ptx::tmem_ld_32x32b_x32(acc3 + c0, r);
+              ptx::tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                int q[4];
+#pragma unroll
+                for (int v = 0; v < 4; ++v) q[v] = sat_i8(__fmul_rn(Act<T>::round(__uint_as_float(r[4 * j + v])), qs));
+                w[(c0 >> 2) + j] = pack4_i8(q[0], q[1], q[2], q[3]);
+              }
+            }
+            ptx::tc_fence_before();
+            if (issuer) ptx::tma_store_wait_read<0>();   // the group's previous store has finished reading the staging tile
+            ptx::named_bar_sync(g_bar, 128);             // ... and every thread of the group is past its TMEM loads of chunk c
+            if (issuer) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(cc == 0 ? buf_empty + g : region_free + par), 0));
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+            ptx::fence_proxy_async_smem();
+            ptx::named_bar_sync(g_bar, 128);
+            if (issuer) {
+              ptx::tma_store_2d(&tm_out0, st_tile, head * MLAPO_KV_LORA + c * 128, tok0);
+              ptx::tma_store_commit();
+            }
+          }
+        } else {
+#pragma unroll 1
+          for (int c = 0; c < 4; ++c) {
+            ptx::mbar_wait(ptx::smem_u32(unit_full + (c & 1)), (it * 2 + (c >> 1)) & 1);
+            __syncwarp();
+            ptx::tc_fence_after();
+            uint32_t w[32];
+            {
+              const uint32_t acc3 = lane_base + par * 256 + (c & 1) * 128 + g * 64;
+#pragma unroll
+              for (int hh = 0; hh < 2; ++hh) {  // 32 columns at a time keeps the live registers under the 96 of a 640-thread CTA
+                uint32_t r[32];
+                ptx::tmem_ld_32x32b_x32(acc3 + 32 * hh, r);
+                ptx::tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 16; ++j) w[16 * hh + j] = Act<T>::pack(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+              }
+            }
+            ptx::tc_fence_before();
+            if (issuer) ptx::tma_store_wait_read<0>();
+            ptx::named_bar_sync(g_bar, 128);
+            if (issuer) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(c < 2 ? buf_empty + c : region_free + par), 0));
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+            ptx::fence_proxy_async_smem();
+            ptx::named_bar_sync(g_bar, 128);
+            if (issuer) {
+              ptx::tma_store_2d(&tm_out0, st_tile, head * MLAPO_KV_LORA + c * 128 + g * 64, tok0);
+              ptx::tma_store_commit();
+            }
+          }
+        }
+        if (issuer && g == 1 && it < 3) tl_mark(tl, 7 + 3 * it);  // unit `it` drained
+      }
+      if (issuer) ptx::tma_store_wait_read<0>();
     }
-    if (t_issuer) ptx::tma_store_wait_read<0>();
   }
 
   // nobody leaves while the peer may still address this CTA's shared memory, barriers or tensor memory

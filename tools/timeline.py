@@ -100,6 +100,12 @@ def main(workload="c2", pdl=False, persistent=False, legacy=False):
                   f" CTA end p10/p50/p90/max {np.percentile(e, 10):.2f} {np.median(e):.2f} {np.percentile(e, 90):.2f} {e.max():.2f}")
         g = a[:, 0]
         print(f"   CTA start skew (globaltimer ns): p50-min {np.median(g) - g.min():.0f}  max-min {g.max() - g.min():.0f}")
+    if qname == "q_pair":
+        tr = tl[1][1024:1024 + 8].reshape(-1)
+        names = ["mm2_done", "qn_free", "ld0", "deq0", "ld1", "deq1", "ld2", "deq2", "ld3", "deq3", "rope_deq", "fence", "g_bar", "arrive", "rope_st", "fetch"]
+        for it in range(2):
+            b = it * 32
+            print(f"dequant trace unit {it + 2} (cycles since its mm2_done mark): " + " ".join(f"{names[j]}={tr[b + j] - tr[b]}" for j in range(16)))
     cabi.set_debug_flags(0)
 
 
