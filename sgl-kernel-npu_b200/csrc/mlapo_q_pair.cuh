@@ -20,6 +20,8 @@
 
 namespace mlapo {
 
+constexpr int kMagic = 0x4B400000;      // bits of 1.5 * 2^23: for an int v with |v| < 2^22, float(v) == as_float(kMagic + v) - kMagicF
+constexpr float kMagicF = 12582912.f;
 constexpr int kPThreads = 640;
 constexpr int kPStages = 4;
 constexpr int kPHalfB = MLAPO_Q_HEAD / 2;                            // 96 W_UQ rows per CTA
@@ -215,8 +217,6 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
       // ---------------- dequant set.  Group g: nope columns [64g, 64g+64) -> q_nope tile g (absorb A operand, k-block g);
       //                  rope dims [16g, 16g+16) and their partners 32 + the same -> RoPE -> q_out1.
       const uint32_t r_acc_read = ptx::mapa(ptx::smem_u32(acc_read), 0);
-      constexpr int kMagic = 0x4B400000;   // bits of 1.5 * 2^23: int v, |v| < 2^22  ->  float(v) = as_float(kMagic + v) - 1.5 * 2^23
-      constexpr float kMagicF = 12582912.f;
       int2* const s_cst = s_cst_all + g * kPCstPerGroup;  // [0,64) nope cols 64g.., [64,80) rope dims 16g.., [80,96) 32+16g..
       // Fetched one unit ahead: the column constants {bias + kMagic, descale} of the group's 96 columns and the token scale.
       float ts = 1.f;
