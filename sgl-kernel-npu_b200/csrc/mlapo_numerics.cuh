@@ -39,10 +39,13 @@ template <> struct Act<__half> {
 };
 
 // fp32 -> fp16 (RNE) -> clamp [-128,127] -> round-half-even -> int8   (golden: test_mla:81-83)
+// Written without the quarter-rate scalar conversions: the packed F2FP does the RNE rounding to fp16, and adding 1.5 * 2^23
+// rounds the clamped value (|h| <= 128) to the nearest-even integer exactly, leaving it in the low mantissa bits.
 __device__ __forceinline__ int sat_i8(float f) {
-  float h = __half2float(__float2half_rn(f));
+  const __half2 h2 = __floats2half2_rn(f, f);
+  float h = __low2float(h2);
   h = fminf(fmaxf(h, -128.f), 127.f);
-  return __float2int_rn(h);
+  return __float_as_int(__fadd_rn(h, 12582912.f)) - 0x4B400000;
 }
 __device__ __forceinline__ uint32_t pack4_i8(int a, int b, int c, int d) {
   return (uint32_t)(a & 0xFF) | ((uint32_t)(b & 0xFF) << 8) | ((uint32_t)(c & 0xFF) << 16) | ((uint32_t)(d & 0xFF) << 24);
