@@ -6,12 +6,14 @@
 // only 192 TMEM columns per unit.  That leaves room for a second accumulator set, so a pair walks a list of units and
 // MM2 of unit i+1 streams in while unit i is dequantised, absorbed and stored:
 //   MM2    acc2 = a1 . Wuq[head]^T        kind::i8, M=256 (2x128), N=192, TMEM region (i&1)*256 + [0,192)
-//   epi2   16 epilogue warps = 4 groups of 128 threads (thread = token row).  Group q takes nope columns [32q,32q+32)
-//          -> swizzled smem (absorb A operand) and rope dims [8q,8q+8) with their partners +32 -> RoPE -> q_out1
+//   epi2   dequant set (warps 4..11, two groups of 128 threads, thread = token row): group g takes nope columns
+//          [64g,64g+64) -> swizzled smem (absorb A operand, k-block g) and rope dims [16g,16g+16) with their partners +32
+//          -> RoPE -> q_out1
 //   BMM3   acc3 = q_nope . Wuk[head][:, chunk c]   kind::f16, M=256, N=128 (each CTA holds 64 of the 128 columns),
 //          buffer c&1 of the same TMEM region: [0,128) (the nope columns, already drained) / [128,256)
-//   epi3   act out: groups {0,1} / {2,3} form two teams; team t drains columns [64t,64t+64) of every chunk through one
-//          16 KB staging tile -> TMA store.   int8 out: team t drains whole chunks c = t, t+2 (128 int8 = one 128-byte row)
+//   epi3   drain set (warps 12..19, two groups): act out — group g drains columns [64g,64g+64) of every chunk through its
+//          16 KB staging tile -> TMA store; int8 out — group g drains whole chunks c = g, g+2 (128 int8 = one 128-byte row).
+//          The two sets work on different units at the same time (dequant of unit i+1 under the drains of unit i).
 // Warps: 0 TMA a1+W_UQ | 1 MM2 issuer (leader CTA), TMEM alloc | 2 TMA W_UK | 3 absorb issuer (leader CTA) | 4..19 epilogue.
 // Barriers live at the same offset in both CTAs.  TMA completions of both CTAs are counted on the LEADER's full
 // barriers; tcgen05.commit multicasts to both CTAs; epilogue -> MMA signals are remote arrives on the leader's copies.
@@ -29,7 +31,7 @@ constexpr int kPStageBytes = kTile16K + kPHalfB * kBlockKBytes;      // 28672
 constexpr int kPNopeOff = kPStages * kPStageBytes;                   // 114688: 2 x 16 KB (k-block 0 / 1 of this CTA's token tile)
 constexpr int kPWukSlots = 3;
 constexpr int kPWukOff = kPNopeOff + 2 * kTile16K;                   // 147456: 3 x 16 KB ([128 k x 64 n] per slot)
-constexpr int kPStageOff = kPWukOff + kPWukSlots * kTile16K;         // 196608: 2 x 16 KB output staging (one per team)
+constexpr int kPStageOff = kPWukOff + kPWukSlots * kTile16K;         // 196608: 2 x 16 KB output staging (one per drain group)
 constexpr int kPBarOff = kPStageOff + 2 * kTile16K;                  // 229376
 constexpr int kPCstPerGroup = 96;
 constexpr int kPSmemBytes = kPBarOff + 256 + 2 * kPCstPerGroup * 8 + 1024;  // 232192
@@ -57,7 +59,7 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
   uint64_t* buf_empty = bars + 22;      // [2] leader's: remote arrives after chunks 0 / 1 -> absorb chunk c+2
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
   int2* s_cst_all = reinterpret_cast<int2*>(smem + kPBarOff + 256);
-  // arrivals per completion: act out — both teams drain every chunk; int8 out — team t alone drains chunks t, t+2
+  // arrivals per completion: act out — both drain groups take part in every chunk; int8 out — group g alone drains chunks g, g+2
   constexpr uint32_t kBufEmptyCount = kInt8Out ? 2u : 4u;
   constexpr uint32_t kRegionFreeCount = kInt8Out ? 4u : 8u;
 
