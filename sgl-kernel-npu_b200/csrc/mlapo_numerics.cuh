@@ -41,14 +41,16 @@ template <> struct Act<__half> {
 // fp32 -> fp16 (RNE) -> clamp [-128,127] -> round-half-even -> int8   (golden: test_mla:81-83)
 // Written without the quarter-rate scalar conversions: the packed F2FP does the RNE rounding to fp16, and adding 1.5 * 2^23
 // rounds the clamped value (|h| <= 128) to the nearest-even integer exactly, leaving it in the low mantissa bits.
+// Returns a word whose LOW BYTE is the int8 result (two's complement); the upper bytes are the magic constant's.
 __device__ __forceinline__ int sat_i8(float f) {
   const __half2 h2 = __floats2half2_rn(f, f);
   float h = __low2float(h2);
   h = fminf(fmaxf(h, -128.f), 127.f);
-  return __float_as_int(__fadd_rn(h, 12582912.f)) - 0x4B400000;
+  return __float_as_int(__fadd_rn(h, 12582912.f));
 }
+// low bytes of four words -> one word (three byte permutes)
 __device__ __forceinline__ uint32_t pack4_i8(int a, int b, int c, int d) {
-  return (uint32_t)(a & 0xFF) | ((uint32_t)(b & 0xFF) << 8) | ((uint32_t)(c & 0xFF) << 16) | ((uint32_t)(d & 0xFF) << 24);
+  return __byte_perm(__byte_perm((uint32_t)a, (uint32_t)b, 0x0040), __byte_perm((uint32_t)c, (uint32_t)d, 0x0040), 0x5410);
 }
 template <class T>
 __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
