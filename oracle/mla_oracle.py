@@ -290,12 +290,15 @@ def sum_squares_f32(x: torch.Tensor, var_mode: str) -> torch.Tensor:
 def rms_norm_f32(x, gamma, var_mode="exact", beta=None):
     """``fp32(x) * rsqrt(mean(x^2)+eps) * fp32(gamma) [+ fp32(beta)]`` in fp32 (test_mla:70-74, 432-433).
 
-    ``rsqrt`` is evaluated as two correctly rounded operations, ``1 / sqrt(.)``,
-    which is what torch's CPU ``rsqrt`` does and what the CUDA path mirrors with
-    ``__fdiv_rn(1, __fsqrt_rn(.))``.
+    ``rsqrt`` is evaluated as two correctly rounded operations, ``1 / sqrt(.)``
+    (what torch's CPU ``rsqrt`` returns on the golden's inputs), mirrored on the
+    CUDA path by ``__fdiv_rn(1, __fsqrt_rn(.))``.
     """
     var = sum_squares_f32(x, var_mode)
-    r = 1.0 / torch.sqrt(var + EPS)
+    # numpy's float32 sqrt and divide are the correctly rounded IEEE operations on every host; torch.sqrt on CPU is not
+    # (observed: 0x40257d15 -> 0x3fcdd3ea instead of 0x3fcdd3eb), which flips one bf16 rounding in ~10^6 outputs
+    v = (var + EPS).numpy().astype(np.float32)
+    r = torch.from_numpy(np.float32(1.0) / np.sqrt(v, dtype=np.float32))
     y = x.to(torch.float32) * r * gamma.to(torch.float32)
     if beta is not None:
         y = y + beta.to(torch.float32)

@@ -32,6 +32,10 @@ CASES = [
     (128, 3, 2048, "bf16", "krope_ctkv", PT, 0.0),
     (257, 5, 8192, "bf16", "int8_nzcache", PT, 0.02),
     (256, 1, 7168, "fp16", "nzcache", PT, 0.0),
+    # two token tiles per CTA and >= 96 (head, 256-token) units in one wave (the decode configuration of the bench)
+    (130, 96, 6144, "bf16", "int8_nzcache", PT, 0.05),
+    (256, 100, 7168, "fp16", "krope_ctkv", TOK, 0.0),
+    (200, 128, 7168, "bf16", "nzcache", PT, 0.0),
     # prefill-sized: no split-K, 256-wide MM1 tiles, many token super-tiles (the reference stops at 1024 tokens)
     (2400, 2, 7168, "bf16", "krope_ctkv", PT, 0.05),
     # more (head, 256-token) units than SMs: the q path runs in its streaming form (persistent CTAs, overlapped units)

@@ -19,3 +19,7 @@ res, ocase, otaps = hz.compare(case, qm, g, taps)
 print(sys.argv[1:], {k: v for k, v in res.items()})
 bad = (g["q_out1"].cpu() != ocase.t["q_out1"]).nonzero()
 print("q_out1 mismatches at (token, head, col):", bad[:8].tolist())
+for key in ("kv_cache", "kv_cache_rope"):
+    a, b = g[key].cpu().reshape(-1), ocase.t[key].reshape(-1)
+    idx = (a != b).nonzero().reshape(-1)
+    print(key, "mismatches:", [(int(i), float(a[i]), float(b[i])) for i in idx[:8]])
