@@ -162,17 +162,21 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
     ptx::tc_fence_after();
     if (issuer) tl_mark(tl, 6);  // MMAs retired
     __syncwarp();                                 // tcgen05.ld below is warp-aligned: reconverge after the one-lane branch
+    // each token tile gets its own staging tiles when the drained pipeline is large enough for all of them (decode shape);
+    // otherwise the tiles are re-used and the previous token tile's stores must have been read first
+    constexpr bool kOwnStaging = MT * GRANULES * kTile16K <= STAGES * STAGE_BYTES;
     for (int m = 0; m < mt_valid; ++m) {
-      if (m > 0) {  // the staging tiles are re-used per token tile: the previous tile's stores must have been read
+      if (m > 0 && !kOwnStaging) {
         if (issuer) ptx::tma_store_wait_read<0>();
         ptx::named_bar_sync(1, 128);
       }
+      uint8_t* const stg = smem + (kOwnStaging ? m * GRANULES * kTile16K : 0);
 #pragma unroll 1
       for (int g = 0; g < GRANULES; ++g) {
         uint32_t r[32];
         ptx::tmem_ld_32x32b_x32(t_base + m * BN + g * 32, r);
         ptx::tmem_ld_wait();
-        const uint32_t tile = ptx::smem_u32(smem + g * kTile16K);
+        const uint32_t tile = ptx::smem_u32(stg + g * kTile16K);
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           ptx::st_shared_v4(tile + ptx::sw128_offset(row, j), r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
@@ -182,7 +186,7 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
       if (issuer) {
         for (int g = 0; g < GRANULES; ++g)
           if (n0 + g * 32 < MLAPO_MM1_OUT)
-            ptx::tma_store_3d(tm_p, ptx::smem_u32(smem + g * kTile16K), n0 + g * 32, m0 + m * kBlockM, split);
+            ptx::tma_store_3d(tm_p, ptx::smem_u32(stg + g * kTile16K), n0 + g * 32, m0 + m * kBlockM, split);
         ptx::tma_store_commit();
       }
     }
