@@ -242,10 +242,13 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
       const int t = tok0 + m * kBlockM + row;
       const int tc = t < qa.m_total ? t : qa.m_total - 1;  // clamped row for loads; TMA stores clip rows >= N
       const float ts = per_token ? qa.tok_scale1[tc] : 1.f;
-      auto deq = [&](uint32_t acc, int c) -> float {
-        const int2 cst = s_cst[c];
-        return per_token ? __fmul_rn(__fmul_rn(__int2float_rn((int)acc), __int_as_float(cst.y)), ts)
-                         : __fmul_rn(__int2float_rn((int)acc + cst.x), __int_as_float(cst.y));
+      // y = fp32(acc + bias) * descale * token scale for columns c, c+1 (c even): the per-tensor mode carries a token scale of 1
+      // (x * 1.0f is exact), the per-token mode a bias of 0, so one expression serves both; one 16-byte load brings both columns'
+      // constants
+      auto deq2 = [&](uint32_t acc0, uint32_t acc1, int c, float& f0, float& f1) {
+        const int4 cst = *reinterpret_cast<const int4*>(s_cst + c);
+        f0 = __fmul_rn(__fmul_rn(__int2float_rn((int)acc0 + cst.x), __int_as_float(cst.y)), ts);
+        f1 = __fmul_rn(__fmul_rn(__int2float_rn((int)acc1 + cst.z), __int_as_float(cst.w)), ts);
       };
       // cos/sin rows of this token (issued before the MM2 wait; consumed after the nope slice)
       uint4 cs[8], sn[8];
@@ -270,7 +273,11 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
         for (int j = 0; j < 4; ++j) {
           uint32_t w[4];
 #pragma unroll
-          for (int u = 0; u < 4; ++u) w[u] = Act<T>::pack(deq(r[8 * j + 2 * u], c0 + 8 * j + 2 * u), deq(r[8 * j + 2 * u + 1], c0 + 8 * j + 2 * u + 1));
+          for (int u = 0; u < 4; ++u) {
+            float f0, f1;
+            deq2(r[8 * j + 2 * u], r[8 * j + 2 * u + 1], c0 + 8 * j + 2 * u, f0, f1);
+            w[u] = Act<T>::pack(f0, f1);
+          }
           ptx::st_shared_v4(tile + ptx::sw128_offset(row, ((c0 & 63) >> 3) + j), w[0], w[1], w[2], w[3]);
         }
       };
@@ -297,13 +304,21 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
         ptx::tc_fence_before();
         ptx::mbar_arrive(ptx::smem_u32(qn_ready + m));
 #pragma unroll
-        for (int j = 0; j < 32; ++j) x[j] = Act<T>::round(deq(ra[j], 128 + j));
+        for (int j = 0; j < 32; j += 2) {
+          deq2(ra[j], ra[j + 1], 128 + j, x[j], x[j + 1]);
+          x[j] = Act<T>::round(x[j]);
+          x[j + 1] = Act<T>::round(x[j + 1]);
+        }
         ptx::tmem_ld_wait();
         // acc2[m] fully read: the absorb buffer that overlaps the rope columns is free too
         ptx::tc_fence_before();
         ptx::mbar_arrive(ptx::smem_u32(rope_done + m));
 #pragma unroll
-        for (int j = 0; j < 32; ++j) x[32 + j] = Act<T>::round(deq(rb[j], 160 + j));
+        for (int j = 0; j < 32; j += 2) {
+          deq2(rb[j], rb[j + 1], 160 + j, x[32 + j], x[33 + j]);
+          x[32 + j] = Act<T>::round(x[32 + j]);
+          x[33 + j] = Act<T>::round(x[33 + j]);
+        }
       }
 
       stage_acquire();
@@ -674,10 +689,13 @@ q_stream_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant
         for (int j = 0; j < 8; ++j) { cs[j] = ptx::ld_global_nc_v4(cp + j); sn[j] = ptx::ld_global_nc_v4(sp + j); }
       }
       ptx::named_bar_sync(3, 256);  // constants visible to both groups
-      auto deq = [&](uint32_t acc, int c) -> float {
-        const int2 cst = s_cst[c];
-        return per_token ? __fmul_rn(__fmul_rn(__int2float_rn((int)acc), __int_as_float(cst.y)), ts)
-                         : __fmul_rn(__int2float_rn((int)acc + cst.x), __int_as_float(cst.y));
+      // y = fp32(acc + bias) * descale * token scale for columns c, c+1 (c even): the per-tensor mode carries a token scale of 1
+      // (x * 1.0f is exact), the per-token mode a bias of 0, so one expression serves both; one 16-byte load brings both columns'
+      // constants
+      auto deq2 = [&](uint32_t acc0, uint32_t acc1, int c, float& f0, float& f1) {
+        const int4 cst = *reinterpret_cast<const int4*>(s_cst + c);
+        f0 = __fmul_rn(__fmul_rn(__int2float_rn((int)acc0 + cst.x), __int_as_float(cst.y)), ts);
+        f1 = __fmul_rn(__fmul_rn(__int2float_rn((int)acc1 + cst.z), __int_as_float(cst.w)), ts);
       };
 
       ptx::mbar_wait(ptx::smem_u32(mm2_done), it & 1);
@@ -694,9 +712,17 @@ q_stream_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant
         ptx::tmem_ld_32x32b_x32(acc2 + 160, rb);
         ptx::tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 32; ++j) x[j] = Act<T>::round(deq(ra[j], 128 + j));
+        for (int j = 0; j < 32; j += 2) {
+          deq2(ra[j], ra[j + 1], 128 + j, x[j], x[j + 1]);
+          x[j] = Act<T>::round(x[j]);
+          x[j + 1] = Act<T>::round(x[j + 1]);
+        }
 #pragma unroll
-        for (int j = 0; j < 32; ++j) x[32 + j] = Act<T>::round(deq(rb[j], 160 + j));
+        for (int j = 0; j < 32; j += 2) {
+          deq2(rb[j], rb[j + 1], 160 + j, x[32 + j], x[33 + j]);
+          x[32 + j] = Act<T>::round(x[32 + j]);
+          x[33 + j] = Act<T>::round(x[33 + j]);
+        }
       }
       stage_acquire();
 #pragma unroll
@@ -733,7 +759,11 @@ q_stream_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant
       {
         auto nope_chunk = [&](const uint32_t (&r)[32], int c0) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) wn[(c0 >> 1) + j] = Act<T>::pack(deq(r[2 * j], c0 + 2 * j), deq(r[2 * j + 1], c0 + 2 * j + 1));
+          for (int j = 0; j < 16; ++j) {
+            float f0, f1;
+            deq2(r[2 * j], r[2 * j + 1], c0 + 2 * j, f0, f1);
+            wn[(c0 >> 1) + j] = Act<T>::pack(f0, f1);
+          }
         };
         uint32_t ra[32], rb[32];
         ptx::tmem_ld_32x32b_x32(acc2 + 0, ra);
