@@ -145,6 +145,27 @@ int batch_matmul_transpose_launch(const void* a, const void* b, void* c, int64_t
                                   int32_t act_dtype, int32_t b_format, void* stream);
 
 /*
+ * Slot producers: the ops that create and book-keep the slot_mapping this operator scatters by.  Integer work,
+ * bit-exact against the reference tests' goldens; asynchronous on `stream`, device pointers, no scratch memory.
+ *  - mlapo_alloc_extend: paged allocation of the new tokens of `batch` requests.  Replaces sglang::npu_kernel::alloc_extend
+ *    (schema csrc/pytorch_extensions.cpp:31-33; golden tests/python/sgl_kernel_npu/test_alloc_extend_slot.py:9-85).
+ *    pre_lens/seq_lens/last_loc/free_pages int32 or int64 (lens_are_int64), out_indices [sum(seq - pre)] int32 or int64,
+ *    values[0] <- number of pages taken (may be null); out_capacity = elements out_indices can hold.
+ *  - mlapo_cache_loc_assign: token_pool[req[i], start_i : end_i] <- cache_loc[packed run i] (update = 0, reference
+ *    cache_loc_assign) or the reverse copy (update = 1, cache_loc_update); csrc/cache_location_assign/op_host/cache_loc_assign.cpp:88-114.
+ *    req int32|int64, token_pool int32 [pool, row_size], start/end int64, cache_loc int32.
+ *  - mlapo_assign_cache: out[i, dst_start_i : dst_end_i] <- src[src_start_i : src_end_i], any element size 1..8 bytes, index
+ *    tensors int32 or int64; csrc/assign_cache_op/op_host/assign_cache.cpp:40-82.
+ */
+int mlapo_alloc_extend(const void* pre_lens, const void* seq_lens, const void* last_loc, const void* free_pages, int64_t page_size,
+                       void* out_indices, void* values, int32_t batch, int64_t out_capacity, int32_t lens_are_int64,
+                       int32_t out_is_int64, void* stream);
+int mlapo_cache_loc_assign(const void* req_indices, int32_t req_is_int64, void* token_pool, const void* start_offset, const void* end_offset,
+                           void* cache_loc, int32_t batch, int64_t row_size, int32_t update, void* stream);
+int mlapo_assign_cache(void* out, const void* src, const void* dst_start, const void* dst_end, const void* src_start, const void* src_end,
+                       int32_t batch, int64_t row_elems, int32_t elem_bytes, int32_t idx_is_int64, void* stream);
+
+/*
  * Format tools.  The reference has them only as test helpers; they are exported so that Ascend-format
  * checkpoints and caches can be prepared and read on the device.  All asynchronous on `stream`, device pointers.
  *  - mlapo_transdata_nd_to_nz: ND [rows, cols] -> FRACTAL_NZ [1, ceil(cols/c0), ceil16(rows), c0], zero padded; int8 weights

@@ -40,6 +40,7 @@
 #include "mlapo_decode_persistent.cuh"
 #include "mlapo_format.cuh"
 #include "mlapo_bmt.cuh"
+#include "mlapo_slots.cuh"
 
 namespace mlapo {
 
@@ -563,6 +564,57 @@ int batch_matmul_transpose_launch(const void* a, const void* b, void* c, int64_t
   if (act_dtype == MLAPO_ACT_BF16) return bmt_launch_impl<__nv_bfloat16>(a, b, c, m, batch, k, n, b_format == MLAPO_FORMAT_NZ, st);
   if (act_dtype == MLAPO_ACT_FP16) return bmt_launch_impl<__half>(a, b, c, m, batch, k, n, b_format == MLAPO_FORMAT_NZ, st);
   return fail(MLAPO_ERR_INVALID_ARG, "batch_matmul_transpose: tensors must be fp16 or bf16");
+}
+
+int mlapo_alloc_extend(const void* pre_lens, const void* seq_lens, const void* last_loc, const void* free_pages, int64_t page_size,
+                       void* out_indices, void* values, int32_t batch, int64_t out_capacity, int32_t lens_are_int64,
+                       int32_t out_is_int64, void* stream) {
+  if (!pre_lens || !seq_lens || !last_loc || !free_pages || !out_indices) return fail(MLAPO_ERR_INVALID_ARG, "alloc_extend: null pointer");
+  if (batch <= 0 || page_size <= 0 || out_capacity < 0) return fail(MLAPO_ERR_INVALID_ARG, "alloc_extend: batch=%d page_size=%lld", batch, (long long)page_size);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define MLAPO_AE(I, O)                                                                                                        \
+  alloc_extend_kernel<I, O><<<batch, 256, 0, st>>>(reinterpret_cast<const I*>(pre_lens), reinterpret_cast<const I*>(seq_lens), \
+                                                   reinterpret_cast<const I*>(last_loc), reinterpret_cast<const I*>(free_pages), \
+                                                   page_size, reinterpret_cast<O*>(out_indices), reinterpret_cast<I*>(values), batch, out_capacity)
+  if (lens_are_int64) { if (out_is_int64) MLAPO_AE(long long, long long); else MLAPO_AE(long long, int); }
+  else { if (out_is_int64) MLAPO_AE(int, long long); else MLAPO_AE(int, int); }
+#undef MLAPO_AE
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "alloc_extend launch: %s", cudaGetErrorString(e));
+}
+
+int mlapo_cache_loc_assign(const void* req_indices, int32_t req_is_int64, void* token_pool, const void* start_offset, const void* end_offset,
+                           void* cache_loc, int32_t batch, int64_t row_size, int32_t update, void* stream) {
+  if (!req_indices || !token_pool || !start_offset || !end_offset || !cache_loc) return fail(MLAPO_ERR_INVALID_ARG, "cache_loc_assign: null pointer");
+  if (batch <= 0 || row_size <= 0) return fail(MLAPO_ERR_INVALID_ARG, "cache_loc_assign: batch=%d row_size=%lld", batch, (long long)row_size);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (req_is_int64)
+    cache_loc_kernel<long long><<<batch, 128, 0, st>>>(reinterpret_cast<const long long*>(req_indices), reinterpret_cast<int32_t*>(token_pool),
+                                                       reinterpret_cast<const long long*>(start_offset), reinterpret_cast<const long long*>(end_offset),
+                                                       reinterpret_cast<int32_t*>(cache_loc), row_size, update);
+  else
+    cache_loc_kernel<int><<<batch, 128, 0, st>>>(reinterpret_cast<const int*>(req_indices), reinterpret_cast<int32_t*>(token_pool),
+                                                 reinterpret_cast<const long long*>(start_offset), reinterpret_cast<const long long*>(end_offset),
+                                                 reinterpret_cast<int32_t*>(cache_loc), row_size, update);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "cache_loc_assign launch: %s", cudaGetErrorString(e));
+}
+
+int mlapo_assign_cache(void* out, const void* src, const void* dst_start, const void* dst_end, const void* src_start, const void* src_end,
+                       int32_t batch, int64_t row_elems, int32_t elem_bytes, int32_t idx_is_int64, void* stream) {
+  if (!out || !src || !dst_start || !dst_end || !src_start || !src_end) return fail(MLAPO_ERR_INVALID_ARG, "assign_cache: null pointer");
+  if (batch <= 0 || row_elems <= 0 || elem_bytes <= 0 || elem_bytes > 8) return fail(MLAPO_ERR_INVALID_ARG, "assign_cache: batch=%d row=%lld elem_bytes=%d", batch, (long long)row_elems, elem_bytes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (idx_is_int64)
+    assign_cache_kernel<long long><<<batch, 256, 0, st>>>(reinterpret_cast<uint8_t*>(out), reinterpret_cast<const uint8_t*>(src),
+        reinterpret_cast<const long long*>(dst_start), reinterpret_cast<const long long*>(dst_end), reinterpret_cast<const long long*>(src_start),
+        reinterpret_cast<const long long*>(src_end), row_elems, elem_bytes);
+  else
+    assign_cache_kernel<int><<<batch, 256, 0, st>>>(reinterpret_cast<uint8_t*>(out), reinterpret_cast<const uint8_t*>(src),
+        reinterpret_cast<const int*>(dst_start), reinterpret_cast<const int*>(dst_end), reinterpret_cast<const int*>(src_start),
+        reinterpret_cast<const int*>(src_end), row_elems, elem_bytes);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "assign_cache launch: %s", cudaGetErrorString(e));
 }
 
 static unsigned grid_for(long long work) {

@@ -271,6 +271,76 @@ void batch_matmul_transpose(const at::Tensor& tensor_a, const at::Tensor& tensor
              "batch_matmul_transpose_launch");
 }
 
+// ---- slot producers (csrc/pytorch_extensions.cpp:31-45): same schemas, CUDA tensors
+static int is_i64(const at::Tensor& t, const char* name) {
+  TORCH_CHECK(t.scalar_type() == at::kInt || t.scalar_type() == at::kLong, name, " must be int32 or int64");
+  return t.scalar_type() == at::kLong ? 1 : 0;
+}
+static void need_cuda_contig(const at::Tensor& t, const char* name) {
+  TORCH_CHECK(t.is_cuda() && t.is_contiguous(), name, " must be a contiguous CUDA tensor");
+}
+
+void alloc_extend(const at::Tensor& pre_lens, const at::Tensor& seq_lens, const at::Tensor& last_loc, const at::Tensor& free_pages,
+                  int64_t page_size, at::Tensor& out_indices, at::Tensor& values) {
+  for (const at::Tensor* t : {&pre_lens, &seq_lens, &last_loc, &free_pages, (const at::Tensor*)&out_indices, (const at::Tensor*)&values})
+    need_cuda_contig(*t, "alloc_extend tensor");
+  const int i64 = is_i64(pre_lens, "pre_lens");
+  TORCH_CHECK(seq_lens.scalar_type() == pre_lens.scalar_type() && last_loc.scalar_type() == pre_lens.scalar_type() &&
+                  free_pages.scalar_type() == pre_lens.scalar_type() && values.scalar_type() == pre_lens.scalar_type(),
+              "pre_lens, seq_lens, last_loc, free_pages and values must share one integer dtype");
+  if (pre_lens.numel() == 0) return;
+  const c10::cuda::CUDAGuard guard(pre_lens.device());
+  check_cabi(mlapo_alloc_extend(pre_lens.data_ptr(), seq_lens.data_ptr(), last_loc.data_ptr(), free_pages.data_ptr(), page_size,
+                                out_indices.data_ptr(), values.data_ptr(), (int32_t)pre_lens.numel(), out_indices.numel(), i64,
+                                is_i64(out_indices, "out_indices"), at::cuda::getCurrentCUDAStream()),
+             "mlapo_alloc_extend");
+}
+
+static void cache_loc_common(const at::Tensor& req, const at::Tensor& token_pool, const at::Tensor& start, const at::Tensor& end,
+                             const at::Tensor& cache_loc, int update) {
+  // csrc/cache_location_assign/op_host/cache_loc_assign.cpp:73-86
+  TORCH_CHECK((req.scalar_type() == at::kInt || req.scalar_type() == at::kLong) && token_pool.scalar_type() == at::kInt &&
+                  start.scalar_type() == at::kLong && end.scalar_type() == at::kLong && cache_loc.scalar_type() == at::kInt,
+              "Only support inputTensor combo1: int64, int32, int64, int64, int32; combo2: int32, int32, int64, int64, int32");
+  for (const at::Tensor* t : {&req, &token_pool, &start, &end, &cache_loc}) need_cuda_contig(*t, "cache_loc tensor");
+  TORCH_CHECK(token_pool.dim() == 2, "token_pool must be [pool, row]");
+  if (req.numel() == 0) return;
+  const c10::cuda::CUDAGuard guard(token_pool.device());
+  check_cabi(mlapo_cache_loc_assign(req.data_ptr(), req.scalar_type() == at::kLong, token_pool.data_ptr(), start.data_ptr(), end.data_ptr(),
+                                    cache_loc.data_ptr(), (int32_t)req.numel(), token_pool.size(1), update, at::cuda::getCurrentCUDAStream()),
+             "mlapo_cache_loc_assign");
+}
+at::Tensor cache_loc_assign(const at::Tensor& req, const at::Tensor& token_pool, const at::Tensor& start, const at::Tensor& end,
+                            const at::Tensor& cache_loc) {
+  cache_loc_common(req, token_pool, start, end, cache_loc, 0);
+  return token_pool;
+}
+at::Tensor cache_loc_update(const at::Tensor& req, const at::Tensor& token_pool, const at::Tensor& start, const at::Tensor& end,
+                            const at::Tensor& cache_loc) {
+  cache_loc_common(req, token_pool, start, end, cache_loc, 1);
+  return cache_loc;
+}
+
+bool assign_cache_op(at::Tensor& out, const at::Tensor& src, const at::Tensor& dst_start, const at::Tensor& dst_end,
+                     const at::Tensor& src_start, const at::Tensor& src_end) {
+  // csrc/assign_cache_op/op_host/assign_cache.cpp:40-82: malformed arguments return false instead of throwing
+  const at::Tensor* idx[4] = {&dst_start, &dst_end, &src_start, &src_end};
+  if (out.dim() < 2 || src.dim() < 1 || out.scalar_type() != src.scalar_type()) return false;
+  for (auto* t : idx)
+    if (t->dim() < 1 || t->size(0) != out.size(0) || t->scalar_type() != dst_start.scalar_type()) return false;
+  if (dst_start.scalar_type() != at::kInt && dst_start.scalar_type() != at::kLong) return false;
+  need_cuda_contig(out, "out");
+  need_cuda_contig(src, "src");
+  for (auto* t : idx) need_cuda_contig(*t, "index tensor");
+  if (out.size(0) == 0) return true;
+  const c10::cuda::CUDAGuard guard(out.device());
+  check_cabi(mlapo_assign_cache(out.data_ptr(), src.data_ptr(), dst_start.data_ptr(), dst_end.data_ptr(), src_start.data_ptr(), src_end.data_ptr(),
+                                (int32_t)out.size(0), out.stride(0), (int32_t)out.element_size(), dst_start.scalar_type() == at::kLong,
+                                at::cuda::getCurrentCUDAStream()),
+             "mlapo_assign_cache");
+  return true;
+}
+
 std::string sgl_kernel_npu_version() { return std::string(mlapo_version()); }
 void sgl_kernel_npu_print_version() { std::printf("%s\n", mlapo_version()); }
 
@@ -296,6 +366,19 @@ TORCH_LIBRARY_FRAGMENT(npu, m) {
   m.def(  // csrc/pytorch_extensions.cpp:117-119, verbatim
       "batch_matmul_transpose(Tensor tensor_a, Tensor tensor_b, Tensor(a!) tensor_c, "
       "str? format_mode=None, str? quant_mode=None) -> ()");
+  // csrc/pytorch_extensions.cpp:31-45, verbatim
+  m.def(
+      "alloc_extend(Tensor pre_lens, Tensor seq_lens, Tensor last_loc, Tensor free_pages, int page_size, "
+      "Tensor(a!) out_indices, Tensor(b!) values) -> ()");
+  m.def(
+      "cache_loc_assign(Tensor req_indices, Tensor token_pool, Tensor start_offset, Tensor end_offset, Tensor "
+      "out_cache_loc) -> Tensor");
+  m.def(
+      "cache_loc_update(Tensor req_indices, Tensor token_pool, Tensor start_offset, Tensor end_offset, Tensor "
+      "out_cache_loc) -> Tensor");
+  m.def(
+      "assign_cache_op(Tensor! out, Tensor src, Tensor dst_start_idx, Tensor dst_end_idx, Tensor src_start_idx, "
+      "Tensor src_end_idx) -> bool");
 }
 
 // csrc/pytorch_extensions.cpp:205, 268 register under PrivateUse1 (the NPU); here the device is CUDA.
@@ -303,4 +386,8 @@ TORCH_LIBRARY_IMPL(npu, CUDA, m) {
   m.impl("mla_preprocess", TORCH_FN(sglang::npu_kernel::mla_preprocess));
   m.impl("mla_preprocess_repack_weight", TORCH_FN(sglang::npu_kernel::mla_preprocess_repack_weight));
   m.impl("batch_matmul_transpose", TORCH_FN(sglang::npu_kernel::batch_matmul_transpose));
+  m.impl("alloc_extend", TORCH_FN(sglang::npu_kernel::alloc_extend));
+  m.impl("cache_loc_assign", TORCH_FN(sglang::npu_kernel::cache_loc_assign));
+  m.impl("cache_loc_update", TORCH_FN(sglang::npu_kernel::cache_loc_update));
+  m.impl("assign_cache_op", TORCH_FN(sglang::npu_kernel::assign_cache_op));
 }

@@ -57,6 +57,10 @@ def _load():
                                                ctypes.c_int32, ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p]
     lib.batch_matmul_transpose_launch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64,
                                                   ctypes.c_int64, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+    V, I32, I64 = ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64
+    lib.mlapo_alloc_extend.argtypes = [V, V, V, V, I64, V, V, I32, I64, I32, I32, V]
+    lib.mlapo_cache_loc_assign.argtypes = [V, I32, V, V, V, V, I32, I64, I32, V]
+    lib.mlapo_assign_cache.argtypes = [V, V, V, V, V, V, I32, I64, I32, I32, V]
     lib.mla_preprocess_launch.argtypes = [ctypes.POINTER(MlapoParams), ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
     lib.mla_preprocess_launch_static.argtypes = [ctypes.POINTER(MlapoParams), ctypes.c_void_p]
     lib.mlapo_launches_per_call.argtypes = [ctypes.POINTER(MlapoParams)]
@@ -341,3 +345,75 @@ def mla_preprocess(hiddenState, gamma0, beta0, wdqkv_km, descale0, gamma1, beta1
             workspace = torch.empty(max(workspace_layout(p).total_bytes, 256), dtype=torch.uint8, device=hiddenState.device)
         launch(p, workspace)
     return q_out0, kv_cache_out0, q_out1, kv_cache_out1
+
+
+# ------------------------------------------------------------------------------------------------ slot producers
+def _is_i64(t, what):
+    if t.dtype not in (torch.int32, torch.int64):
+        raise RuntimeError(f"{what} must be int32 or int64")
+    return 1 if t.dtype == torch.int64 else 0
+
+
+def alloc_extend(pre_lens, seq_lens, last_loc, free_pages, page_size, out_indices, values) -> None:
+    """Same arguments as torch.ops.npu.alloc_extend (csrc/pytorch_extensions.cpp:31-33): writes the slots of the new tokens
+    of every request into out_indices (packed in request order) and the number of pages taken into values[0]."""
+    for t, nm in ((pre_lens, "pre_lens"), (seq_lens, "seq_lens"), (last_loc, "last_loc"), (free_pages, "free_pages"),
+                  (out_indices, "out_indices"), (values, "values")):
+        _need_cuda(t, nm)
+    i64 = _is_i64(pre_lens, "pre_lens")
+    if not (seq_lens.dtype == last_loc.dtype == free_pages.dtype == values.dtype == pre_lens.dtype):
+        raise RuntimeError("pre_lens, seq_lens, last_loc, free_pages and values must share one integer dtype")
+    if pre_lens.numel() == 0:
+        return
+    with torch.cuda.device(pre_lens.device):
+        _check(lib.mlapo_alloc_extend(pre_lens.data_ptr(), seq_lens.data_ptr(), last_loc.data_ptr(), free_pages.data_ptr(), int(page_size),
+                                      out_indices.data_ptr(), values.data_ptr(), pre_lens.numel(), out_indices.numel(), i64,
+                                      _is_i64(out_indices, "out_indices"), _stream_ptr(pre_lens)), "mlapo_alloc_extend")
+
+
+def _cache_loc(req_indices, token_pool, start_offset, end_offset, out_cache_loc, update):
+    ok = (req_indices.dtype in (torch.int32, torch.int64) and token_pool.dtype == torch.int32 and start_offset.dtype == torch.int64
+          and end_offset.dtype == torch.int64 and out_cache_loc.dtype == torch.int32)
+    if not ok:  # csrc/cache_location_assign/op_host/cache_loc_assign.cpp:73-86
+        raise RuntimeError("Only support inputTensor combo1: int64, int32, int64, int64, int32; combo2: int32, int32, int64, int64, int32")
+    for t, nm in ((req_indices, "req_indices"), (token_pool, "token_pool"), (start_offset, "start_offset"), (end_offset, "end_offset"),
+                  (out_cache_loc, "out_cache_loc")):
+        _need_cuda(t, nm)
+    if req_indices.numel():
+        with torch.cuda.device(token_pool.device):
+            _check(lib.mlapo_cache_loc_assign(req_indices.data_ptr(), _is_i64(req_indices, "req_indices"), token_pool.data_ptr(),
+                                              start_offset.data_ptr(), end_offset.data_ptr(), out_cache_loc.data_ptr(), req_indices.numel(),
+                                              token_pool.shape[1], update, _stream_ptr(token_pool)), "mlapo_cache_loc_assign")
+
+
+def cache_loc_assign(req_indices, token_pool, start_offset, end_offset, out_cache_loc):
+    """token_pool[req[i], start_i:end_i] = out_cache_loc[packed run i]; returns token_pool (cache_loc_assign.cpp:88-100)."""
+    _cache_loc(req_indices, token_pool, start_offset, end_offset, out_cache_loc, 0)
+    return token_pool
+
+
+def cache_loc_update(req_indices, token_pool, start_offset, end_offset, out_cache_loc):
+    """out_cache_loc[packed run i] = token_pool[req[i], start_i:end_i]; returns out_cache_loc (cache_loc_assign.cpp:102-114)."""
+    _cache_loc(req_indices, token_pool, start_offset, end_offset, out_cache_loc, 1)
+    return out_cache_loc
+
+
+def assign_cache_op(out, src, dst_start_idx, dst_end_idx, src_start_idx, src_end_idx) -> bool:
+    """out[i, dst_start_i:dst_end_i] = src[src_start_i:src_end_i] (assign_cache.cpp:40-82); False on malformed arguments, as
+    the reference."""
+    idx = (dst_start_idx, dst_end_idx, src_start_idx, src_end_idx)
+    if out.dim() < 2 or src.dim() < 1 or any(t.dim() < 1 for t in idx):
+        return False
+    if any(t.shape[0] != out.shape[0] for t in idx) or out.dtype != src.dtype:
+        return False
+    if any(t.dtype != idx[0].dtype for t in idx) or idx[0].dtype not in (torch.int32, torch.int64):
+        return False
+    for t, nm in ((out, "out"), (src, "src")) + tuple((t, "index tensor") for t in idx):
+        _need_cuda(t, nm)
+    if out.shape[0] == 0:
+        return True
+    with torch.cuda.device(out.device):
+        _check(lib.mlapo_assign_cache(out.data_ptr(), src.data_ptr(), idx[0].data_ptr(), idx[1].data_ptr(), idx[2].data_ptr(), idx[3].data_ptr(),
+                                      out.shape[0], out.stride(0), out.element_size(), _is_i64(idx[0], "index"), _stream_ptr(out)),
+               "mlapo_assign_cache")
+    return True
