@@ -145,6 +145,18 @@ int batch_matmul_transpose_launch(const void* a, const void* b, void* c, int64_t
                                   int32_t act_dtype, int32_t b_format, void* stream);
 
 /*
+ * split_qkv_rmsnorm_rope: split a fused qkv row [q_hidden | kv_hidden | kv_hidden], RMSNorm every q and k head
+ * (weight, optional bias; skipped when has_norm = 0), rotate the first rope_dim dims (neox_style 1: halves, 0: interleaved pairs),
+ * copy v.  Replaces the Triton kernel behind sgl_kernel_npu.norm.split_qkv_rmsnorm_rope.split_qkv_rmsnorm_rope
+ * (python/sgl_kernel_npu/sgl_kernel_npu/norm/split_qkv_rmsnorm_rope.py:374-439).  fp32 math, one rounding at the store.
+ * qkv act [batch, q_hidden + 2 kv_hidden], sin/cos act [batch, rope_dim], weights/biases act [head_dim]; head_dim a power of two.
+ */
+int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* cos, void* q_out, void* k_out, void* v_out,
+                                  const void* q_weight, const void* k_weight, const void* q_bias, const void* k_bias, int64_t batch,
+                                  int32_t q_hidden, int32_t kv_hidden, int32_t head_dim, int32_t rope_dim, float eps, int32_t has_norm,
+                                  int32_t neox_style, int32_t act_dtype, void* stream);
+
+/*
  * Slot producers: the ops that create and book-keep the slot_mapping this operator scatters by.  Integer work,
  * bit-exact against the reference tests' goldens; asynchronous on `stream`, device pointers, no scratch memory.
  *  - mlapo_alloc_extend: paged allocation of the new tokens of `batch` requests.  Replaces sglang::npu_kernel::alloc_extend

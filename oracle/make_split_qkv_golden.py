@@ -1,0 +1,58 @@
+"""Writes tests/golden/split_qkv_golden.npz with the reference TEST's own golden helpers rms_norm / custom_rope
+(tests/python/sgl_kernel_npu/test_split_qkv_rmsnorm_rope.py:11-44), imported from /root/reference with the NPU modules stubbed,
+applied the way that test applies them (:101-120), on a scaled-down copy of its two cases (rope_dim = head_dim and head_dim / 2).
+Inputs are stored as bf16 bit patterns, the golden q / k as float32 (the helpers compute in float32 and do not round)."""
+import importlib.util
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+REF = "/root/reference/tests/python/sgl_kernel_npu/test_split_qkv_rmsnorm_rope.py"
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden", "split_qkv_golden.npz")
+
+
+def load():
+    for m in ("torch_npu", "sgl_kernel_npu", "sgl_kernel_npu.norm"):
+        sys.modules.setdefault(m, types.ModuleType(m))
+    stub = types.ModuleType("sgl_kernel_npu.norm.split_qkv_rmsnorm_rope")
+    stub.split_qkv_rmsnorm_rope = stub.split_qkvgate_gemma_rmsnorm_rope = None
+    sys.modules["sgl_kernel_npu.norm.split_qkv_rmsnorm_rope"] = stub
+    spec = importlib.util.spec_from_file_location("ref_test_split_qkv", REF)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def bits(t):
+    return t.contiguous().view(torch.int16).numpy().view(np.uint16)
+
+
+def main():
+    ref = load()
+    qh, kvh, hd, bsz, eps = 1024, 256, 128, 6, 1e-6
+    rec = {"meta": np.array([qh, kvh, hd, bsz])}
+    for ci, rope_dim in enumerate((128, 64)):
+        g = torch.Generator().manual_seed(100 + ci)
+        bf = lambda *s: torch.randn(*s, generator=g).to(torch.bfloat16)
+        qkv, qw, kw, qb, kb = bf(bsz, qh + 2 * kvh), bf(hd), bf(hd), bf(hd), bf(hd)
+        sin = torch.rand(bsz, 1, 1, rope_dim, generator=g).to(torch.bfloat16)
+        cos = torch.rand(bsz, 1, 1, rope_dim, generator=g).to(torch.bfloat16)
+        _q, _k, _v = qkv.split([qh, kvh, kvh], dim=-1)
+        nq = ref.rms_norm(_q.reshape(-1, hd), qw, qb, eps).reshape(bsz, 1, -1, hd)
+        nk = ref.rms_norm(_k.reshape(-1, hd), kw, kb, eps).reshape(bsz, 1, -1, hd)
+        rq, rk = ref.custom_rope(nq[..., :rope_dim], nk[..., :rope_dim], sin, cos, half_rope_dim=rope_dim // 2)
+        cq = np.concatenate((rq, nq[..., rope_dim:]), axis=-1).reshape(bsz, -1)
+        ck = np.concatenate((rk, nk[..., rope_dim:]), axis=-1).reshape(bsz, -1)
+        for name, t in (("qkv", qkv), ("qw", qw), ("kw", kw), ("qb", qb), ("kb", kb), ("sin", sin), ("cos", cos)):
+            rec[f"c{ci}_{name}"] = bits(t)
+        rec[f"c{ci}_q"], rec[f"c{ci}_k"] = cq.astype(np.float32), ck.astype(np.float32)
+        rec[f"c{ci}_rope_dim"] = np.array(rope_dim)
+    np.savez_compressed(OUT, **rec)
+    print("wrote", OUT, os.path.getsize(OUT), "bytes")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,43 @@
+"""CPU oracle for split_qkv_rmsnorm_rope.  TEST INFRASTRUCTURE ONLY — imported by tests/ and nothing else.
+
+numpy restatement of the contract of the reference's Triton kernel (python/sgl_kernel_npu/sgl_kernel_npu/norm/
+split_qkv_rmsnorm_rope.py:9-372): fp32 throughout, one rounding to the tensor dtype at the store.  Pinned by
+tests/test_split_qkv.py against fixtures produced with the reference TEST's own golden helpers rms_norm / custom_rope
+(tests/python/sgl_kernel_npu/test_split_qkv_rmsnorm_rope.py:11-44, script oracle/make_split_qkv_golden.py)."""
+import numpy as np
+import torch
+
+
+def split_qkv_rmsnorm_rope(qkv, sin, cos, q_hidden, kv_hidden, head_dim, eps=None, q_weight=None, k_weight=None, q_bias=None,
+                           k_bias=None, is_neox_style=True):
+    dt = qkv.dtype
+    f = lambda t: None if t is None else t.to(torch.float32).numpy().astype(np.float32)
+    x = f(qkv)
+    b = x.shape[0]
+    rd = sin.shape[-1]
+    s, c = f(sin).reshape(b, 1, rd), f(cos).reshape(b, 1, rd)
+    h = rd // 2
+
+    def one(part, w, bias):
+        n = part.reshape(b, -1, head_dim)
+        if eps is not None:
+            rstd = np.float32(1) / np.sqrt(np.mean(n * n, axis=-1, keepdims=True, dtype=np.float32) + np.float32(eps), dtype=np.float32)
+            n = n * rstd * f(w)
+            if bias is not None:
+                n = n + f(bias)
+        rot = n[..., :rd]
+        if is_neox_style:
+            cat = np.concatenate((-rot[..., h:], rot[..., :h]), axis=-1)
+            ss, cc = s, c
+        else:
+            cat = np.empty_like(rot)
+            cat[..., 0::2] = -rot[..., 1::2]
+            cat[..., 1::2] = rot[..., 0::2]
+            ss, cc = np.repeat(s[..., :h], 2, axis=-1), np.repeat(c[..., :h], 2, axis=-1)
+        out = np.concatenate((cat * ss + rot * cc, n[..., rd:]), axis=-1).astype(np.float32)
+        return torch.from_numpy(out.reshape(b, -1)).to(dt)
+
+    q = one(x[:, :q_hidden], q_weight, q_bias)
+    k = one(x[:, q_hidden:q_hidden + kv_hidden], k_weight, k_bias)
+    v = qkv[:, q_hidden + kv_hidden:].clone()
+    return q, k, v

@@ -41,6 +41,7 @@
 #include "mlapo_format.cuh"
 #include "mlapo_bmt.cuh"
 #include "mlapo_slots.cuh"
+#include "mlapo_split_qkv.cuh"
 
 namespace mlapo {
 
@@ -615,6 +616,30 @@ int mlapo_assign_cache(void* out, const void* src, const void* dst_start, const 
         reinterpret_cast<const int*>(src_end), row_elems, elem_bytes);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "assign_cache launch: %s", cudaGetErrorString(e));
+}
+
+int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* cos, void* q_out, void* k_out, void* v_out,
+                                  const void* q_weight, const void* k_weight, const void* q_bias, const void* k_bias, int64_t batch,
+                                  int32_t q_hidden, int32_t kv_hidden, int32_t head_dim, int32_t rope_dim, float eps, int32_t has_norm,
+                                  int32_t neox_style, int32_t act_dtype, void* stream) {
+  if (!qkv || !sin || !cos || !q_out || !k_out || !v_out) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: null pointer");
+  if (has_norm && (!q_weight || !k_weight)) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: eps given but no norm weights");
+  if ((q_bias == nullptr) != (k_bias == nullptr)) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: q_bias and k_bias go together");
+  if (batch <= 0 || head_dim <= 0 || head_dim > kSplitMaxHeadDim || (head_dim & (head_dim - 1)) || q_hidden % head_dim || kv_hidden % head_dim ||
+      kv_hidden <= 0 || q_hidden % kv_hidden || rope_dim <= 0 || rope_dim > head_dim || (rope_dim & 1))
+    return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: batch=%lld q_hidden=%d kv_hidden=%d head_dim=%d (power of two <= %d) rope_dim=%d",
+                (long long)batch, q_hidden, kv_hidden, head_dim, kSplitMaxHeadDim, rope_dim);
+  SplitQkvArgs a{qkv, sin, cos, q_out, k_out, v_out, q_weight, k_weight, q_bias, k_bias, batch, q_hidden, kv_hidden, head_dim, rope_dim, eps,
+                 has_norm, neox_style};
+  const long long items = batch * ((q_hidden + 2LL * kv_hidden) / head_dim);
+  long long blocks = (items + kSplitWarps - 1) / kSplitWarps;
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (act_dtype == MLAPO_ACT_BF16) split_qkv_rmsnorm_rope_kernel<__nv_bfloat16><<<(unsigned)blocks, kSplitWarps * 32, 0, st>>>(a);
+  else if (act_dtype == MLAPO_ACT_FP16) split_qkv_rmsnorm_rope_kernel<__half><<<(unsigned)blocks, kSplitWarps * 32, 0, st>>>(a);
+  else return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: tensors must be fp16 or bf16");
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "split_qkv_rmsnorm_rope launch: %s", cudaGetErrorString(e));
 }
 
 static unsigned grid_for(long long work) {

@@ -1,0 +1,119 @@
+"""split_qkv_rmsnorm_rope.  CPU: the numpy oracle against fixtures made with the reference test's own golden
+helpers (oracle/make_split_qkv_golden.py).  GPU: the CUDA kernel, called through the reference's module path
+sgl_kernel_npu.norm.split_qkv_rmsnorm_rope (ctypes over the C ABI), against the fixtures and against the oracle.
+Tolerances: the reference test asserts atol 5e-2 (test_split_qkv_rmsnorm_rope.py:122-137); here additionally at most ONE bf16 /
+fp16 ulp from the fp32 result rounded once, and nearly all elements identical (the sum of squares is associated differently)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import split_qkv_oracle as sq
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "split_qkv_golden.npz")
+
+
+def bf(bits):
+    return torch.from_numpy(bits.view(np.int16).copy()).view(torch.bfloat16)
+
+
+def fixture(ci):
+    z = np.load(GOLD)
+    qh, kvh, hd, bsz = (int(v) for v in z["meta"])
+    t = {k: bf(z[f"c{ci}_{k}"]) for k in ("qkv", "qw", "kw", "qb", "kb", "sin", "cos")}
+    return qh, kvh, hd, bsz, int(z[f"c{ci}_rope_dim"]), t, z[f"c{ci}_q"], z[f"c{ci}_k"]
+
+
+def ordinal(t):
+    """16-bit float bit patterns mapped to integers that are monotone in the value, so that differences count ulps"""
+    b = t.contiguous().view(torch.int16).to(torch.int32)
+    return torch.where(b < 0, -(b & 0x7FFF), b)
+
+
+def close(got, want_f32):
+    """(fraction identical, worst ulp distance) of `got` against the float32 reference rounded once to got's dtype"""
+    want = torch.from_numpy(np.ascontiguousarray(want_f32)).to(got.dtype) if isinstance(want_f32, np.ndarray) else want_f32
+    d = (ordinal(got.cpu()) - ordinal(want.reshape(got.shape))).abs()
+    return float((d == 0).float().mean()), int(d.max())
+
+
+# ------------------------------------------------------------------------------------------------ oracle vs reference (CPU)
+@pytest.mark.parametrize("ci", [0, 1])
+def test_oracle_matches_reference_golden(ci):
+    qh, kvh, hd, bsz, rd, t, gq, gk = fixture(ci)
+    q, k, v = sq.split_qkv_rmsnorm_rope(t["qkv"], t["sin"].reshape(bsz, rd), t["cos"].reshape(bsz, rd), qh, kvh, hd, 1e-6,
+                                        t["qw"], t["kw"], t["qb"], t["kb"])
+    for got, want in ((q, gq), (k, gk)):
+        same, worst = close(got, want)
+        assert same >= 0.999 and worst <= 1, (same, worst)
+        np.testing.assert_allclose(got.float().numpy(), want, atol=5e-2)
+    assert torch.equal(v, t["qkv"][:, qh + kvh:])
+
+
+# ------------------------------------------------------------------------------------------------ CUDA
+@pytest.mark.gpu
+@pytest.mark.parametrize("ci", [0, 1])
+def test_cuda_vs_golden_fixture(ci, cuda_device):
+    from sgl_kernel_npu.norm.split_qkv_rmsnorm_rope import split_qkv_rmsnorm_rope
+    qh, kvh, hd, bsz, rd, t, gq, gk = fixture(ci)
+    d = {k: v.to(cuda_device) for k, v in t.items()}
+    q, k, v = split_qkv_rmsnorm_rope(d["qkv"], d["sin"], d["cos"], qh, kvh, hd, eps=1e-6, q_weight=d["qw"], k_weight=d["kw"],
+                                     q_bias=d["qb"], k_bias=d["kb"])
+    for got, want in ((q, gq), (k, gk)):
+        same, worst = close(got, want)
+        assert same >= 0.995 and worst <= 1, (same, worst)
+        np.testing.assert_allclose(got.float().cpu().numpy(), want, atol=5e-2)
+    assert torch.equal(v.cpu(), t["qkv"][:, qh + kvh:])
+
+
+# (batch, q_hidden, kv_hidden, head_dim, rope_dim, norm, bias, neox, dtype); the first two are the reference test's own shapes
+CASES = [
+    (12, 6144, 1024, 128, 128, True, True, True, torch.bfloat16),
+    (12, 6144, 1024, 128, 64, True, True, True, torch.bfloat16),
+    (12, 6144, 1024, 128, 128, False, False, True, torch.bfloat16),   # test_split_qkv_rope: no norm
+    (5, 512, 256, 64, 32, True, False, True, torch.float16),
+    (7, 1024, 256, 128, 128, True, True, False, torch.bfloat16),
+    (3, 256, 128, 32, 16, False, False, True, torch.bfloat16),
+    (1, 1024, 1024, 256, 64, True, True, False, torch.float16),
+    (257, 4096, 512, 128, 64, True, False, True, torch.bfloat16),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "b%d_q%d_kv%d_hd%d_r%d_%d%d%d_%s" % (c[:5] + tuple(int(x) for x in c[5:8]) + (str(c[8])[6:],)))
+def test_cuda_vs_oracle(case, cuda_device):
+    from sgl_kernel_npu.norm.split_qkv_rmsnorm_rope import split_qkv_rmsnorm_rope
+    b, qh, kvh, hd, rd, norm, bias, neox, dt = case
+    g = torch.Generator().manual_seed(b * 131 + hd + rd)
+    rn = lambda *s: torch.randn(*s, generator=g).to(dt)
+    qkv = rn(b, qh + 2 * kvh)
+    sin, cos = torch.rand(b, rd, generator=g).to(dt), torch.rand(b, rd, generator=g).to(dt)
+    qw, kw = (rn(hd), rn(hd)) if norm else (None, None)
+    qb, kb = (rn(hd), rn(hd)) if norm and bias else (None, None)
+    eps = 1e-6 if norm else None
+    want = sq.split_qkv_rmsnorm_rope(qkv, sin, cos, qh, kvh, hd, eps, qw, kw, qb, kb, neox)
+    dev = lambda t: None if t is None else t.to(cuda_device)
+    got = split_qkv_rmsnorm_rope(dev(qkv), dev(sin), dev(cos), qh, kvh, hd, eps=eps, q_weight=dev(qw), k_weight=dev(kw),
+                                 q_bias=dev(qb), k_bias=dev(kb), is_neox_style=neox)
+    for name, g_, w_ in zip("qk", got[:2], want[:2]):
+        same, worst = close(g_, w_)
+        assert worst <= 1 and same >= 0.99, (name, same, worst)
+    assert torch.equal(got[2].cpu(), want[2])
+    if not norm:  # no reduction on this path: nothing is associated differently, so the result is bit-exact
+        assert torch.equal(got[0].cpu(), want[0]) and torch.equal(got[1].cpu(), want[1])
+
+
+@pytest.mark.gpu
+def test_argument_checks(cuda_device):
+    from sgl_kernel_npu.norm.split_qkv_rmsnorm_rope import split_qkv_rmsnorm_rope
+    x = torch.zeros(2, 96 * 3, dtype=torch.bfloat16, device=cuda_device)
+    s = torch.zeros(2, 32, dtype=torch.bfloat16, device=cuda_device)
+    with pytest.raises(AssertionError):
+        split_qkv_rmsnorm_rope(x, s, s, 96, 96, 96)                    # head_dim not a power of two
+    x = torch.zeros(2, 128 + 2 * 96, dtype=torch.bfloat16, device=cuda_device)
+    with pytest.raises(AssertionError):
+        split_qkv_rmsnorm_rope(x, s, s, 128, 96, 32)                   # q_hidden not a multiple of kv_hidden
+    e = torch.zeros(0, 128 * 3, dtype=torch.bfloat16, device=cuda_device)
+    q, k, v = split_qkv_rmsnorm_rope(e, s[:0], s[:0], 128, 128, 64)    # empty batch: empty outputs, no launch
+    assert q.shape == (0, 128) and k.shape == (0, 128) and v.shape == (0, 128)
