@@ -448,6 +448,24 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   return MLAPO_OK;
 }
 
+// launch of one instantiation of the staged split_qkv kernel; the shared-memory opt-in is made once per instantiation and device
+template <class T, int HD, bool NEOX>
+static cudaError_t split_vec_launch(const SplitQkvArgs& a, unsigned chunks_per_tok, unsigned units, cudaStream_t st) {
+  using G = SplitGeom<HD>;
+  static bool opted[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64 || !opted[dev]) {
+    e = cudaFuncSetAttribute(split_qkv_vec_kernel<T, HD, NEOX>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    if (dev >= 0 && dev < 64) opted[dev] = true;
+  }
+  const unsigned blocks = units < 148u * 3u ? units : 148u * 3u;
+  split_qkv_vec_kernel<T, HD, NEOX><<<blocks, kSplitThreads, G::SMEM_BYTES, st>>>(a, chunks_per_tok, units);
+  return cudaGetLastError();
+}
+
 template <class T>
 static int bmt_launch_impl(const void* a, const void* b, void* c, int64_t m, int64_t batch, int64_t k, int64_t n, int b_is_nz,
                            cudaStream_t st) {
@@ -625,19 +643,57 @@ int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* 
   if (!qkv || !sin || !cos || !q_out || !k_out || !v_out) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: null pointer");
   if (has_norm && (!q_weight || !k_weight)) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: eps given but no norm weights");
   if ((q_bias == nullptr) != (k_bias == nullptr)) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: q_bias and k_bias go together");
-  if (batch <= 0 || head_dim <= 0 || head_dim > kSplitMaxHeadDim || (head_dim & (head_dim - 1)) || q_hidden % head_dim || kv_hidden % head_dim ||
+  if (batch <= 0 || head_dim < 2 || head_dim > kSplitMaxHeadDim || (head_dim & (head_dim - 1)) || q_hidden % head_dim || kv_hidden % head_dim ||
       kv_hidden <= 0 || q_hidden % kv_hidden || rope_dim <= 0 || rope_dim > head_dim || (rope_dim & 1))
     return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: batch=%lld q_hidden=%d kv_hidden=%d head_dim=%d (power of two <= %d) rope_dim=%d",
                 (long long)batch, q_hidden, kv_hidden, head_dim, kSplitMaxHeadDim, rope_dim);
   SplitQkvArgs a{qkv, sin, cos, q_out, k_out, v_out, q_weight, k_weight, q_bias, k_bias, batch, q_hidden, kv_hidden, head_dim, rope_dim, eps,
                  has_norm, neox_style};
-  const long long items = batch * ((q_hidden + 2LL * kv_hidden) / head_dim);
-  long long blocks = (items + kSplitWarps - 1) / kSplitWarps;
-  if (blocks > 148 * 32) blocks = 148 * 32;
+  if (act_dtype != MLAPO_ACT_BF16 && act_dtype != MLAPO_ACT_FP16) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: tensors must be fp16 or bf16");
+  const bool bf = act_dtype == MLAPO_ACT_BF16;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (act_dtype == MLAPO_ACT_BF16) split_qkv_rmsnorm_rope_kernel<__nv_bfloat16><<<(unsigned)blocks, kSplitWarps * 32, 0, st>>>(a);
-  else if (act_dtype == MLAPO_ACT_FP16) split_qkv_rmsnorm_rope_kernel<__half><<<(unsigned)blocks, kSplitWarps * 32, 0, st>>>(a);
-  else return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: tensors must be fp16 or bf16");
+  const int vec = head_dim >= 512 ? 16 : 8;
+  uintptr_t align = 0;
+  for (const void* p : {qkv, sin, cos, (const void*)q_out, (const void*)k_out, (const void*)v_out}) align |= reinterpret_cast<uintptr_t>(p);
+  if (head_dim >= 32 && rope_dim % vec == 0 && (align & 15) == 0) {
+    // vector kernel: a CTA takes chunks of 4096 elements of one token's fused row
+    const long long row = q_hidden + 2LL * kv_hidden;
+    const long long cpt = (row + 4095) / 4096;
+    const long long tok_per_launch = (1LL << 31) / cpt;  // unit indices stay below 2^31
+    const size_t es = 2;
+    for (long long t0 = 0; t0 < batch; t0 += tok_per_launch) {
+      const long long nb = batch - t0 < tok_per_launch ? batch - t0 : tok_per_launch;
+      SplitQkvArgs c = a;
+      c.qkv = static_cast<const char*>(qkv) + t0 * row * es;
+      c.sin = static_cast<const char*>(sin) + t0 * rope_dim * es;
+      c.cos = static_cast<const char*>(cos) + t0 * rope_dim * es;
+      c.q_out = static_cast<char*>(q_out) + t0 * q_hidden * es;
+      c.k_out = static_cast<char*>(k_out) + t0 * kv_hidden * es;
+      c.v_out = static_cast<char*>(v_out) + t0 * kv_hidden * es;
+      c.batch = nb;
+      const unsigned units = (unsigned)(nb * cpt);
+      cudaError_t le = cudaSuccess;
+#define MLAPO_SPLIT_CASE(HD)                                                                                       \
+  case HD:                                                                                                         \
+    le = bf ? (neox_style ? split_vec_launch<__nv_bfloat16, HD, true>(c, (unsigned)cpt, units, st)                 \
+                          : split_vec_launch<__nv_bfloat16, HD, false>(c, (unsigned)cpt, units, st))               \
+            : (neox_style ? split_vec_launch<__half, HD, true>(c, (unsigned)cpt, units, st)                        \
+                          : split_vec_launch<__half, HD, false>(c, (unsigned)cpt, units, st));                     \
+    break;
+      switch (head_dim) {
+        MLAPO_SPLIT_CASE(32) MLAPO_SPLIT_CASE(64) MLAPO_SPLIT_CASE(128) MLAPO_SPLIT_CASE(256) MLAPO_SPLIT_CASE(512)
+        default: return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: head_dim=%d", head_dim);
+      }
+#undef MLAPO_SPLIT_CASE
+      if (le != cudaSuccess) return fail(MLAPO_ERR_CUDA, "split_qkv_rmsnorm_rope launch: %s", cudaGetErrorString(le));
+    }
+  } else {
+    const long long items = batch * ((q_hidden + 2LL * kv_hidden) / head_dim);
+    long long blocks = (items + kSplitWarps - 1) / kSplitWarps;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    if (bf) split_qkv_scalar_kernel<__nv_bfloat16><<<(unsigned)blocks, kSplitWarps * 32, 0, st>>>(a);
+    else split_qkv_scalar_kernel<__half><<<(unsigned)blocks, kSplitWarps * 32, 0, st>>>(a);
+  }
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "split_qkv_rmsnorm_rope launch: %s", cudaGetErrorString(e));
 }

@@ -4,9 +4,17 @@
 // everything in fp32, ONE rounding at the store;  n = x * (1/sqrt(mean(x^2) + eps)) [* w [+ b]];  neox style:
 // out[:h] = n[:h]*cos[:h] - n[h:r]*sin[:h], out[h:r] = n[h:r]*cos[h:r] + n[:h]*sin[h:r]  (h = rope_dim/2, r = rope_dim);
 // interleaved style: pairs (2i, 2i+1) with sin[i], cos[i];  dims >= rope_dim pass through normalised.
-// One warp per (token, head); the head vector sits in shared memory so that RoPE partners are a plain read.
+//
+// HBM-bound by its bytes (4 per element), but an SM has only ~22 issue slots and ~0.17 shared-memory wavefronts per element at
+// 6.5 TB/s, so the main kernel is laid out to spend few of either.  A CTA takes 4096-element chunks of one token's fused row
+// through a ring of stages filled by 1-D bulk copies; head_dim / V lanes make a head (V = 8, 16 for head_dim 512), a lane owns
+// two slices of V/2 elements chosen so that a neox RoPE pair lives in ONE lane (no exchange), shared-memory reads are
+// conflict-free 8/16-byte accesses, the fp32 arithmetic is issued as two-wide f32x2 instructions, results go straight to global.
+// Shapes the vector layout does not fit (head_dim < 32, rope_dim not a multiple of V, unaligned pointers) take the scalar kernel
+// at the end of the file.
 #pragma once
 #include "mlapo_numerics.cuh"
+#include "sm100_ptx.cuh"
 
 namespace mlapo {
 
@@ -27,11 +35,260 @@ struct SplitQkvArgs {
   int has_norm, neox;
 };
 
+
 constexpr int kSplitWarps = 8;
 constexpr int kSplitMaxHeadDim = 512;
 
+// two-wide fp32 arithmetic (FMUL2 / FFMA2 on sm_100): half the issue slots of the scalar forms
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+  unsigned long long d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)));
+  return *reinterpret_cast<float2*>(&d);
+}
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;"
+      : "=l"(d)
+      : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)), "l"(*reinterpret_cast<unsigned long long*>(&c)));
+  return *reinterpret_cast<float2*>(&d);
+}
+
+// V 16-bit elements as raw words; one load / store instruction up to 16 bytes, two for 32
+template <int V>
+struct Raw16 {
+  uint32_t w[(V + 1) / 2];
+  __device__ __forceinline__ void load(const void* p) {
+    if constexpr (V == 2) w[0] = *reinterpret_cast<const uint32_t*>(p);
+    else if constexpr (V == 4) { const uint2 t = *reinterpret_cast<const uint2*>(p); w[0] = t.x; w[1] = t.y; }
+    else {
+#pragma unroll
+      for (int i = 0; i < V / 8; ++i) {
+        const uint4 t = reinterpret_cast<const uint4*>(p)[i];
+        w[4 * i] = t.x; w[4 * i + 1] = t.y; w[4 * i + 2] = t.z; w[4 * i + 3] = t.w;
+      }
+    }
+  }
+  __device__ __forceinline__ void store(void* p) const {
+    if constexpr (V == 4) *reinterpret_cast<uint2*>(p) = make_uint2(w[0], w[1]);
+#pragma unroll
+    for (int i = 0; i < V / 8; ++i) reinterpret_cast<uint4*>(p)[i] = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
+  }
+  __device__ __forceinline__ void zero() {
+#pragma unroll
+    for (int i = 0; i < (V + 1) / 2; ++i) w[i] = 0u;
+  }
+};
+
+template <int HD>
+struct SplitGeom {
+  static constexpr int V = HD >= 512 ? 16 : 8;          // elements per lane
+  static constexpr int L = HD / V;                      // lanes per head: 4 .. 32
+  static constexpr int SPAN = 32 * V;                   // elements of the fused row per warp
+  static constexpr int U = 16 / V;                      // spans per warp and chunk
+  static constexpr int CHUNK = kSplitWarps * U * SPAN;  // elements of one token's row a CTA takes per stage (4096 = 8 KB)
+  static constexpr int STAGES = 4;
+  static constexpr int STAGE_BYTES = CHUNK * 2 + 4 * HD;  // chunk, then this token's sin and cos (<= HD elements each)
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 16 * HD;
+};
+
+// Work unit = (token, chunk of its fused row).  A ninth warp keeps the STAGES-deep ring full with 1-D bulk copies (row chunk, sin,
+// cos) onto one mbarrier per stage; the 8 working warps pull their 16 bytes per lane into registers, release the stage at once
+// (one arrive per warp) and store results straight to global, so no CTA-wide barrier sits in the loop.
+// total_units = batch * chunks_per_tok fits 32 bits (the host splits larger batches).
+constexpr int kSplitThreads = (kSplitWarps + 1) * 32;
+
+template <class T, int HD, bool NEOX>
+__global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQkvArgs a, unsigned chunks_per_tok, unsigned total_units) {
+  using namespace ptx;
+  using G = SplitGeom<HD>;
+  constexpr int V = G::V, L = G::L, SPAN = G::SPAN, U = G::U, P = V / 2, S = G::STAGES;
+  extern __shared__ __align__(16) uint8_t smem[];
+  __shared__ __align__(8) uint64_t s_full[S], s_empty[S];
+  float* s_wb = reinterpret_cast<float*>(smem + S * G::STAGE_BYTES);  // [4][HD]: q weight, k weight, q bias, k bias
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qh = a.q_hidden, kvh = a.kv_hidden, row = qh + 2 * kvh;
+  const int rd = a.rope_dim, half = rd / 2;
+
+  const unsigned stride = gridDim.x;
+  const unsigned dt = stride / chunks_per_tok, dc = stride - dt * chunks_per_tok;
+  unsigned unit = blockIdx.x, t = unit / chunks_per_tok, ch = unit - t * chunks_per_tok;
+  auto advance = [&]() {
+    unit += stride; t += dt; ch += dc;
+    if (ch >= chunks_per_tok) { ch -= chunks_per_tok; ++t; }
+  };
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), kSplitWarps); }
+    fence_mbar_init();
+  }
+  if (a.has_norm) {
+    const bool has_bias = a.q_bias != nullptr;
+    for (int i = threadIdx.x; i < HD; i += kSplitThreads) {
+      s_wb[i] = Act<T>::to_f(reinterpret_cast<const T*>(a.q_weight)[i]);
+      s_wb[HD + i] = Act<T>::to_f(reinterpret_cast<const T*>(a.k_weight)[i]);
+      s_wb[2 * HD + i] = has_bias ? Act<T>::to_f(reinterpret_cast<const T*>(a.q_bias)[i]) : 0.f;
+      s_wb[3 * HD + i] = has_bias ? Act<T>::to_f(reinterpret_cast<const T*>(a.k_bias)[i]) : 0.f;
+    }
+  }
+  __syncthreads();
+
+  if (warp == kSplitWarps) {  // producer
+    if (lane == 0) {
+      for (unsigned it = 0; unit < total_units; ++it, advance()) {
+        const int stage = (int)(it % S);
+        if (it >= (unsigned)S) mbar_wait(smem_u32(&s_empty[stage]), ((it / S) - 1) & 1);
+        const uint32_t bar = smem_u32(&s_full[stage]);
+        const uint32_t dst = smem_u32(smem + stage * G::STAGE_BYTES);
+        const int off = (int)ch * G::CHUNK;
+        const uint32_t bytes = 2u * (uint32_t)(row - off < G::CHUNK ? row - off : G::CHUNK);
+        const bool rope_here = off < qh + kvh;  // a chunk of v heads only needs no sin / cos
+        mbar_arrive_expect_tx(bar, bytes + (rope_here ? 4u * (uint32_t)rd : 0u));
+        bulk_load_1d(dst, reinterpret_cast<const T*>(a.qkv) + (long long)t * row + off, bytes, bar);
+        if (rope_here) {
+          bulk_load_1d(dst + G::CHUNK * 2, reinterpret_cast<const T*>(a.sin) + (long long)t * rd, 2u * (uint32_t)rd, bar);
+          bulk_load_1d(dst + G::CHUNK * 2 + 2 * HD, reinterpret_cast<const T*>(a.cos) + (long long)t * rd, 2u * (uint32_t)rd, bar);
+        }
+      }
+    }
+    return;
+  }
+
+  // The lane's V elements of a head are two slices of W: for neox rope lanes slice A sits in the first half of the rotated dims
+  // and slice B holds its partners in the second half, so the rotation needs no exchange between lanes; every other lane owns
+  // V contiguous elements (behind rope_dim for neox; pairs stay inside a lane for the interleaved style).
+  constexpr int W = V / 2, PW = W / 2;
+  const int j = lane % L;
+  int oA, oB;
+  bool in_rope;
+  if constexpr (NEOX) {
+    in_rope = j * W < half;
+    oA = in_rope ? j * W : rd + V * (j - half / W);
+    oB = in_rope ? half + j * W : oA + W;
+  } else {
+    in_rope = j * V < rd;
+    oA = j * V;
+    oB = oA + W;
+  }
+  const int head_pos = (lane / L) * HD;  // of the lane's head inside the warp's span
+
+  for (unsigned it = 0; unit < total_units; ++it, advance()) {
+    const int stage = (int)(it % S);
+    mbar_wait(smem_u32(&s_full[stage]), (it / S) & 1);
+    const uint8_t* st = smem + stage * G::STAGE_BYTES;
+    const int off = (int)ch * G::CHUNK;
+    Raw16<W> rawA[U], rawB[U];
+    int col[U], kind[U];  // col: of the lane's head in the fused row;  kind: 0 q, 1 k, 2 v, 3 beyond the row
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int pos = (warp * U + u) * SPAN + head_pos;
+      const int c = off + pos;
+      col[u] = c;
+      kind[u] = c >= row ? 3 : c < qh ? 0 : c < qh + kvh ? 1 : 2;
+      if (kind[u] < 3) { rawA[u].load(st + (pos + oA) * 2); rawB[u].load(st + (pos + oB) * 2); }
+      else { rawA[u].zero(); rawB[u].zero(); }
+    }
+    // this token's sin / cos for the lane's slices; the sign of the rotation is folded into sin
+    float2 snA[PW], csA[PW], snB[PW], csB[PW];
+    if (in_rope && off < qh + kvh) {
+      const uint8_t* ssin = st + G::CHUNK * 2;
+      const uint8_t* scos = ssin + 2 * HD;
+      if constexpr (NEOX) {
+        Raw16<W> r;
+        r.load(ssin + oA * 2);
+#pragma unroll
+        for (int p = 0; p < PW; ++p) snA[p] = make_float2(-Act<T>::lo(r.w[p]), -Act<T>::hi(r.w[p]));
+        r.load(ssin + oB * 2);
+#pragma unroll
+        for (int p = 0; p < PW; ++p) snB[p] = make_float2(Act<T>::lo(r.w[p]), Act<T>::hi(r.w[p]));
+        r.load(scos + oA * 2);
+#pragma unroll
+        for (int p = 0; p < PW; ++p) csA[p] = make_float2(Act<T>::lo(r.w[p]), Act<T>::hi(r.w[p]));
+        r.load(scos + oB * 2);
+#pragma unroll
+        for (int p = 0; p < PW; ++p) csB[p] = make_float2(Act<T>::lo(r.w[p]), Act<T>::hi(r.w[p]));
+      } else {
+        Raw16<W> rs, rc;  // pair i of the head uses sin[i], cos[i]: W values for the lane's W pairs
+        rs.load(ssin + oA);
+        rc.load(scos + oA);
+#pragma unroll
+        for (int p = 0; p < W; ++p) {
+          const float s = (p & 1) ? Act<T>::hi(rs.w[p >> 1]) : Act<T>::lo(rs.w[p >> 1]);
+          const float c = (p & 1) ? Act<T>::hi(rc.w[p >> 1]) : Act<T>::lo(rc.w[p >> 1]);
+          (p < PW ? snA[p] : snB[p - PW]) = make_float2(-s, s);
+          (p < PW ? csA[p] : csB[p - PW]) = make_float2(c, c);
+        }
+      }
+    }
+    __syncwarp();  // every lane holds its part of the stage: give it back
+    if (lane == 0) mbar_arrive(smem_u32(&s_empty[stage]));
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float2 xA[PW], xB[PW];
+      float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int p = 0; p < PW; ++p) {
+        xA[p] = make_float2(Act<T>::lo(rawA[u].w[p]), Act<T>::hi(rawA[u].w[p]));
+        xB[p] = make_float2(Act<T>::lo(rawB[u].w[p]), Act<T>::hi(rawB[u].w[p]));
+        acc = fma2(xA[p], xA[p], acc);
+        acc = fma2(xB[p], xB[p], acc);
+      }
+      if (a.has_norm) {
+        float ss = acc.x + acc.y;
+#pragma unroll
+        for (int o = L / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+        if (kind[u] < 2) {
+          const float rstd = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(ss * (1.f / HD), a.eps)));
+          const float2 r2 = make_float2(rstd, rstd);
+          const float* wk = s_wb + kind[u] * HD;
+          const float* bk = s_wb + (2 + kind[u]) * HD;
+#pragma unroll
+          for (int p = 0; p < PW; p += 2) {
+            float4 w4 = *reinterpret_cast<const float4*>(wk + oA + 2 * p), b4 = *reinterpret_cast<const float4*>(bk + oA + 2 * p);
+            xA[p] = fma2(mul2(xA[p], r2), make_float2(w4.x, w4.y), make_float2(b4.x, b4.y));
+            xA[p + 1] = fma2(mul2(xA[p + 1], r2), make_float2(w4.z, w4.w), make_float2(b4.z, b4.w));
+            w4 = *reinterpret_cast<const float4*>(wk + oB + 2 * p);
+            b4 = *reinterpret_cast<const float4*>(bk + oB + 2 * p);
+            xB[p] = fma2(mul2(xB[p], r2), make_float2(w4.x, w4.y), make_float2(b4.x, b4.y));
+            xB[p + 1] = fma2(mul2(xB[p + 1], r2), make_float2(w4.z, w4.w), make_float2(b4.z, b4.w));
+          }
+        }
+      }
+      if (kind[u] == 3) continue;
+      T* dst;
+      if (kind[u] == 2) {  // v: the bits pass through
+        dst = reinterpret_cast<T*>(a.v_out) + (long long)t * kvh + (col[u] - qh - kvh);
+        rawA[u].store(dst + oA);
+        rawB[u].store(dst + oB);
+        continue;
+      }
+      if (in_rope) {
+#pragma unroll
+        for (int p = 0; p < PW; ++p) {
+          if constexpr (NEOX) {  // A: n*cos - partner*sin;  B: n*cos + partner*sin
+            const float2 na = fma2(xB[p], snA[p], mul2(xA[p], csA[p]));
+            xB[p] = fma2(xA[p], snB[p], mul2(xB[p], csB[p]));
+            xA[p] = na;
+          } else {  // (x0, x1) -> (x0 c - x1 s, x1 c + x0 s)
+            xA[p] = fma2(make_float2(xA[p].y, xA[p].x), snA[p], mul2(xA[p], csA[p]));
+            xB[p] = fma2(make_float2(xB[p].y, xB[p].x), snB[p], mul2(xB[p], csB[p]));
+          }
+        }
+      }
+      Raw16<W> outA, outB;
+#pragma unroll
+      for (int p = 0; p < PW; ++p) {
+        outA.w[p] = Act<T>::pack(xA[p].x, xA[p].y);
+        outB.w[p] = Act<T>::pack(xB[p].x, xB[p].y);
+      }
+      dst = kind[u] == 0 ? reinterpret_cast<T*>(a.q_out) + (long long)t * qh + col[u] : reinterpret_cast<T*>(a.k_out) + (long long)t * kvh + (col[u] - qh);
+      outA.store(dst + oA);
+      outB.store(dst + oB);
+    }
+  }
+}
+
+// Scalar kernel for the shapes the vector layout does not fit: one warp per (token, head), element by element.
 template <class T>
-__global__ void __launch_bounds__(kSplitWarps * 32) split_qkv_rmsnorm_rope_kernel(SplitQkvArgs a) {
+__global__ void __launch_bounds__(kSplitWarps * 32) split_qkv_scalar_kernel(SplitQkvArgs a) {
   __shared__ float s_x[kSplitWarps][kSplitMaxHeadDim];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = a.q_hidden / a.head_dim, nk = a.kv_hidden / a.head_dim;
@@ -56,16 +313,15 @@ __global__ void __launch_bounds__(kSplitWarps * 32) split_qkv_rmsnorm_rope_kerne
     for (int e = lane; e < hd; e += 32) {
       const float v = Act<T>::to_f(src[e]);
       x[e] = v;
-      ss = __fadd_rn(ss, __fmul_rn(v, v));
+      ss = fmaf(v, v, ss);
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) ss = __fadd_rn(ss, __shfl_xor_sync(0xffffffffu, ss, o));
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
     if (a.has_norm) {
       const float rstd = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(__fdiv_rn(ss, (float)hd), a.eps)));
       for (int e = lane; e < hd; e += 32) {
-        float n = __fmul_rn(__fmul_rn(x[e], rstd), Act<T>::to_f(w[e]));
-        if (b) n = __fadd_rn(n, Act<T>::to_f(b[e]));
-        x[e] = n;
+        const float n = __fmul_rn(x[e], rstd);
+        x[e] = b ? fmaf(n, Act<T>::to_f(w[e]), Act<T>::to_f(b[e])) : __fmul_rn(n, Act<T>::to_f(w[e]));
       }
     }
     __syncwarp();
@@ -84,7 +340,7 @@ __global__ void __launch_bounds__(kSplitWarps * 32) split_qkv_rmsnorm_rope_kerne
           s = Act<T>::to_f(sn[e >> 1]);
           c = Act<T>::to_f(cs[e >> 1]);
         }
-        o = __fadd_rn(__fmul_rn(rot, s), __fmul_rn(o, c));
+        o = fmaf(rot, s, __fmul_rn(o, c));
       }
       dst[e] = Act<T>::from_f(o);
     }

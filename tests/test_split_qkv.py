@@ -77,6 +77,12 @@ CASES = [
     (3, 256, 128, 32, 16, False, False, True, torch.bfloat16),
     (1, 1024, 1024, 256, 64, True, True, False, torch.float16),
     (257, 4096, 512, 128, 64, True, False, True, torch.bfloat16),
+    (4, 512, 256, 128, 24, True, True, True, torch.bfloat16),      # rope_dim a multiple of 8 only
+    (4, 512, 256, 128, 96, True, False, False, torch.bfloat16),
+    (9, 1024, 512, 512, 128, True, True, True, torch.float16),    # 16 elements per lane
+    (9, 1024, 512, 512, 64, True, True, False, torch.bfloat16),
+    (3, 256, 128, 64, 20, True, True, True, torch.bfloat16),       # rope_dim the vector layout does not fit: scalar kernel
+    (3, 64, 32, 16, 8, True, True, False, torch.float16),          # head_dim below 32: scalar kernel
 ]
 
 
