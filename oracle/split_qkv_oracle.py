@@ -9,7 +9,9 @@ import torch
 
 
 def split_qkv_rmsnorm_rope(qkv, sin, cos, q_hidden, kv_hidden, head_dim, eps=None, q_weight=None, k_weight=None, q_bias=None,
-                           k_bias=None, is_neox_style=True):
+                           k_bias=None, is_neox_style=True, with_scale=False):
+    """-> (q, k, v); with_scale adds (mq, mk), float32 arrays |rot * sin| + |n * cos| (|n| outside the rotated dims): the magnitude
+    the result was summed from, which bounds a sound tolerance where the rotation cancels."""
     dt = qkv.dtype
     f = lambda t: None if t is None else t.to(torch.float32).numpy().astype(np.float32)
     x = f(qkv)
@@ -35,9 +37,10 @@ def split_qkv_rmsnorm_rope(qkv, sin, cos, q_hidden, kv_hidden, head_dim, eps=Non
             cat[..., 1::2] = rot[..., 0::2]
             ss, cc = np.repeat(s[..., :h], 2, axis=-1), np.repeat(c[..., :h], 2, axis=-1)
         out = np.concatenate((cat * ss + rot * cc, n[..., rd:]), axis=-1).astype(np.float32)
-        return torch.from_numpy(out.reshape(b, -1)).to(dt)
+        scale = np.concatenate((np.abs(cat * ss) + np.abs(rot * cc), np.abs(n[..., rd:])), axis=-1).astype(np.float32)
+        return torch.from_numpy(out.reshape(b, -1)).to(dt), scale.reshape(b, -1)
 
-    q = one(x[:, :q_hidden], q_weight, q_bias)
-    k = one(x[:, q_hidden:q_hidden + kv_hidden], k_weight, k_bias)
+    q, mq = one(x[:, :q_hidden], q_weight, q_bias)
+    k, mk = one(x[:, q_hidden:q_hidden + kv_hidden], k_weight, k_bias)
     v = qkv[:, q_hidden + kv_hidden:].clone()
-    return q, k, v
+    return (q, k, v, mq, mk) if with_scale else (q, k, v)

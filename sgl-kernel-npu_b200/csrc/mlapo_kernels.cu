@@ -450,7 +450,7 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
 
 // launch of one instantiation of the staged split_qkv kernel; the shared-memory opt-in is made once per instantiation and device
 template <class T, int HD, bool NEOX>
-static cudaError_t split_vec_launch(const SplitQkvArgs& a, unsigned chunks_per_tok, unsigned units, cudaStream_t st) {
+static cudaError_t split_vec_launch(const SplitQkvArgs& a, cudaStream_t st) {
   using G = SplitGeom<HD>;
   static bool opted[64] = {};
   int dev = 0;
@@ -461,8 +461,20 @@ static cudaError_t split_vec_launch(const SplitQkvArgs& a, unsigned chunks_per_t
     if (e != cudaSuccess) return e;
     if (dev >= 0 && dev < 64) opted[dev] = true;
   }
-  const unsigned blocks = units < 148u * 3u ? units : 148u * 3u;
-  split_qkv_vec_kernel<T, HD, NEOX><<<blocks, kSplitThreads, G::SMEM_BYTES, st>>>(a, chunks_per_tok, units);
+  // CTAs per chunk index of the row, in proportion to the chunk's cost (its length plus a fixed part per token), 3 CTAs per SM
+  const long long row = a.q_hidden + 2LL * a.kv_hidden;
+  const unsigned cpt = (unsigned)((row + G::CHUNK - 1) / G::CHUNK);
+  const long long last_len = row - (long long)(cpt - 1) * G::CHUNK;
+  const long long w_full = G::CHUNK + 512, w_last = last_len + 512;
+  const unsigned ctas = 148u * 3u;
+  unsigned g_last = (unsigned)((ctas * w_last + ((cpt - 1) * w_full + w_last) / 2) / ((cpt - 1) * w_full + w_last));
+  if (g_last < 1) g_last = 1;
+  unsigned g_full = cpt > 1 ? (ctas - g_last) / (cpt - 1) : 0;
+  if (cpt > 1 && g_full < 1) g_full = 1;
+  const unsigned batch = (unsigned)a.batch;
+  if (g_last > batch) g_last = batch;
+  if (g_full > batch) g_full = batch;
+  split_qkv_vec_kernel<T, HD, NEOX><<<(cpt - 1) * g_full + g_last, kSplitThreads, G::SMEM_BYTES, st>>>(a, cpt, g_full, g_last);
   return cudaGetLastError();
 }
 
@@ -656,10 +668,9 @@ int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* 
   uintptr_t align = 0;
   for (const void* p : {qkv, sin, cos, (const void*)q_out, (const void*)k_out, (const void*)v_out}) align |= reinterpret_cast<uintptr_t>(p);
   if (head_dim >= 32 && rope_dim % vec == 0 && (align & 15) == 0) {
-    // vector kernel: a CTA takes chunks of 4096 elements of one token's fused row
+    // vector kernel; token indices are 32-bit in it, so a (hypothetical) larger batch goes in pieces
     const long long row = q_hidden + 2LL * kv_hidden;
-    const long long cpt = (row + 4095) / 4096;
-    const long long tok_per_launch = (1LL << 31) / cpt;  // unit indices stay below 2^31
+    const long long tok_per_launch = 1LL << 31;
     const size_t es = 2;
     for (long long t0 = 0; t0 < batch; t0 += tok_per_launch) {
       const long long nb = batch - t0 < tok_per_launch ? batch - t0 : tok_per_launch;
@@ -671,14 +682,11 @@ int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* 
       c.k_out = static_cast<char*>(k_out) + t0 * kv_hidden * es;
       c.v_out = static_cast<char*>(v_out) + t0 * kv_hidden * es;
       c.batch = nb;
-      const unsigned units = (unsigned)(nb * cpt);
       cudaError_t le = cudaSuccess;
-#define MLAPO_SPLIT_CASE(HD)                                                                                       \
-  case HD:                                                                                                         \
-    le = bf ? (neox_style ? split_vec_launch<__nv_bfloat16, HD, true>(c, (unsigned)cpt, units, st)                 \
-                          : split_vec_launch<__nv_bfloat16, HD, false>(c, (unsigned)cpt, units, st))               \
-            : (neox_style ? split_vec_launch<__half, HD, true>(c, (unsigned)cpt, units, st)                        \
-                          : split_vec_launch<__half, HD, false>(c, (unsigned)cpt, units, st));                     \
+#define MLAPO_SPLIT_CASE(HD)                                                                                                       \
+  case HD:                                                                                                                         \
+    le = bf ? (neox_style ? split_vec_launch<__nv_bfloat16, HD, true>(c, st) : split_vec_launch<__nv_bfloat16, HD, false>(c, st))   \
+            : (neox_style ? split_vec_launch<__half, HD, true>(c, st) : split_vec_launch<__half, HD, false>(c, st));               \
     break;
       switch (head_dim) {
         MLAPO_SPLIT_CASE(32) MLAPO_SPLIT_CASE(64) MLAPO_SPLIT_CASE(128) MLAPO_SPLIT_CASE(256) MLAPO_SPLIT_CASE(512)

@@ -94,11 +94,13 @@ struct SplitGeom {
 // Work unit = (token, chunk of its fused row).  A ninth warp keeps the STAGES-deep ring full with 1-D bulk copies (row chunk, sin,
 // cos) onto one mbarrier per stage; the 8 working warps pull their 16 bytes per lane into registers, release the stage at once
 // (one arrive per warp) and store results straight to global, so no CTA-wide barrier sits in the loop.
-// total_units = batch * chunks_per_tok fits 32 bits (the host splits larger batches).
+// A CTA stays on ONE chunk index of the row and walks over tokens, so where a lane's heads lie and go is loop-invariant.  The
+// grid is (chunks_per_tok - 1) * g_full + g_last CTAs: g_full per full chunk index, g_last for the last, possibly shorter, chunk
+// (sized by the host in proportion to its length so that all CTAs finish together).
 constexpr int kSplitThreads = (kSplitWarps + 1) * 32;
 
 template <class T, int HD, bool NEOX>
-__global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQkvArgs a, unsigned chunks_per_tok, unsigned total_units) {
+__global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQkvArgs a, unsigned chunks_per_tok, unsigned g_full, unsigned g_last) {
   using namespace ptx;
   using G = SplitGeom<HD>;
   constexpr int V = G::V, L = G::L, SPAN = G::SPAN, U = G::U, P = V / 2, S = G::STAGES;
@@ -109,13 +111,12 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
   const int qh = a.q_hidden, kvh = a.kv_hidden, row = qh + 2 * kvh;
   const int rd = a.rope_dim, half = rd / 2;
 
-  const unsigned stride = gridDim.x;
-  const unsigned dt = stride / chunks_per_tok, dc = stride - dt * chunks_per_tok;
-  unsigned unit = blockIdx.x, t = unit / chunks_per_tok, ch = unit - t * chunks_per_tok;
-  auto advance = [&]() {
-    unit += stride; t += dt; ch += dc;
-    if (ch >= chunks_per_tok) { ch -= chunks_per_tok; ++t; }
-  };
+  const unsigned full_ctas = (chunks_per_tok - 1) * g_full;
+  const bool last = blockIdx.x >= full_ctas;
+  const unsigned ch = last ? chunks_per_tok - 1 : blockIdx.x / g_full;
+  const unsigned tstep = last ? g_last : g_full;
+  const unsigned batch = (unsigned)a.batch;
+  unsigned t = last ? blockIdx.x - full_ctas : blockIdx.x - ch * g_full;
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), kSplitWarps); }
     fence_mbar_init();
@@ -133,9 +134,9 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
 
   if (warp == kSplitWarps) {  // producer
     if (lane == 0) {
-      for (unsigned it = 0; unit < total_units; ++it, advance()) {
+      for (unsigned it = 0; t < batch; ++it, t += tstep) {
         const int stage = (int)(it % S);
-        if (it >= (unsigned)S) mbar_wait(smem_u32(&s_empty[stage]), ((it / S) - 1) & 1);
+        if (it >= (unsigned)S) mbar_wait_light(smem_u32(&s_empty[stage]), ((it / S) - 1) & 1);
         const uint32_t bar = smem_u32(&s_full[stage]);
         const uint32_t dst = smem_u32(smem + stage * G::STAGE_BYTES);
         const int off = (int)ch * G::CHUNK;
@@ -169,21 +170,32 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
     oB = oA + W;
   }
   const int head_pos = (lane / L) * HD;  // of the lane's head inside the warp's span
-
-  for (unsigned it = 0; unit < total_units; ++it, advance()) {
-    const int stage = (int)(it % S);
-    mbar_wait(smem_u32(&s_full[stage]), (it / S) & 1);
-    const uint8_t* st = smem + stage * G::STAGE_BYTES;
-    const int off = (int)ch * G::CHUNK;
-    Raw16<W> rawA[U], rawB[U];
-    int col[U], kind[U];  // col: of the lane's head in the fused row;  kind: 0 q, 1 k, 2 v, 3 beyond the row
+  // Where the lane's head of span u lies (kind: 0 q, 1 k, 2 v, 3 beyond the row) and where it goes: out0 is the output position
+  // for token 0, tstr the output's token stride.
+  int kind[U], tstr[U];
+  T* out0[U];
+  const int off = (int)ch * G::CHUNK;
+  {
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int pos = (warp * U + u) * SPAN + head_pos;
-      const int c = off + pos;
-      col[u] = c;
+      const int c = off + (u * kSplitWarps + warp) * SPAN + head_pos;
       kind[u] = c >= row ? 3 : c < qh ? 0 : c < qh + kvh ? 1 : 2;
-      if (kind[u] < 3) { rawA[u].load(st + (pos + oA) * 2); rawB[u].load(st + (pos + oB) * 2); }
+      tstr[u] = kind[u] == 0 ? qh : kvh;
+      out0[u] = kind[u] == 0 ? reinterpret_cast<T*>(a.q_out) + c
+                : kind[u] == 1 ? reinterpret_cast<T*>(a.k_out) + (c - qh) : reinterpret_cast<T*>(a.v_out) + (c - qh - kvh);
+    }
+  }
+  const uint32_t full0 = smem_u32(&s_full[0]), empty0 = smem_u32(&s_empty[0]);
+  const int ldA = (warp * SPAN + head_pos + oA) * 2, ldB = (warp * SPAN + head_pos + oB) * 2;  // in a stage, round 0
+
+  for (unsigned it = 0; t < batch; ++it, t += tstep) {
+    const int stage = (int)(it % S);
+    mbar_wait_light(full0 + 8 * stage, (it / S) & 1);
+    const uint8_t* st = smem + stage * G::STAGE_BYTES;
+    Raw16<W> rawA[U], rawB[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (kind[u] < 3) { rawA[u].load(st + ldA + u * kSplitWarps * SPAN * 2); rawB[u].load(st + ldB + u * kSplitWarps * SPAN * 2); }
       else { rawA[u].zero(); rawB[u].zero(); }
     }
     // this token's sin / cos for the lane's slices; the sign of the rotation is folded into sin
@@ -219,7 +231,7 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
       }
     }
     __syncwarp();  // every lane holds its part of the stage: give it back
-    if (lane == 0) mbar_arrive(smem_u32(&s_empty[stage]));
+    if (lane == 0) mbar_arrive(empty0 + 8 * stage);
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       float2 xA[PW], xB[PW];
@@ -236,7 +248,11 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
 #pragma unroll
         for (int o = L / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
         if (kind[u] < 2) {
-          const float rstd = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(ss * (1.f / HD), a.eps)));
+          // 1/sqrt by the hardware approximation and one Newton step (error below one fp32 ulp): five instructions where the
+          // IEEE sqrt and division take ~35, a third of this loop's issue slots
+          const float m = __fadd_rn(ss * (1.f / HD), a.eps);
+          const float y0 = rsqrtf(m);
+          const float rstd = fmaf(y0, fmaf(-(0.5f * m) * y0, y0, 0.5f), y0);
           const float2 r2 = make_float2(rstd, rstd);
           const float* wk = s_wb + kind[u] * HD;
           const float* bk = s_wb + (2 + kind[u]) * HD;
@@ -253,9 +269,8 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
         }
       }
       if (kind[u] == 3) continue;
-      T* dst;
+      T* dst = out0[u] + (long long)t * tstr[u];
       if (kind[u] == 2) {  // v: the bits pass through
-        dst = reinterpret_cast<T*>(a.v_out) + (long long)t * kvh + (col[u] - qh - kvh);
         rawA[u].store(dst + oA);
         rawB[u].store(dst + oB);
         continue;
@@ -279,7 +294,6 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
         outA.w[p] = Act<T>::pack(xA[p].x, xA[p].y);
         outB.w[p] = Act<T>::pack(xB[p].x, xB[p].y);
       }
-      dst = kind[u] == 0 ? reinterpret_cast<T*>(a.q_out) + (long long)t * qh + col[u] : reinterpret_cast<T*>(a.k_out) + (long long)t * kvh + (col[u] - qh);
       outA.store(dst + oA);
       outB.store(dst + oB);
     }

@@ -72,6 +72,14 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       wait_timeout(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z), threadIdx.x, bar, parity);
   }
 }
+// The same bound by an iteration count (try_wait itself suspends for a while): two instructions per retry instead of a clock read,
+// for loops whose waiters compete for issue slots with the working warps.
+__device__ __forceinline__ void mbar_wait_light(uint32_t bar, uint32_t parity) {
+  unsigned n = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++n > (1u << 26)) wait_timeout(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z), threadIdx.x, bar, parity);
+  }
+}
 
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
