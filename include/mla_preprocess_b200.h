@@ -157,6 +157,16 @@ int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* 
                                   int32_t neox_style, int32_t act_dtype, void* stream);
 
 /*
+ * split_qkvgate_gemma_rmsnorm_rope (same reference module, split_qkv_rmsnorm_rope.py:441-747): the fused row is
+ * [q_0 | gate_0 | q_1 | gate_1 ... | k | v] (every q head followed by a gate head of head_dim), q and k heads are normalised with
+ * (1 + weight) and no bias, the first rope_dim dims rotated neox style, v and the gate heads copied.
+ * qkvgate act [batch, 2 q_hidden + 2 kv_hidden], gate_out act [batch, q_hidden]; the rest as above.
+ */
+int split_qkvgate_gemma_rmsnorm_rope_launch(const void* qkvgate, const void* sin, const void* cos, void* q_out, void* k_out, void* v_out,
+                                            void* gate_out, const void* q_weight, const void* k_weight, int64_t batch, int32_t q_hidden,
+                                            int32_t kv_hidden, int32_t head_dim, int32_t rope_dim, float eps, int32_t act_dtype, void* stream);
+
+/*
  * Slot producers: the ops that create and book-keep the slot_mapping this operator scatters by.  Integer work,
  * bit-exact against the reference tests' goldens; asynchronous on `stream`, device pointers, no scratch memory.
  *  - mlapo_alloc_extend: paged allocation of the new tokens of `batch` requests.  Replaces sglang::npu_kernel::alloc_extend

@@ -50,6 +50,18 @@ def main():
             rec[f"c{ci}_{name}"] = bits(t)
         rec[f"c{ci}_q"], rec[f"c{ci}_k"] = cq.astype(np.float32), ck.astype(np.float32)
         rec[f"c{ci}_rope_dim"] = np.array(rope_dim)
+    # the gated gemma variant through the reference test's golden_ref_split_qkvgate_gemma_rmsnorm_rope (:221-266), its own shape
+    qh, kvh, hd, bsz, rope_dim = 512, 256, 256, 12, 64
+    g = torch.Generator().manual_seed(200)
+    bf = lambda *s: torch.randn(*s, generator=g).to(torch.bfloat16)
+    x, qw, kw = bf(bsz, 2 * qh + 2 * kvh), bf(hd), bf(hd)
+    sin = torch.rand(bsz, 1, 1, rope_dim, generator=g).to(torch.bfloat16)
+    cos = torch.rand(bsz, 1, 1, rope_dim, generator=g).to(torch.bfloat16)
+    gq, gk, gv, gg = ref.golden_ref_split_qkvgate_gemma_rmsnorm_rope(x, sin, cos, qh, kvh, hd, rope_dim, eps, qw, kw)
+    for name, t in (("qkv", x), ("qw", qw), ("kw", kw), ("sin", sin), ("cos", cos), ("v", gv), ("gate", gg)):
+        rec[f"g_{name}"] = bits(t)
+    rec["g_q"], rec["g_k"] = gq.astype(np.float32), gk.astype(np.float32)
+    rec["g_meta"] = np.array([qh, kvh, hd, bsz, rope_dim])
     np.savez_compressed(OUT, **rec)
     print("wrote", OUT, os.path.getsize(OUT), "bytes")
 

@@ -9,7 +9,7 @@ import torch
 
 
 def split_qkv_rmsnorm_rope(qkv, sin, cos, q_hidden, kv_hidden, head_dim, eps=None, q_weight=None, k_weight=None, q_bias=None,
-                           k_bias=None, is_neox_style=True, with_scale=False):
+                           k_bias=None, is_neox_style=True, with_scale=False, gemma=False):
     """-> (q, k, v); with_scale adds (mq, mk), float32 arrays |rot * sin| + |n * cos| (|n| outside the rotated dims): the magnitude
     the result was summed from, which bounds a sound tolerance where the rotation cancels."""
     dt = qkv.dtype
@@ -24,7 +24,7 @@ def split_qkv_rmsnorm_rope(qkv, sin, cos, q_hidden, kv_hidden, head_dim, eps=Non
         n = part.reshape(b, -1, head_dim)
         if eps is not None:
             rstd = np.float32(1) / np.sqrt(np.mean(n * n, axis=-1, keepdims=True, dtype=np.float32) + np.float32(eps), dtype=np.float32)
-            n = n * rstd * f(w)
+            n = n * rstd * (f(w) + np.float32(1) if gemma else f(w))
             if bias is not None:
                 n = n + f(bias)
         rot = n[..., :rd]
@@ -44,3 +44,16 @@ def split_qkv_rmsnorm_rope(qkv, sin, cos, q_hidden, kv_hidden, head_dim, eps=Non
     k, mk = one(x[:, q_hidden:q_hidden + kv_hidden], k_weight, k_bias)
     v = qkv[:, q_hidden + kv_hidden:].clone()
     return (q, k, v, mq, mk) if with_scale else (q, k, v)
+
+
+def split_qkvgate_gemma_rmsnorm_rope(qkvgate, sin, cos, q_hidden, kv_hidden, head_dim, rope_dim, eps, q_weight, k_weight, with_scale=False):
+    """The gated variant (reference split_qkv_rmsnorm_rope.py:441-747, golden test_split_qkv_rmsnorm_rope.py:221-266): every q head
+    is followed by its gate head; q, k normalised with (1 + weight); -> (q, k, v, gate[, mq, mk])."""
+    b = qkvgate.shape[0]
+    qg = qkvgate[:, :2 * q_hidden].reshape(b, q_hidden // head_dim, 2, head_dim)
+    q_in = qg[:, :, 0].reshape(b, q_hidden)
+    gate = qg[:, :, 1].reshape(b, q_hidden).clone()
+    plain = torch.cat((q_in, qkvgate[:, 2 * q_hidden:]), dim=1).contiguous()
+    sin, cos = sin.reshape(b, rope_dim), cos.reshape(b, rope_dim)
+    out = split_qkv_rmsnorm_rope(plain, sin, cos, q_hidden, kv_hidden, head_dim, eps, q_weight, k_weight, None, None, True, with_scale, gemma=True)
+    return out[:3] + (gate,) + out[3:]

@@ -462,7 +462,7 @@ static cudaError_t split_vec_launch(const SplitQkvArgs& a, cudaStream_t st) {
     if (dev >= 0 && dev < 64) opted[dev] = true;
   }
   // CTAs per chunk index of the row, in proportion to the chunk's cost (its length plus a fixed part per token), 3 CTAs per SM
-  const long long row = a.q_hidden + 2LL * a.kv_hidden;
+  const long long row = (a.gated ? 2LL : 1LL) * a.q_hidden + 2LL * a.kv_hidden;
   const unsigned cpt = (unsigned)((row + G::CHUNK - 1) / G::CHUNK);
   const long long last_len = row - (long long)(cpt - 1) * G::CHUNK;
   const long long w_full = G::CHUNK + 512, w_last = last_len + 512;
@@ -648,10 +648,11 @@ int mlapo_assign_cache(void* out, const void* src, const void* dst_start, const 
   return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "assign_cache launch: %s", cudaGetErrorString(e));
 }
 
-int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* cos, void* q_out, void* k_out, void* v_out,
-                                  const void* q_weight, const void* k_weight, const void* q_bias, const void* k_bias, int64_t batch,
-                                  int32_t q_hidden, int32_t kv_hidden, int32_t head_dim, int32_t rope_dim, float eps, int32_t has_norm,
-                                  int32_t neox_style, int32_t act_dtype, void* stream) {
+// shared by split_qkv_rmsnorm_rope_launch and split_qkvgate_gemma_rmsnorm_rope_launch (gate_out != null: gated rows, gemma norm)
+static int split_qkv_impl(const void* qkv, const void* sin, const void* cos, void* q_out, void* k_out, void* v_out, void* gate_out,
+                          const void* q_weight, const void* k_weight, const void* q_bias, const void* k_bias, int64_t batch,
+                          int32_t q_hidden, int32_t kv_hidden, int32_t head_dim, int32_t rope_dim, float eps, int32_t has_norm,
+                          int32_t neox_style, int32_t gemma, int32_t act_dtype, void* stream) {
   if (!qkv || !sin || !cos || !q_out || !k_out || !v_out) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: null pointer");
   if (has_norm && (!q_weight || !k_weight)) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: eps given but no norm weights");
   if ((q_bias == nullptr) != (k_bias == nullptr)) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: q_bias and k_bias go together");
@@ -659,17 +660,18 @@ int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* 
       kv_hidden <= 0 || q_hidden % kv_hidden || rope_dim <= 0 || rope_dim > head_dim || (rope_dim & 1))
     return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: batch=%lld q_hidden=%d kv_hidden=%d head_dim=%d (power of two <= %d) rope_dim=%d",
                 (long long)batch, q_hidden, kv_hidden, head_dim, kSplitMaxHeadDim, rope_dim);
+  const int gated = gate_out != nullptr;
   SplitQkvArgs a{qkv, sin, cos, q_out, k_out, v_out, q_weight, k_weight, q_bias, k_bias, batch, q_hidden, kv_hidden, head_dim, rope_dim, eps,
-                 has_norm, neox_style};
+                 has_norm, neox_style, gate_out, gated, gemma};
   if (act_dtype != MLAPO_ACT_BF16 && act_dtype != MLAPO_ACT_FP16) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: tensors must be fp16 or bf16");
   const bool bf = act_dtype == MLAPO_ACT_BF16;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int vec = head_dim >= 512 ? 16 : 8;
   uintptr_t align = 0;
-  for (const void* p : {qkv, sin, cos, (const void*)q_out, (const void*)k_out, (const void*)v_out}) align |= reinterpret_cast<uintptr_t>(p);
+  for (const void* p : {qkv, sin, cos, (const void*)q_out, (const void*)k_out, (const void*)v_out, (const void*)gate_out}) align |= reinterpret_cast<uintptr_t>(p);
   if (head_dim >= 32 && rope_dim % vec == 0 && (align & 15) == 0) {
     // vector kernel; token indices are 32-bit in it, so a (hypothetical) larger batch goes in pieces
-    const long long row = q_hidden + 2LL * kv_hidden;
+    const long long row = (gated ? 2LL : 1LL) * q_hidden + 2LL * kv_hidden;
     const long long tok_per_launch = 1LL << 31;
     const size_t es = 2;
     for (long long t0 = 0; t0 < batch; t0 += tok_per_launch) {
@@ -681,6 +683,7 @@ int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* 
       c.q_out = static_cast<char*>(q_out) + t0 * q_hidden * es;
       c.k_out = static_cast<char*>(k_out) + t0 * kv_hidden * es;
       c.v_out = static_cast<char*>(v_out) + t0 * kv_hidden * es;
+      if (gated) c.gate_out = static_cast<char*>(gate_out) + t0 * q_hidden * es;
       c.batch = nb;
       cudaError_t le = cudaSuccess;
 #define MLAPO_SPLIT_CASE(HD)                                                                                                       \
@@ -696,7 +699,7 @@ int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* 
       if (le != cudaSuccess) return fail(MLAPO_ERR_CUDA, "split_qkv_rmsnorm_rope launch: %s", cudaGetErrorString(le));
     }
   } else {
-    const long long items = batch * ((q_hidden + 2LL * kv_hidden) / head_dim);
+    const long long items = batch * (((gated ? 2LL : 1LL) * q_hidden + 2LL * kv_hidden) / head_dim);
     long long blocks = (items + kSplitWarps - 1) / kSplitWarps;
     if (blocks > 148 * 32) blocks = 148 * 32;
     if (bf) split_qkv_scalar_kernel<__nv_bfloat16><<<(unsigned)blocks, kSplitWarps * 32, 0, st>>>(a);
@@ -704,6 +707,22 @@ int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* 
   }
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "split_qkv_rmsnorm_rope launch: %s", cudaGetErrorString(e));
+}
+
+int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* cos, void* q_out, void* k_out, void* v_out,
+                                  const void* q_weight, const void* k_weight, const void* q_bias, const void* k_bias, int64_t batch,
+                                  int32_t q_hidden, int32_t kv_hidden, int32_t head_dim, int32_t rope_dim, float eps, int32_t has_norm,
+                                  int32_t neox_style, int32_t act_dtype, void* stream) {
+  return split_qkv_impl(qkv, sin, cos, q_out, k_out, v_out, nullptr, q_weight, k_weight, q_bias, k_bias, batch, q_hidden, kv_hidden, head_dim,
+                        rope_dim, eps, has_norm, neox_style, 0, act_dtype, stream);
+}
+
+int split_qkvgate_gemma_rmsnorm_rope_launch(const void* qkvgate, const void* sin, const void* cos, void* q_out, void* k_out, void* v_out,
+                                            void* gate_out, const void* q_weight, const void* k_weight, int64_t batch, int32_t q_hidden,
+                                            int32_t kv_hidden, int32_t head_dim, int32_t rope_dim, float eps, int32_t act_dtype, void* stream) {
+  if (!gate_out) return fail(MLAPO_ERR_INVALID_ARG, "split_qkvgate_gemma_rmsnorm_rope: null gate_out");
+  return split_qkv_impl(qkvgate, sin, cos, q_out, k_out, v_out, gate_out, q_weight, k_weight, nullptr, nullptr, batch, q_hidden, kv_hidden,
+                        head_dim, rope_dim, eps, 1, 1, 1, act_dtype, stream);
 }
 
 static unsigned grid_for(long long work) {

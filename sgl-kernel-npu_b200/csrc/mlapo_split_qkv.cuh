@@ -33,6 +33,10 @@ struct SplitQkvArgs {
   int q_hidden, kv_hidden, head_dim, rope_dim;
   float eps;
   int has_norm, neox;
+  // split_qkvgate_gemma_rmsnorm_rope (same reference module, :441-747): every q head is followed by a gate head of the same
+  // width ([q_0 | gate_0 | q_1 | gate_1 ... | k | v]) that is copied to gate_out, and the norm multiplies by (1 + weight)
+  void* gate_out;        // act [batch, q_hidden] or null
+  int gated, gemma;
 };
 
 
@@ -108,7 +112,9 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
   __shared__ __align__(8) uint64_t s_full[S], s_empty[S];
   float* s_wb = reinterpret_cast<float*>(smem + S * G::STAGE_BYTES);  // [4][HD]: q weight, k weight, q bias, k bias
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qh = a.q_hidden, kvh = a.kv_hidden, row = qh + 2 * kvh;
+  const int qh = a.q_hidden, kvh = a.kv_hidden;
+  const int qspan = a.gated ? 2 * qh : qh;  // columns of the fused row before k
+  const int row = qspan + 2 * kvh;
   const int rd = a.rope_dim, half = rd / 2;
 
   const unsigned full_ctas = (chunks_per_tok - 1) * g_full;
@@ -123,9 +129,10 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
   }
   if (a.has_norm) {
     const bool has_bias = a.q_bias != nullptr;
+    const float w1 = a.gemma ? 1.f : 0.f;
     for (int i = threadIdx.x; i < HD; i += kSplitThreads) {
-      s_wb[i] = Act<T>::to_f(reinterpret_cast<const T*>(a.q_weight)[i]);
-      s_wb[HD + i] = Act<T>::to_f(reinterpret_cast<const T*>(a.k_weight)[i]);
+      s_wb[i] = Act<T>::to_f(reinterpret_cast<const T*>(a.q_weight)[i]) + w1;
+      s_wb[HD + i] = Act<T>::to_f(reinterpret_cast<const T*>(a.k_weight)[i]) + w1;
       s_wb[2 * HD + i] = has_bias ? Act<T>::to_f(reinterpret_cast<const T*>(a.q_bias)[i]) : 0.f;
       s_wb[3 * HD + i] = has_bias ? Act<T>::to_f(reinterpret_cast<const T*>(a.k_bias)[i]) : 0.f;
     }
@@ -141,7 +148,7 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
         const uint32_t dst = smem_u32(smem + stage * G::STAGE_BYTES);
         const int off = (int)ch * G::CHUNK;
         const uint32_t bytes = 2u * (uint32_t)(row - off < G::CHUNK ? row - off : G::CHUNK);
-        const bool rope_here = off < qh + kvh;  // a chunk of v heads only needs no sin / cos
+        const bool rope_here = off < qspan + kvh;  // a chunk of v heads only needs no sin / cos
         mbar_arrive_expect_tx(bar, bytes + (rope_here ? 4u * (uint32_t)rd : 0u));
         bulk_load_1d(dst, reinterpret_cast<const T*>(a.qkv) + (long long)t * row + off, bytes, bar);
         if (rope_here) {
@@ -170,7 +177,7 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
     oB = oA + W;
   }
   const int head_pos = (lane / L) * HD;  // of the lane's head inside the warp's span
-  // Where the lane's head of span u lies (kind: 0 q, 1 k, 2 v, 3 beyond the row) and where it goes: out0 is the output position
+  // Where the lane's head of span u lies (kind: 0 q, 1 k, 2 v or gate: copied, 3 beyond the row) and where it goes: out0 is the output position
   // for token 0, tstr the output's token stride.
   int kind[U], tstr[U];
   T* out0[U];
@@ -179,10 +186,17 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int c = off + (u * kSplitWarps + warp) * SPAN + head_pos;
-      kind[u] = c >= row ? 3 : c < qh ? 0 : c < qh + kvh ? 1 : 2;
-      tstr[u] = kind[u] == 0 ? qh : kvh;
-      out0[u] = kind[u] == 0 ? reinterpret_cast<T*>(a.q_out) + c
-                : kind[u] == 1 ? reinterpret_cast<T*>(a.k_out) + (c - qh) : reinterpret_cast<T*>(a.v_out) + (c - qh - kvh);
+      tstr[u] = kvh;
+      if (c >= row) { kind[u] = 3; out0[u] = nullptr; }
+      else if (c >= qspan + kvh) { kind[u] = 2; out0[u] = reinterpret_cast<T*>(a.v_out) + (c - qspan - kvh); }
+      else if (c >= qspan) { kind[u] = 1; out0[u] = reinterpret_cast<T*>(a.k_out) + (c - qspan); }
+      else {
+        tstr[u] = qh;
+        const int hh = c / HD;  // gated rows: even heads are q, odd heads their gates
+        const bool gate = a.gated && (hh & 1);
+        kind[u] = gate ? 2 : 0;
+        out0[u] = (gate ? reinterpret_cast<T*>(a.gate_out) : reinterpret_cast<T*>(a.q_out)) + (a.gated ? (hh >> 1) * HD : c);
+      }
     }
   }
   const uint32_t full0 = smem_u32(&s_full[0]), empty0 = smem_u32(&s_empty[0]);
@@ -200,7 +214,7 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
     }
     // this token's sin / cos for the lane's slices; the sign of the rotation is folded into sin
     float2 snA[PW], csA[PW], snB[PW], csB[PW];
-    if (in_rope && off < qh + kvh) {
+    if (in_rope && off < qspan + kvh) {
       const uint8_t* ssin = st + G::CHUNK * 2;
       const uint8_t* scos = ssin + 2 * HD;
       if constexpr (NEOX) {
@@ -270,7 +284,7 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
       }
       if (kind[u] == 3) continue;
       T* dst = out0[u] + (long long)t * tstr[u];
-      if (kind[u] == 2) {  // v: the bits pass through
+      if (kind[u] == 2) {  // v, gate: the bits pass through
         rawA[u].store(dst + oA);
         rawB[u].store(dst + oB);
         continue;
@@ -306,20 +320,31 @@ __global__ void __launch_bounds__(kSplitWarps * 32) split_qkv_scalar_kernel(Spli
   __shared__ float s_x[kSplitWarps][kSplitMaxHeadDim];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = a.q_hidden / a.head_dim, nk = a.kv_hidden / a.head_dim;
-  const int heads = nq + 2 * nk;
+  const int nqs = a.gated ? 2 * nq : nq;  // heads of the fused row before k (q and gate heads alternate when gated)
+  const int heads = nqs + 2 * nk;
   const long long total = a.batch * heads;
   const int hd = a.head_dim, rd = a.rope_dim, half = a.rope_dim / 2;
+  const float w1 = a.gemma ? 1.f : 0.f;
   float* x = s_x[warp];
   for (long long item = (long long)blockIdx.x * kSplitWarps + warp; item < total; item += (long long)gridDim.x * kSplitWarps) {
     const long long t = item / heads;
     const int h = (int)(item % heads);
-    const T* src = reinterpret_cast<const T*>(a.qkv) + t * (a.q_hidden + 2LL * a.kv_hidden) + (long long)h * hd;
+    const T* src = reinterpret_cast<const T*>(a.qkv) + t * heads * hd + (long long)h * hd;
     T* dst;
     const T *w = nullptr, *b = nullptr;
-    if (h < nq) { dst = reinterpret_cast<T*>(a.q_out) + t * a.q_hidden + (long long)h * hd; w = (const T*)a.q_weight; b = (const T*)a.q_bias; }
-    else if (h < nq + nk) { dst = reinterpret_cast<T*>(a.k_out) + t * a.kv_hidden + (long long)(h - nq) * hd; w = (const T*)a.k_weight; b = (const T*)a.k_bias; }
-    else {  // v: plain copy
-      dst = reinterpret_cast<T*>(a.v_out) + t * a.kv_hidden + (long long)(h - nq - nk) * hd;
+    bool copy = false;
+    if (h < nqs) {
+      const int hq = a.gated ? h >> 1 : h;
+      copy = a.gated && (h & 1);
+      dst = reinterpret_cast<T*>(copy ? a.gate_out : a.q_out) + t * a.q_hidden + (long long)hq * hd;
+      w = (const T*)a.q_weight; b = (const T*)a.q_bias;
+    } else if (h < nqs + nk) {
+      dst = reinterpret_cast<T*>(a.k_out) + t * a.kv_hidden + (long long)(h - nqs) * hd; w = (const T*)a.k_weight; b = (const T*)a.k_bias;
+    } else {
+      copy = true;
+      dst = reinterpret_cast<T*>(a.v_out) + t * a.kv_hidden + (long long)(h - nqs - nk) * hd;
+    }
+    if (copy) {  // v, gate
       for (int e = lane; e < hd; e += 32) dst[e] = src[e];
       continue;
     }
@@ -335,7 +360,8 @@ __global__ void __launch_bounds__(kSplitWarps * 32) split_qkv_scalar_kernel(Spli
       const float rstd = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(__fdiv_rn(ss, (float)hd), a.eps)));
       for (int e = lane; e < hd; e += 32) {
         const float n = __fmul_rn(x[e], rstd);
-        x[e] = b ? fmaf(n, Act<T>::to_f(w[e]), Act<T>::to_f(b[e])) : __fmul_rn(n, Act<T>::to_f(w[e]));
+        const float we = Act<T>::to_f(w[e]) + w1;
+        x[e] = b ? fmaf(n, we, Act<T>::to_f(b[e])) : __fmul_rn(n, we);
       }
     }
     __syncwarp();

@@ -53,7 +53,67 @@ def test_oracle_matches_reference_golden(ci):
     assert torch.equal(v, t["qkv"][:, qh + kvh:])
 
 
+def gated_fixture():
+    z = np.load(GOLD)
+    qh, kvh, hd, bsz, rd = (int(v) for v in z["g_meta"])
+    t = {k: bf(z[f"g_{k}"]) for k in ("qkv", "qw", "kw", "sin", "cos", "v", "gate")}
+    return qh, kvh, hd, bsz, rd, t, z["g_q"], z["g_k"]
+
+
+def within_summed_ulp(got, want_f32, scale, mant=8):
+    """|got - want| <= one ulp (mant bits of significand) of the magnitude the result was summed from"""
+    err = np.abs(got.float().cpu().numpy() - want_f32)
+    return bool((err <= np.exp2(np.floor(np.log2(np.maximum(scale, 1e-30))) - (mant - 1))).all())
+
+
+def test_oracle_gated_matches_reference_golden():
+    qh, kvh, hd, bsz, rd, t, gq, gk = gated_fixture()
+    q, k, v, gate = sq.split_qkvgate_gemma_rmsnorm_rope(t["qkv"], t["sin"], t["cos"], qh, kvh, hd, rd, 1e-6, t["qw"], t["kw"])
+    for got, want in ((q, gq), (k, gk)):
+        same, worst = close(got, want)
+        assert same >= 0.999 and worst <= 1, (same, worst)
+        np.testing.assert_allclose(got.float().numpy(), want, atol=5e-2)
+    assert torch.equal(v, t["v"].reshape(v.shape)) and torch.equal(gate, t["gate"].reshape(gate.shape))
+
+
 # ------------------------------------------------------------------------------------------------ CUDA
+@pytest.mark.gpu
+def test_cuda_gated_vs_golden_fixture(cuda_device):
+    from sgl_kernel_npu.norm.split_qkv_rmsnorm_rope import split_qkvgate_gemma_rmsnorm_rope
+    qh, kvh, hd, bsz, rd, t, gq, gk = gated_fixture()
+    d = {k: v.to(cuda_device) for k, v in t.items()}
+    q, k, v, gate = split_qkvgate_gemma_rmsnorm_rope(d["qkv"], d["sin"], d["cos"], qh, kvh, hd, rd, 1e-6, d["qw"], d["kw"])
+    *_, mq, mk = sq.split_qkvgate_gemma_rmsnorm_rope(t["qkv"], t["sin"], t["cos"], qh, kvh, hd, rd, 1e-6, t["qw"], t["kw"], with_scale=True)
+    for got, want, m in ((q, gq, mq), (k, gk, mk)):
+        assert close(got, want)[0] >= 0.995 and within_summed_ulp(got, want, m)
+        np.testing.assert_allclose(got.float().cpu().numpy(), want, atol=5e-2)
+    assert torch.equal(v.cpu(), t["v"].reshape(v.shape)) and torch.equal(gate.cpu(), t["gate"].reshape(gate.shape))
+
+
+# (batch, q_hidden, kv_hidden, head_dim, rope_dim, dtype): Qwen3-Next-like (partial rotary 0.25), a ragged chunking, the scalar kernel
+GATED_CASES = [(12, 512, 256, 256, 64, torch.bfloat16), (300, 4096, 512, 256, 64, torch.bfloat16), (33, 2048, 1024, 128, 128, torch.float16),
+               (5, 256, 128, 64, 20, torch.bfloat16), (4, 64, 32, 16, 8, torch.bfloat16)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", GATED_CASES, ids=lambda c: "b%d_q%d_kv%d_hd%d_r%d_%s" % (c[:5] + (str(c[5])[6:],)))
+def test_cuda_gated_vs_oracle(case, cuda_device):
+    from sgl_kernel_npu.norm.split_qkv_rmsnorm_rope import split_qkvgate_gemma_rmsnorm_rope
+    b, qh, kvh, hd, rd, dt = case
+    g = torch.Generator().manual_seed(b * 17 + hd + rd)
+    x = torch.randn(b, 2 * qh + 2 * kvh, generator=g).to(dt)
+    sin, cos = torch.rand(b, rd, generator=g).to(dt), torch.rand(b, rd, generator=g).to(dt)
+    qw, kw = torch.randn(hd, generator=g).to(dt), torch.randn(hd, generator=g).to(dt)
+    wq, wk, wv, wg, mq, mk = sq.split_qkvgate_gemma_rmsnorm_rope(x, sin, cos, qh, kvh, hd, rd, 1e-6, qw, kw, with_scale=True)
+    dev = lambda t: t.to(cuda_device)
+    q, k, v, gate = split_qkvgate_gemma_rmsnorm_rope(dev(x), dev(sin), dev(cos), qh, kvh, hd, rd, 1e-6, dev(qw), dev(kw))
+    mant = 8 if dt == torch.bfloat16 else 11
+    for got, want, m in ((q, wq, mq), (k, wk, mk)):
+        assert close(got, want)[0] >= 0.99
+        assert within_summed_ulp(got, want.float().numpy(), m, mant)
+    assert torch.equal(v.cpu(), wv) and torch.equal(gate.cpu(), wg)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("ci", [0, 1])
 def test_cuda_vs_golden_fixture(ci, cuda_device):
