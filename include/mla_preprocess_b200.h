@@ -157,6 +157,18 @@ int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* 
                                   int32_t neox_style, int32_t act_dtype, void* stream);
 
 /*
+ * split_qkv_rmsnorm_rope_pos_cache_half_npu (python/sgl_kernel_npu/sgl_kernel_npu/norm/split_qkv_rmsnorm_rope_pos_cache_half_npu.py:232-407):
+ * as split_qkv_rmsnorm_rope, neox style, but cos / sin are row clamp(positions[t], 0, max_seq - 1) of cos_sin_cache
+ * [max_seq, cache_stride >= rope_dim] laid out [cos(rope_dim/2) | sin(rope_dim/2)], tensor dtype or float32; cast_norm = 1 rounds the
+ * normalised value to the tensor dtype before the rotation (the reference's cast_norm_to_bf16, its default).
+ */
+int split_qkv_rmsnorm_rope_pos_cache_launch(const void* qkv, const void* positions, int32_t positions_are_int64, const void* cos_sin_cache,
+                                            int32_t cache_is_f32, int64_t cache_stride, int32_t max_seq, void* q_out, void* k_out, void* v_out,
+                                            const void* q_weight, const void* k_weight, const void* q_bias, const void* k_bias, int64_t batch,
+                                            int32_t q_hidden, int32_t kv_hidden, int32_t head_dim, int32_t rope_dim, float eps, int32_t has_norm,
+                                            int32_t cast_norm, int32_t act_dtype, void* stream);
+
+/*
  * split_qkvgate_gemma_rmsnorm_rope (same reference module, split_qkv_rmsnorm_rope.py:441-747): the fused row is
  * [q_0 | gate_0 | q_1 | gate_1 ... | k | v] (every q head followed by a gate head of head_dim), q and k heads are normalised with
  * (1 + weight) and no bias, the first rope_dim dims rotated neox style, v and the gate heads copied.

@@ -26,6 +26,18 @@ def load():
     return mod
 
 
+def load_pos_cache_test():
+    for m in ("sglang", "sglang.srt"):
+        sys.modules.setdefault(m, types.ModuleType(m))
+    u = types.ModuleType("sglang.srt.utils")
+    u.is_npu = lambda: False
+    sys.modules["sglang.srt.utils"] = u
+    spec = importlib.util.spec_from_file_location("ref_test_pos_cache", os.path.join(os.path.dirname(REF), "test_split_qkv_rmsnorm_rope_pos_cache_half_npu.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def bits(t):
     return t.contiguous().view(torch.int16).numpy().view(np.uint16)
 
@@ -62,6 +74,22 @@ def main():
         rec[f"g_{name}"] = bits(t)
     rec["g_q"], rec["g_k"] = gq.astype(np.float32), gk.astype(np.float32)
     rec["g_meta"] = np.array([qh, kvh, hd, bsz, rope_dim])
+    # the position-cache variant through the reference test's golden_split_qkv_rmsnorm_rope_pos_cache_half
+    # (test_split_qkv_rmsnorm_rope_pos_cache_half_npu.py:73-125; it computes in bf16, op by op) and its cache builder (:14-33)
+    pc = load_pos_cache_test()
+    for ci, (bsz, qh, kvh, hd, rope_dim, norm) in enumerate(((12, 1024, 256, 128, 128, True), (8, 1024, 256, 128, 64, True), (8, 512, 256, 64, 64, False))):
+        g = torch.Generator().manual_seed(300 + ci)
+        max_pos = 128
+        x = torch.randn(bsz, qh + 2 * kvh, generator=g).to(torch.bfloat16)
+        pos = torch.randint(0, max_pos, (bsz,), generator=g, dtype=torch.int64)
+        cache = pc._make_cos_sin_cache(max_pos, rope_dim, 10000.0, torch.float32, torch.device("cpu"))
+        qw, kw = torch.randn(hd, generator=g).to(torch.bfloat16), torch.randn(hd, generator=g).to(torch.bfloat16)
+        gq, gk, gv = pc.golden_split_qkv_rmsnorm_rope_pos_cache_half(x, pos, cache, qh, kvh, hd, rope_dim, eps if norm else None,
+                                                                     qw if norm else None, kw if norm else None, use_qk_norm=norm)
+        for name, t in (("qkv", x), ("qw", qw), ("kw", kw), ("q", gq), ("k", gk), ("v", gv)):
+            rec[f"p{ci}_{name}"] = bits(t)
+        rec[f"p{ci}_pos"], rec[f"p{ci}_cache"] = pos.numpy(), cache.numpy()
+        rec[f"p{ci}_meta"] = np.array([bsz, qh, kvh, hd, rope_dim, int(norm)])
     np.savez_compressed(OUT, **rec)
     print("wrote", OUT, os.path.getsize(OUT), "bytes")
 

@@ -9,7 +9,7 @@ import torch
 
 
 def split_qkv_rmsnorm_rope(qkv, sin, cos, q_hidden, kv_hidden, head_dim, eps=None, q_weight=None, k_weight=None, q_bias=None,
-                           k_bias=None, is_neox_style=True, with_scale=False, gemma=False):
+                           k_bias=None, is_neox_style=True, with_scale=False, gemma=False, cast_norm=False):
     """-> (q, k, v); with_scale adds (mq, mk), float32 arrays |rot * sin| + |n * cos| (|n| outside the rotated dims): the magnitude
     the result was summed from, which bounds a sound tolerance where the rotation cancels."""
     dt = qkv.dtype
@@ -27,6 +27,8 @@ def split_qkv_rmsnorm_rope(qkv, sin, cos, q_hidden, kv_hidden, head_dim, eps=Non
             n = n * rstd * (f(w) + np.float32(1) if gemma else f(w))
             if bias is not None:
                 n = n + f(bias)
+            if cast_norm:  # the rotation starts from the value as the tensor dtype holds it
+                n = torch.from_numpy(n).to(dt).to(torch.float32).numpy()
         rot = n[..., :rd]
         if is_neox_style:
             cat = np.concatenate((-rot[..., h:], rot[..., :h]), axis=-1)
@@ -57,3 +59,26 @@ def split_qkvgate_gemma_rmsnorm_rope(qkvgate, sin, cos, q_hidden, kv_hidden, hea
     sin, cos = sin.reshape(b, rope_dim), cos.reshape(b, rope_dim)
     out = split_qkv_rmsnorm_rope(plain, sin, cos, q_hidden, kv_hidden, head_dim, eps, q_weight, k_weight, None, None, True, with_scale, gemma=True)
     return out[:3] + (gate,) + out[3:]
+
+
+def split_qkv_rmsnorm_rope_pos_cache_half(qkv, positions, cos_sin_cache, q_hidden, kv_hidden, head_dim, eps=None, q_weight=None, k_weight=None,
+                                          q_bias=None, k_bias=None, rope_dim=None, cast_norm=True, with_scale=False):
+    """The position-cache variant (reference split_qkv_rmsnorm_rope_pos_cache_half_npu.py:25-230): cos / sin are row
+    clamp(positions[t], 0, max_seq - 1) of the cache [max_seq, rope_dim] = [cos(rope_dim/2) | sin(rope_dim/2)], one value per neox pair;
+    with cast_norm the normalised value is rounded to the tensor dtype before the rotation; fp32 arithmetic, one rounding at the store."""
+    rd = head_dim if rope_dim is None else rope_dim
+    p = positions.to(torch.int64).clamp(0, cos_sin_cache.shape[0] - 1)
+    rows = cos_sin_cache.to(torch.float32)[p][:, :rd]
+    cos, sin = rows[:, :rd // 2], rows[:, rd // 2:]
+    # the same restatement as above with cos / sin repeated over both halves; they stay float32 (a float32 cache is not rounded)
+    return split_qkv_rmsnorm_rope(qkv, _F32(torch.cat((sin, sin), 1)), _F32(torch.cat((cos, cos), 1)), q_hidden, kv_hidden, head_dim, eps,
+                                  q_weight, k_weight, q_bias, k_bias, True, with_scale, cast_norm=cast_norm and eps is not None)
+
+
+class _F32:
+    """wraps a float32 tensor so that the restatement's `.to(float32).numpy()` and `.shape` see it unchanged"""
+    def __init__(self, t):
+        self.t, self.shape = t, t.shape
+
+    def to(self, _):
+        return self.t

@@ -648,12 +648,21 @@ int mlapo_assign_cache(void* out, const void* src, const void* dst_start, const 
   return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "assign_cache launch: %s", cudaGetErrorString(e));
 }
 
-// shared by split_qkv_rmsnorm_rope_launch and split_qkvgate_gemma_rmsnorm_rope_launch (gate_out != null: gated rows, gemma norm)
+struct SplitPosCache {
+  const void* positions;
+  const void* cache;
+  long long cache_stride;
+  int pos_i64, cache_f32, max_seq, cast_norm;
+};
+
+// shared by the split_qkv launch entry points (gate_out != null: gated rows, gemma norm; pc != null: cos / sin from a position cache)
 static int split_qkv_impl(const void* qkv, const void* sin, const void* cos, void* q_out, void* k_out, void* v_out, void* gate_out,
                           const void* q_weight, const void* k_weight, const void* q_bias, const void* k_bias, int64_t batch,
                           int32_t q_hidden, int32_t kv_hidden, int32_t head_dim, int32_t rope_dim, float eps, int32_t has_norm,
-                          int32_t neox_style, int32_t gemma, int32_t act_dtype, void* stream) {
-  if (!qkv || !sin || !cos || !q_out || !k_out || !v_out) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: null pointer");
+                          int32_t neox_style, int32_t gemma, int32_t act_dtype, void* stream, const SplitPosCache* pc = nullptr) {
+  if (!qkv || !q_out || !k_out || !v_out || (!pc && (!sin || !cos))) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: null pointer");
+  if (pc && (!pc->positions || !pc->cache || pc->max_seq < 1 || pc->cache_stride < rope_dim))
+    return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope_pos_cache: positions / cos_sin_cache [max_seq >= 1, >= rope_dim]");
   if (has_norm && (!q_weight || !k_weight)) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: eps given but no norm weights");
   if ((q_bias == nullptr) != (k_bias == nullptr)) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: q_bias and k_bias go together");
   if (batch <= 0 || head_dim < 2 || head_dim > kSplitMaxHeadDim || (head_dim & (head_dim - 1)) || q_hidden % head_dim || kv_hidden % head_dim ||
@@ -662,13 +671,18 @@ static int split_qkv_impl(const void* qkv, const void* sin, const void* cos, voi
                 (long long)batch, q_hidden, kv_hidden, head_dim, kSplitMaxHeadDim, rope_dim);
   const int gated = gate_out != nullptr;
   SplitQkvArgs a{qkv, sin, cos, q_out, k_out, v_out, q_weight, k_weight, q_bias, k_bias, batch, q_hidden, kv_hidden, head_dim, rope_dim, eps,
-                 has_norm, neox_style, gate_out, gated, gemma};
+                 has_norm, neox_style, gate_out, gated, gemma, nullptr, nullptr, 0, 0, 0, 0, 0};
+  if (pc) {
+    a.positions = pc->positions; a.cache = pc->cache; a.cache_stride = pc->cache_stride;
+    a.pos_i64 = pc->pos_i64; a.cache_f32 = pc->cache_f32; a.max_seq = pc->max_seq; a.cast_norm = pc->cast_norm && has_norm;
+  }
   if (act_dtype != MLAPO_ACT_BF16 && act_dtype != MLAPO_ACT_FP16) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: tensors must be fp16 or bf16");
   const bool bf = act_dtype == MLAPO_ACT_BF16;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int vec = head_dim >= 512 ? 16 : 8;
   uintptr_t align = 0;
   for (const void* p : {qkv, sin, cos, (const void*)q_out, (const void*)k_out, (const void*)v_out, (const void*)gate_out}) align |= reinterpret_cast<uintptr_t>(p);
+  if (pc) align |= reinterpret_cast<uintptr_t>(pc->cache) | (uintptr_t)(pc->cache_stride * (pc->cache_f32 ? 4 : 2));  // bulk copies of cache rows
   if (head_dim >= 32 && rope_dim % vec == 0 && (align & 15) == 0) {
     // vector kernel; token indices are 32-bit in it, so a (hypothetical) larger batch goes in pieces
     const long long row = (gated ? 2LL : 1LL) * q_hidden + 2LL * kv_hidden;
@@ -678,8 +692,11 @@ static int split_qkv_impl(const void* qkv, const void* sin, const void* cos, voi
       const long long nb = batch - t0 < tok_per_launch ? batch - t0 : tok_per_launch;
       SplitQkvArgs c = a;
       c.qkv = static_cast<const char*>(qkv) + t0 * row * es;
-      c.sin = static_cast<const char*>(sin) + t0 * rope_dim * es;
-      c.cos = static_cast<const char*>(cos) + t0 * rope_dim * es;
+      if (pc) c.positions = static_cast<const char*>(pc->positions) + t0 * (pc->pos_i64 ? 8 : 4);
+      else {
+        c.sin = static_cast<const char*>(sin) + t0 * rope_dim * es;
+        c.cos = static_cast<const char*>(cos) + t0 * rope_dim * es;
+      }
       c.q_out = static_cast<char*>(q_out) + t0 * q_hidden * es;
       c.k_out = static_cast<char*>(k_out) + t0 * kv_hidden * es;
       c.v_out = static_cast<char*>(v_out) + t0 * kv_hidden * es;
@@ -715,6 +732,16 @@ int split_qkv_rmsnorm_rope_launch(const void* qkv, const void* sin, const void* 
                                   int32_t neox_style, int32_t act_dtype, void* stream) {
   return split_qkv_impl(qkv, sin, cos, q_out, k_out, v_out, nullptr, q_weight, k_weight, q_bias, k_bias, batch, q_hidden, kv_hidden, head_dim,
                         rope_dim, eps, has_norm, neox_style, 0, act_dtype, stream);
+}
+
+int split_qkv_rmsnorm_rope_pos_cache_launch(const void* qkv, const void* positions, int32_t positions_are_int64, const void* cos_sin_cache,
+                                            int32_t cache_is_f32, int64_t cache_stride, int32_t max_seq, void* q_out, void* k_out, void* v_out,
+                                            const void* q_weight, const void* k_weight, const void* q_bias, const void* k_bias, int64_t batch,
+                                            int32_t q_hidden, int32_t kv_hidden, int32_t head_dim, int32_t rope_dim, float eps, int32_t has_norm,
+                                            int32_t cast_norm, int32_t act_dtype, void* stream) {
+  const SplitPosCache pc{positions, cos_sin_cache, cache_stride, positions_are_int64, cache_is_f32, max_seq, cast_norm};
+  return split_qkv_impl(qkv, nullptr, nullptr, q_out, k_out, v_out, nullptr, q_weight, k_weight, q_bias, k_bias, batch, q_hidden, kv_hidden,
+                        head_dim, rope_dim, eps, has_norm, 1, 0, act_dtype, stream, &pc);
 }
 
 int split_qkvgate_gemma_rmsnorm_rope_launch(const void* qkvgate, const void* sin, const void* cos, void* q_out, void* k_out, void* v_out,

@@ -37,6 +37,13 @@ struct SplitQkvArgs {
   // width ([q_0 | gate_0 | q_1 | gate_1 ... | k | v]) that is copied to gate_out, and the norm multiplies by (1 + weight)
   void* gate_out;        // act [batch, q_hidden] or null
   int gated, gemma;
+  // split_qkv_rmsnorm_rope_pos_cache_half_npu (reference norm/split_qkv_rmsnorm_rope_pos_cache_half_npu.py:25-230): cos / sin come
+  // from row clamp(positions[t], 0, max_seq - 1) of a cache [max_seq, rope_dim] laid out [cos(rope_dim/2) | sin(rope_dim/2)] (one
+  // value per neox pair), and the normalised value may be rounded to the tensor dtype before the rotation (cast_norm)
+  const void* positions;  // int32 / int64 [batch], or null: sin / cos above are used
+  const void* cache;      // act or f32 [max_seq, cache_stride]
+  long long cache_stride; // elements
+  int pos_i64, cache_f32, max_seq, cast_norm;
 };
 
 
@@ -149,9 +156,14 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
         const int off = (int)ch * G::CHUNK;
         const uint32_t bytes = 2u * (uint32_t)(row - off < G::CHUNK ? row - off : G::CHUNK);
         const bool rope_here = off < qspan + kvh;  // a chunk of v heads only needs no sin / cos
-        mbar_arrive_expect_tx(bar, bytes + (rope_here ? 4u * (uint32_t)rd : 0u));
+        const uint32_t cs_bytes = !rope_here ? 0u : a.positions ? (a.cache_f32 ? 4u : 2u) * (uint32_t)rd : 4u * (uint32_t)rd;
+        mbar_arrive_expect_tx(bar, bytes + cs_bytes);
         bulk_load_1d(dst, reinterpret_cast<const T*>(a.qkv) + (long long)t * row + off, bytes, bar);
-        if (rope_here) {
+        if (rope_here && a.positions) {  // one cache row [cos | sin]
+          long long p = a.pos_i64 ? reinterpret_cast<const long long*>(a.positions)[t] : (long long)reinterpret_cast<const int*>(a.positions)[t];
+          p = p < 0 ? 0 : p >= a.max_seq ? a.max_seq - 1 : p;
+          bulk_load_1d(dst + G::CHUNK * 2, reinterpret_cast<const uint8_t*>(a.cache) + p * a.cache_stride * (a.cache_f32 ? 4 : 2), cs_bytes, bar);
+        } else if (rope_here) {
           bulk_load_1d(dst + G::CHUNK * 2, reinterpret_cast<const T*>(a.sin) + (long long)t * rd, 2u * (uint32_t)rd, bar);
           bulk_load_1d(dst + G::CHUNK * 2 + 2 * HD, reinterpret_cast<const T*>(a.cos) + (long long)t * rd, 2u * (uint32_t)rd, bar);
         }
@@ -217,7 +229,28 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
     if (in_rope && off < qspan + kvh) {
       const uint8_t* ssin = st + G::CHUNK * 2;
       const uint8_t* scos = ssin + 2 * HD;
-      if constexpr (NEOX) {
+      if (NEOX && a.positions) {  // cache row in the stage: cos then sin, one value per pair -> both slices use the same
+        if (a.cache_f32) {
+          const float* cf = reinterpret_cast<const float*>(ssin);
+#pragma unroll
+          for (int p = 0; p < PW; ++p) {
+            const float2 c = *reinterpret_cast<const float2*>(cf + oA + 2 * p), sv = *reinterpret_cast<const float2*>(cf + half + oA + 2 * p);
+            csA[p] = csB[p] = c;
+            snA[p] = make_float2(-sv.x, -sv.y);
+            snB[p] = sv;
+          }
+        } else {
+          Raw16<W> rc, rs;
+          rc.load(ssin + oA * 2);
+          rs.load(ssin + (half + oA) * 2);
+#pragma unroll
+          for (int p = 0; p < PW; ++p) {
+            csA[p] = csB[p] = make_float2(Act<T>::lo(rc.w[p]), Act<T>::hi(rc.w[p]));
+            snB[p] = make_float2(Act<T>::lo(rs.w[p]), Act<T>::hi(rs.w[p]));
+            snA[p] = make_float2(-snB[p].x, -snB[p].y);
+          }
+        }
+      } else if constexpr (NEOX) {
         Raw16<W> r;
         r.load(ssin + oA * 2);
 #pragma unroll
@@ -279,6 +312,14 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
             b4 = *reinterpret_cast<const float4*>(bk + oB + 2 * p);
             xB[p] = fma2(mul2(xB[p], r2), make_float2(w4.x, w4.y), make_float2(b4.x, b4.y));
             xB[p + 1] = fma2(mul2(xB[p + 1], r2), make_float2(w4.z, w4.w), make_float2(b4.z, b4.w));
+          }
+          if (a.cast_norm) {  // the rotation then starts from the normalised value as the tensor dtype holds it
+#pragma unroll
+            for (int p = 0; p < PW; ++p) {
+              const uint32_t wa = Act<T>::pack(xA[p].x, xA[p].y), wb = Act<T>::pack(xB[p].x, xB[p].y);
+              xA[p] = make_float2(Act<T>::lo(wa), Act<T>::hi(wa));
+              xB[p] = make_float2(Act<T>::lo(wb), Act<T>::hi(wb));
+            }
           }
         }
       }
@@ -361,17 +402,28 @@ __global__ void __launch_bounds__(kSplitWarps * 32) split_qkv_scalar_kernel(Spli
       for (int e = lane; e < hd; e += 32) {
         const float n = __fmul_rn(x[e], rstd);
         const float we = Act<T>::to_f(w[e]) + w1;
-        x[e] = b ? fmaf(n, we, Act<T>::to_f(b[e])) : __fmul_rn(n, we);
+        const float y = b ? fmaf(n, we, Act<T>::to_f(b[e])) : __fmul_rn(n, we);
+        x[e] = a.cast_norm ? Act<T>::round(y) : y;
       }
     }
     __syncwarp();
     const T* sn = reinterpret_cast<const T*>(a.sin) + t * rd;
     const T* cs = reinterpret_cast<const T*>(a.cos) + t * rd;
+    long long crow = 0;  // position-cache mode: element offset of the token's cache row
+    if (a.positions) {
+      long long p = a.pos_i64 ? reinterpret_cast<const long long*>(a.positions)[t] : (long long)reinterpret_cast<const int*>(a.positions)[t];
+      crow = (p < 0 ? 0 : p >= a.max_seq ? a.max_seq - 1 : p) * a.cache_stride;
+    }
     for (int e = lane; e < hd; e += 32) {
       float o = x[e];
       if (e < rd) {
         float rot, s, c;
-        if (a.neox) {
+        if (a.positions) {  // neox, one cache value per pair
+          rot = e < half ? -x[e + half] : x[e - half];
+          const long long ci = crow + (e < half ? e : e - half);
+          c = a.cache_f32 ? reinterpret_cast<const float*>(a.cache)[ci] : Act<T>::to_f(reinterpret_cast<const T*>(a.cache)[ci]);
+          s = a.cache_f32 ? reinterpret_cast<const float*>(a.cache)[ci + half] : Act<T>::to_f(reinterpret_cast<const T*>(a.cache)[ci + half]);
+        } else if (a.neox) {
           rot = e < half ? -x[e + half] : x[e - half];
           s = Act<T>::to_f(sn[e]);
           c = Act<T>::to_f(cs[e]);

@@ -76,7 +76,88 @@ def test_oracle_gated_matches_reference_golden():
     assert torch.equal(v, t["v"].reshape(v.shape)) and torch.equal(gate, t["gate"].reshape(gate.shape))
 
 
+def pos_fixture(ci):
+    z = np.load(GOLD)
+    bsz, qh, kvh, hd, rd, norm = (int(v) for v in z[f"p{ci}_meta"])
+    t = {k: bf(z[f"p{ci}_{k}"]) for k in ("qkv", "qw", "kw", "q", "k", "v")}
+    t["pos"], t["cache"] = torch.from_numpy(z[f"p{ci}_pos"]), torch.from_numpy(z[f"p{ci}_cache"])
+    return bsz, qh, kvh, hd, rd, bool(norm), t
+
+
+def assert_ref_tolerance(got, want):
+    """the reference test's own bound (_assert_close_fp32, test_split_qkv_rmsnorm_rope_pos_cache_half_npu.py:128-136, :196-198): its
+    golden computes op by op in bf16, so it is not closer than this to fp32 arithmetic"""
+    torch.testing.assert_close(got.float().cpu(), want.float().reshape(got.shape), atol=5e-2, rtol=5e-3)
+
+
+@pytest.mark.parametrize("ci", [0, 1, 2])
+def test_oracle_pos_cache_matches_reference_golden(ci):
+    bsz, qh, kvh, hd, rd, norm, t = pos_fixture(ci)
+    q, k, v = sq.split_qkv_rmsnorm_rope_pos_cache_half(t["qkv"], t["pos"], t["cache"], qh, kvh, hd, 1e-6 if norm else None,
+                                                       t["qw"] if norm else None, t["kw"] if norm else None, rope_dim=rd)
+    assert_ref_tolerance(q, t["q"])
+    assert_ref_tolerance(k, t["k"])
+    assert torch.equal(v, t["v"].reshape(v.shape))
+    # and most elements agree to the bit although the golden rounds after every operation
+    assert close(q, t["q"].reshape(q.shape))[0] > 0.6
+
+
 # ------------------------------------------------------------------------------------------------ CUDA
+@pytest.mark.gpu
+@pytest.mark.parametrize("ci", [0, 1, 2])
+def test_cuda_pos_cache_vs_golden_fixture(ci, cuda_device):
+    from sgl_kernel_npu.norm.split_qkv_rmsnorm_rope_pos_cache_half_npu import split_qkv_rmsnorm_rope_pos_cache_half_npu as fn
+    bsz, qh, kvh, hd, rd, norm, t = pos_fixture(ci)
+    d = {k: v.to(cuda_device) for k, v in t.items()}
+    q, k, v = fn(d["qkv"], d["pos"], d["cache"], qh, kvh, hd, eps=1e-6 if norm else None, q_weight=d["qw"] if norm else None,
+                 k_weight=d["kw"] if norm else None, rope_dim=rd)
+    assert_ref_tolerance(q, t["q"])
+    assert_ref_tolerance(k, t["k"])
+    assert torch.equal(v.cpu(), t["v"].reshape(v.shape))
+
+
+# (batch, q_hidden, kv_hidden, head_dim, rope_dim, norm, bias, cast, cache dtype, positions dtype, input dtype)
+POS_CASES = [
+    (12, 6144, 1024, 128, 128, True, False, True, torch.float32, torch.int64, torch.bfloat16),     # the reference test's shapes
+    (8, 4096, 1024, 128, 64, True, False, True, torch.float32, torch.int64, torch.bfloat16),
+    (300, 2048, 512, 128, 64, True, True, False, torch.bfloat16, torch.int32, torch.bfloat16),
+    (9, 1024, 512, 512, 128, True, True, True, torch.float16, torch.int32, torch.float16),
+    (7, 512, 256, 64, 64, False, False, True, torch.float32, torch.int64, torch.bfloat16),
+    (5, 256, 128, 64, 20, True, True, True, torch.float32, torch.int64, torch.bfloat16),          # scalar kernel
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", POS_CASES, ids=lambda c: "b%d_q%d_kv%d_hd%d_r%d_%d%d%d_%s_%s_%s" % (
+    c[:5] + tuple(int(x) for x in c[5:8]) + tuple(str(x)[6:] for x in c[8:])))
+def test_cuda_pos_cache_vs_oracle(case, cuda_device):
+    from sgl_kernel_npu.norm.split_qkv_rmsnorm_rope_pos_cache_half_npu import split_qkv_rmsnorm_rope_pos_cache_half_npu as fn
+    b, qh, kvh, hd, rd, norm, bias, cast, cdt, pdt, dt = case
+    g = torch.Generator().manual_seed(b * 7 + hd + rd)
+    x = torch.randn(b, qh + 2 * kvh, generator=g).to(dt)
+    max_seq = 97
+    cache = (torch.rand(max_seq, rd, generator=g) * 2 - 1).to(cdt)
+    pos = torch.randint(-3, max_seq + 3, (b,), generator=g).to(pdt)   # a few positions outside the cache: clamped
+    rn = lambda: torch.randn(hd, generator=g).to(dt)
+    qw, kw = (rn(), rn()) if norm else (None, None)
+    qb, kb = (rn(), rn()) if norm and bias else (None, None)
+    eps = 1e-6 if norm else None
+    wq, wk, wv, mq, mk = sq.split_qkv_rmsnorm_rope_pos_cache_half(x, pos, cache, qh, kvh, hd, eps, qw, kw, qb, kb, rd, cast, with_scale=True)
+    dev = lambda t: None if t is None else t.to(cuda_device)
+    q, k, v = fn(dev(x), dev(pos), dev(cache), qh, kvh, hd, eps=eps, q_weight=dev(qw), k_weight=dev(kw), q_bias=dev(qb), k_bias=dev(kb),
+                 rope_dim=rd, cast_norm_to_bf16=cast)
+    mant = 8 if dt == torch.bfloat16 else 11
+    for got, want, m in ((q, wq, mq), (k, wk, mk)):
+        # with cast_norm a 1-ulp difference of the fp32 norm can flip the intermediate rounding: fewer identical elements then
+        assert close(got, want)[0] >= (0.97 if cast and norm else 0.99)
+        lim = 2 if cast and norm else 1
+        err = np.abs(got.float().cpu().numpy() - want.float().numpy())
+        assert (err <= lim * np.exp2(np.floor(np.log2(np.maximum(m, 1e-30))) - (mant - 1))).all()
+    assert torch.equal(v.cpu(), wv)
+    with pytest.raises(ValueError):
+        fn(dev(x), dev(pos), dev(cache), qh, kvh, hd, eps=1e-6, q_weight=dev(rn())[:hd // 2], k_weight=dev(rn()), rope_dim=rd)
+
+
 @pytest.mark.gpu
 def test_cuda_gated_vs_golden_fixture(cuda_device):
     from sgl_kernel_npu.norm.split_qkv_rmsnorm_rope import split_qkvgate_gemma_rmsnorm_rope
