@@ -169,6 +169,19 @@ int split_qkv_rmsnorm_rope_pos_cache_launch(const void* qkv, const void* positio
                                             int32_t cast_norm, int32_t act_dtype, void* stream);
 
 /*
+ * split_qkv_rmsnorm_mrope (python/sgl_kernel_npu/sgl_kernel_npu/norm/split_qkv_rmsnorm_mrope.py:335-419, function
+ * triton_split_qkv_rmsnorm_mrope): as split_qkv_rmsnorm_rope with weight (+ bias), neox rotation, optional gate heads (gate_out
+ * non-null: rows [q_0 | gate_0 | ... | k | v]); cos_sin is [3 (t, h, w), batch, rope_dim] with rows [cos | sin], tensor dtype or
+ * float32, and pair i takes the t, h or w row by mrope section (contiguous sections, or interleaved: i % 3 == 1 and i <= 3 h -> h,
+ * i % 3 == 2 and i <= 3 w -> w, else t).  workspace: [batch, rope_dim] elements of cos_sin's type, device memory.
+ */
+int split_qkv_rmsnorm_mrope_launch(const void* qkv, const void* cos_sin, int32_t cos_sin_is_f32, void* workspace, void* q_out, void* k_out,
+                                   void* v_out, void* gate_out, const void* q_weight, const void* k_weight, const void* q_bias,
+                                   const void* k_bias, int64_t batch, int32_t num_q_heads, int32_t num_kv_heads, int32_t head_size,
+                                   int32_t rope_dim, float eps, int32_t section_t, int32_t section_h, int32_t section_w,
+                                   int32_t is_interleaved, int32_t act_dtype, void* stream);
+
+/*
  * split_qkvgate_gemma_rmsnorm_rope (same reference module, split_qkv_rmsnorm_rope.py:441-747): the fused row is
  * [q_0 | gate_0 | q_1 | gate_1 ... | k | v] (every q head followed by a gate head of head_dim), q and k heads are normalised with
  * (1 + weight) and no bias, the first rope_dim dims rotated neox style, v and the gate heads copied.

@@ -38,6 +38,18 @@ def load_pos_cache_test():
     return mod
 
 
+def load_named(test_file, module, attr):
+    for m in ("torch_npu", "sgl_kernel_npu", "sgl_kernel_npu.norm"):
+        sys.modules.setdefault(m, types.ModuleType(m))
+    stub = types.ModuleType(module)
+    setattr(stub, attr, None)
+    sys.modules[module] = stub
+    spec = importlib.util.spec_from_file_location("ref_" + test_file[:-3], os.path.join(os.path.dirname(REF), test_file))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def bits(t):
     return t.contiguous().view(torch.int16).numpy().view(np.uint16)
 
@@ -90,6 +102,21 @@ def main():
             rec[f"p{ci}_{name}"] = bits(t)
         rec[f"p{ci}_pos"], rec[f"p{ci}_cache"] = pos.numpy(), cache.numpy()
         rec[f"p{ci}_meta"] = np.array([bsz, qh, kvh, hd, rope_dim, int(norm)])
+    # the mrope variant through the reference test's _golden (test_split_qkv_rmsnorm_mrope.py:74-110), its two parametrisations
+    mr = load_named("test_split_qkv_rmsnorm_mrope.py", "sgl_kernel_npu.norm.split_qkv_rmsnorm_mrope", "triton_split_qkv_rmsnorm_mrope")
+    for ci, (ntok, rope_dim, section, inter, gate, bias) in enumerate(((7, 256, [32, 48, 48], True, True, False), (65, 128, [48, 40, 40], False, False, True))):
+        g = torch.Generator().manual_seed(400 + ci)
+        nqh, nkh, hs = 2, 1, 256
+        bf = lambda *s: torch.randn(*s, generator=g).to(torch.bfloat16)
+        x = bf(ntok, nqh * hs * (2 if gate else 1) + 2 * nkh * hs)
+        qw, kw = bf(hs), bf(hs)
+        qb, kb = (bf(hs), bf(hs)) if bias else (None, None)
+        cs = (torch.rand(3, ntok, rope_dim, generator=g) * 2 - 1).to(torch.bfloat16)
+        gq, gk, gv, gg = mr._golden(x, qw, kw, cs, nqh, nkh, hs, eps, section, inter, rope_dim, qb, kb, gate)
+        for name, t in (("qkv", x), ("qw", qw), ("kw", kw), ("cs", cs), ("v", gv)) + ((("qb", qb), ("kb", kb)) if bias else ()) + ((("gate", gg),) if gate else ()):
+            rec[f"m{ci}_{name}"] = bits(t)
+        rec[f"m{ci}_q"], rec[f"m{ci}_k"] = gq.numpy().astype(np.float32), gk.numpy().astype(np.float32)
+        rec[f"m{ci}_meta"] = np.array([ntok, nqh, nkh, hs, rope_dim, int(inter), int(gate), int(bias)] + section)
     np.savez_compressed(OUT, **rec)
     print("wrote", OUT, os.path.getsize(OUT), "bytes")
 

@@ -82,3 +82,35 @@ class _F32:
 
     def to(self, _):
         return self.t
+
+
+def mrope_select(cos_sin, mrope_section, is_interleaved):
+    """[3, tokens, rope_dim] -> [tokens, rope_dim]: pair i takes its cos / sin from the t, h or w row by section
+    (the reference test's _select_mrope_cos_sin, test_split_qkv_rmsnorm_mrope.py:8-50)"""
+    rd = cos_sin.shape[-1]
+    i = np.arange(rd // 2)
+    if is_interleaved:
+        sec = np.where((i % 3 == 1) & (i <= 3 * mrope_section[1]), 1, np.where((i % 3 == 2) & (i <= 3 * mrope_section[2]), 2, 0))
+    else:
+        sec = np.where(i < mrope_section[0], 0, np.where(i < mrope_section[0] + mrope_section[1], 1, 2))
+    sec = torch.from_numpy(np.concatenate((sec, sec)))
+    return cos_sin.permute(1, 2, 0)[:, torch.arange(rd), sec]
+
+
+def split_qkv_rmsnorm_mrope(qkv, q_weight, k_weight, cos_sin, num_q_heads, num_kv_heads, head_size, eps, mrope_section, is_interleaved,
+                            rope_dim=None, q_bias=None, k_bias=None, has_gate=False, with_scale=False):
+    """reference split_qkv_rmsnorm_mrope.py:57-333 / golden test_split_qkv_rmsnorm_mrope.py:74-110 -> (q, k, v, gate[, mq, mk])"""
+    b = qkv.shape[0]
+    qh, kvh = num_q_heads * head_size, num_kv_heads * head_size
+    rd = head_size if rope_dim is None else rope_dim
+    sel = mrope_select(cos_sin, mrope_section, is_interleaved).to(torch.float32)
+    cos, sin = sel[:, :rd // 2], sel[:, rd // 2:]
+    if has_gate:
+        qg = qkv[:, :2 * qh].reshape(b, num_q_heads, 2, head_size)
+        gate = qg[:, :, 1].reshape(b, qh).clone()
+        plain = torch.cat((qg[:, :, 0].reshape(b, qh), qkv[:, 2 * qh:]), dim=1).contiguous()
+    else:
+        gate, plain = qkv.new_empty((b, 0)), qkv
+    out = split_qkv_rmsnorm_rope(plain, _F32(torch.cat((sin, sin), 1)), _F32(torch.cat((cos, cos), 1)), qh, kvh, head_size, eps, q_weight, k_weight,
+                                 q_bias, k_bias, True, with_scale)
+    return out[:3] + (gate,) + out[3:]

@@ -648,6 +648,8 @@ int mlapo_assign_cache(void* out, const void* src, const void* dst_start, const 
   return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "assign_cache launch: %s", cudaGetErrorString(e));
 }
 
+static unsigned grid_for(long long work);
+
 struct SplitPosCache {
   const void* positions;
   const void* cache;
@@ -661,12 +663,12 @@ static int split_qkv_impl(const void* qkv, const void* sin, const void* cos, voi
                           int32_t q_hidden, int32_t kv_hidden, int32_t head_dim, int32_t rope_dim, float eps, int32_t has_norm,
                           int32_t neox_style, int32_t gemma, int32_t act_dtype, void* stream, const SplitPosCache* pc = nullptr) {
   if (!qkv || !q_out || !k_out || !v_out || (!pc && (!sin || !cos))) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: null pointer");
-  if (pc && (!pc->positions || !pc->cache || pc->max_seq < 1 || pc->cache_stride < rope_dim))
+  if (pc && (!pc->cache || pc->max_seq < 1 || pc->cache_stride < rope_dim))
     return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope_pos_cache: positions / cos_sin_cache [max_seq >= 1, >= rope_dim]");
   if (has_norm && (!q_weight || !k_weight)) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: eps given but no norm weights");
   if ((q_bias == nullptr) != (k_bias == nullptr)) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: q_bias and k_bias go together");
   if (batch <= 0 || head_dim < 2 || head_dim > kSplitMaxHeadDim || (head_dim & (head_dim - 1)) || q_hidden % head_dim || kv_hidden % head_dim ||
-      kv_hidden <= 0 || q_hidden % kv_hidden || rope_dim <= 0 || rope_dim > head_dim || (rope_dim & 1))
+      kv_hidden <= 0 || q_hidden <= 0 || rope_dim <= 0 || rope_dim > head_dim || (rope_dim & 1))
     return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope: batch=%lld q_hidden=%d kv_hidden=%d head_dim=%d (power of two <= %d) rope_dim=%d",
                 (long long)batch, q_hidden, kv_hidden, head_dim, kSplitMaxHeadDim, rope_dim);
   const int gated = gate_out != nullptr;
@@ -692,7 +694,8 @@ static int split_qkv_impl(const void* qkv, const void* sin, const void* cos, voi
       const long long nb = batch - t0 < tok_per_launch ? batch - t0 : tok_per_launch;
       SplitQkvArgs c = a;
       c.qkv = static_cast<const char*>(qkv) + t0 * row * es;
-      if (pc) c.positions = static_cast<const char*>(pc->positions) + t0 * (pc->pos_i64 ? 8 : 4);
+      if (pc && pc->positions) c.positions = static_cast<const char*>(pc->positions) + t0 * (pc->pos_i64 ? 8 : 4);
+      else if (pc) c.cache = static_cast<const char*>(pc->cache) + t0 * pc->cache_stride * (pc->cache_f32 ? 4 : 2);  // row t for token t
       else {
         c.sin = static_cast<const char*>(sin) + t0 * rope_dim * es;
         c.cos = static_cast<const char*>(cos) + t0 * rope_dim * es;
@@ -739,9 +742,34 @@ int split_qkv_rmsnorm_rope_pos_cache_launch(const void* qkv, const void* positio
                                             const void* q_weight, const void* k_weight, const void* q_bias, const void* k_bias, int64_t batch,
                                             int32_t q_hidden, int32_t kv_hidden, int32_t head_dim, int32_t rope_dim, float eps, int32_t has_norm,
                                             int32_t cast_norm, int32_t act_dtype, void* stream) {
+  if (!positions) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_rope_pos_cache: null positions");
   const SplitPosCache pc{positions, cos_sin_cache, cache_stride, positions_are_int64, cache_is_f32, max_seq, cast_norm};
   return split_qkv_impl(qkv, nullptr, nullptr, q_out, k_out, v_out, nullptr, q_weight, k_weight, q_bias, k_bias, batch, q_hidden, kv_hidden,
                         head_dim, rope_dim, eps, has_norm, 1, 0, act_dtype, stream, &pc);
+}
+
+int split_qkv_rmsnorm_mrope_launch(const void* qkv, const void* cos_sin, int32_t cos_sin_is_f32, void* workspace, void* q_out, void* k_out,
+                                   void* v_out, void* gate_out, const void* q_weight, const void* k_weight, const void* q_bias,
+                                   const void* k_bias, int64_t batch, int32_t num_q_heads, int32_t num_kv_heads, int32_t head_size,
+                                   int32_t rope_dim, float eps, int32_t section_t, int32_t section_h, int32_t section_w,
+                                   int32_t is_interleaved, int32_t act_dtype, void* stream) {
+  if (!cos_sin || !workspace) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_mrope: null cos_sin / workspace");
+  if (batch <= 0 || batch > (1LL << 30) || rope_dim <= 0 || (rope_dim & 1) || num_q_heads <= 0 || num_kv_heads <= 0 || head_size <= 0)
+    return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_rmsnorm_mrope: batch=%lld heads=%d/%d head_size=%d rope_dim=%d", (long long)batch, num_q_heads,
+                num_kv_heads, head_size, rope_dim);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const unsigned blocks = grid_for(batch * rope_dim);
+  if (cos_sin_is_f32)
+    mrope_select_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(cos_sin), static_cast<float*>(workspace), batch, rope_dim,
+                                                       section_t, section_h, section_w, is_interleaved);
+  else
+    mrope_select_kernel<uint16_t><<<blocks, 256, 0, st>>>(static_cast<const uint16_t*>(cos_sin), static_cast<uint16_t*>(workspace), batch,
+                                                          rope_dim, section_t, section_h, section_w, is_interleaved);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(MLAPO_ERR_CUDA, "split_qkv_rmsnorm_mrope select launch: %s", cudaGetErrorString(e));
+  const SplitPosCache pc{nullptr, workspace, rope_dim, 0, cos_sin_is_f32, (int)batch, 0};
+  return split_qkv_impl(qkv, nullptr, nullptr, q_out, k_out, v_out, gate_out, q_weight, k_weight, q_bias, k_bias, batch, num_q_heads * head_size,
+                        num_kv_heads * head_size, head_size, rope_dim, eps, 1, 1, 0, act_dtype, stream, &pc);
 }
 
 int split_qkvgate_gemma_rmsnorm_rope_launch(const void* qkvgate, const void* sin, const void* cos, void* q_out, void* k_out, void* v_out,

@@ -40,8 +40,8 @@ struct SplitQkvArgs {
   // split_qkv_rmsnorm_rope_pos_cache_half_npu (reference norm/split_qkv_rmsnorm_rope_pos_cache_half_npu.py:25-230): cos / sin come
   // from row clamp(positions[t], 0, max_seq - 1) of a cache [max_seq, rope_dim] laid out [cos(rope_dim/2) | sin(rope_dim/2)] (one
   // value per neox pair), and the normalised value may be rounded to the tensor dtype before the rotation (cast_norm)
-  const void* positions;  // int32 / int64 [batch], or null: sin / cos above are used
-  const void* cache;      // act or f32 [max_seq, cache_stride]
+  const void* cache;      // act or f32 [max_seq, cache_stride], or null: sin / cos above are used
+  const void* positions;  // int32 / int64 [batch]; null with a cache: token t uses row t
   long long cache_stride; // elements
   int pos_i64, cache_f32, max_seq, cast_norm;
 };
@@ -156,11 +156,11 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
         const int off = (int)ch * G::CHUNK;
         const uint32_t bytes = 2u * (uint32_t)(row - off < G::CHUNK ? row - off : G::CHUNK);
         const bool rope_here = off < qspan + kvh;  // a chunk of v heads only needs no sin / cos
-        const uint32_t cs_bytes = !rope_here ? 0u : a.positions ? (a.cache_f32 ? 4u : 2u) * (uint32_t)rd : 4u * (uint32_t)rd;
+        const uint32_t cs_bytes = !rope_here ? 0u : a.cache ? (a.cache_f32 ? 4u : 2u) * (uint32_t)rd : 4u * (uint32_t)rd;
         mbar_arrive_expect_tx(bar, bytes + cs_bytes);
         bulk_load_1d(dst, reinterpret_cast<const T*>(a.qkv) + (long long)t * row + off, bytes, bar);
-        if (rope_here && a.positions) {  // one cache row [cos | sin]
-          long long p = a.pos_i64 ? reinterpret_cast<const long long*>(a.positions)[t] : (long long)reinterpret_cast<const int*>(a.positions)[t];
+        if (rope_here && a.cache) {  // one cache row [cos | sin]
+          long long p = !a.positions ? (long long)t : a.pos_i64 ? reinterpret_cast<const long long*>(a.positions)[t] : (long long)reinterpret_cast<const int*>(a.positions)[t];
           p = p < 0 ? 0 : p >= a.max_seq ? a.max_seq - 1 : p;
           bulk_load_1d(dst + G::CHUNK * 2, reinterpret_cast<const uint8_t*>(a.cache) + p * a.cache_stride * (a.cache_f32 ? 4 : 2), cs_bytes, bar);
         } else if (rope_here) {
@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(kSplitThreads, 3) split_qkv_vec_kernel(SplitQk
     if (in_rope && off < qspan + kvh) {
       const uint8_t* ssin = st + G::CHUNK * 2;
       const uint8_t* scos = ssin + 2 * HD;
-      if (NEOX && a.positions) {  // cache row in the stage: cos then sin, one value per pair -> both slices use the same
+      if (NEOX && a.cache) {  // cache row in the stage: cos then sin, one value per pair -> both slices use the same
         if (a.cache_f32) {
           const float* cf = reinterpret_cast<const float*>(ssin);
 #pragma unroll
@@ -410,15 +410,15 @@ __global__ void __launch_bounds__(kSplitWarps * 32) split_qkv_scalar_kernel(Spli
     const T* sn = reinterpret_cast<const T*>(a.sin) + t * rd;
     const T* cs = reinterpret_cast<const T*>(a.cos) + t * rd;
     long long crow = 0;  // position-cache mode: element offset of the token's cache row
-    if (a.positions) {
-      long long p = a.pos_i64 ? reinterpret_cast<const long long*>(a.positions)[t] : (long long)reinterpret_cast<const int*>(a.positions)[t];
+    if (a.cache) {
+      long long p = !a.positions ? t : a.pos_i64 ? reinterpret_cast<const long long*>(a.positions)[t] : (long long)reinterpret_cast<const int*>(a.positions)[t];
       crow = (p < 0 ? 0 : p >= a.max_seq ? a.max_seq - 1 : p) * a.cache_stride;
     }
     for (int e = lane; e < hd; e += 32) {
       float o = x[e];
       if (e < rd) {
         float rot, s, c;
-        if (a.positions) {  // neox, one cache value per pair
+        if (a.cache) {  // neox, one cache value per pair
           rot = e < half ? -x[e + half] : x[e - half];
           const long long ci = crow + (e < half ? e : e - half);
           c = a.cache_f32 ? reinterpret_cast<const float*>(a.cache)[ci] : Act<T>::to_f(reinterpret_cast<const T*>(a.cache)[ci]);
@@ -437,6 +437,28 @@ __global__ void __launch_bounds__(kSplitWarps * 32) split_qkv_scalar_kernel(Spli
       dst[e] = Act<T>::from_f(o);
     }
     __syncwarp();
+  }
+}
+
+// split_qkv_rmsnorm_mrope (reference norm/split_qkv_rmsnorm_mrope.py:57-333, selection as the test's golden,
+// tests/python/sgl_kernel_npu/test_split_qkv_rmsnorm_mrope.py:8-50): cos_sin is [3 (t, h, w), tokens, rope_dim] with rows
+// [cos(rope_dim/2) | sin(rope_dim/2)]; pair i of a token takes its cos / sin from the t, h or w row by its section.  This kernel
+// writes the selected row per token, [tokens, rope_dim] in the same layout, which the kernels above then read as a cache with
+// row t for token t (2 * rope_dim bytes per token beside the 4 bytes per element of the main pass).
+__device__ __forceinline__ int mrope_section_of(int i, int sec_t, int sec_h, int sec_w, int interleaved) {
+  if (interleaved) return (i % 3 == 1 && i <= 3 * sec_h) ? 1 : (i % 3 == 2 && i <= 3 * sec_w) ? 2 : 0;
+  return i < sec_t ? 0 : i < sec_t + sec_h ? 1 : 2;
+}
+template <class E>
+__global__ void mrope_select_kernel(const E* __restrict__ cos_sin, E* __restrict__ out, long long tokens, int rope_dim, int sec_t, int sec_h,
+                                    int sec_w, int interleaved) {
+  const int half = rope_dim / 2;
+  const long long total = tokens * rope_dim;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const long long t = idx / rope_dim;
+    const int e = (int)(idx - t * rope_dim);
+    const int sec = mrope_section_of(e < half ? e : e - half, sec_t, sec_h, sec_w, interleaved);
+    out[idx] = cos_sin[((long long)sec * tokens + t) * rope_dim + e];
   }
 }
 

@@ -102,7 +102,73 @@ def test_oracle_pos_cache_matches_reference_golden(ci):
     assert close(q, t["q"].reshape(q.shape))[0] > 0.6
 
 
+def mrope_fixture(ci):
+    z = np.load(GOLD)
+    ntok, nqh, nkh, hs, rd, inter, gate, bias, *section = (int(v) for v in z[f"m{ci}_meta"])
+    names = ["qkv", "qw", "kw", "cs", "v"] + (["qb", "kb"] if bias else []) + (["gate"] if gate else [])
+    t = {k: bf(z[f"m{ci}_{k}"]) for k in names}
+    t["cs"] = t["cs"].reshape(3, ntok, rd)
+    return ntok, nqh, nkh, hs, rd, bool(inter), bool(gate), section, t, z[f"m{ci}_q"], z[f"m{ci}_k"]
+
+
+@pytest.mark.parametrize("ci", [0, 1])
+def test_oracle_mrope_matches_reference_golden(ci):
+    ntok, nqh, nkh, hs, rd, inter, gate, section, t, gq, gk = mrope_fixture(ci)
+    q, k, v, g = sq.split_qkv_rmsnorm_mrope(t["qkv"], t["qw"], t["kw"], t["cs"], nqh, nkh, hs, 1e-6, section, inter, rd, t.get("qb"), t.get("kb"), gate)
+    for got, want in ((q, gq), (k, gk)):
+        same, worst = close(got, want)
+        assert same >= 0.999 and worst <= 1, (same, worst)
+    assert torch.equal(v, t["v"].reshape(v.shape))
+    assert g.shape == (ntok, nqh * hs if gate else 0) and (not gate or torch.equal(g, t["gate"].reshape(g.shape)))
+
+
 # ------------------------------------------------------------------------------------------------ CUDA
+@pytest.mark.gpu
+@pytest.mark.parametrize("ci", [0, 1])
+def test_cuda_mrope_vs_golden_fixture(ci, cuda_device):
+    from sgl_kernel_npu.norm.split_qkv_rmsnorm_mrope import triton_split_qkv_rmsnorm_mrope as fn
+    ntok, nqh, nkh, hs, rd, inter, gate, section, t, gq, gk = mrope_fixture(ci)
+    d = {k: v.to(cuda_device) for k, v in t.items()}
+    q, k, v, g = fn(d["qkv"], d["qw"], d["kw"], d["cs"], nqh, nkh, hs, 1e-6, section, inter, rope_dim=rd, q_bias=d.get("qb"), k_bias=d.get("kb"),
+                    has_gate=gate)
+    *_, mq, mk = sq.split_qkv_rmsnorm_mrope(t["qkv"], t["qw"], t["kw"], t["cs"], nqh, nkh, hs, 1e-6, section, inter, rd, t.get("qb"), t.get("kb"),
+                                            gate, with_scale=True)
+    for got, want, m in ((q, gq, mq), (k, gk, mk)):
+        assert close(got, want)[0] >= 0.995 and within_summed_ulp(got, want, m)
+    assert torch.equal(v.cpu(), t["v"].reshape(v.shape))
+    assert g.shape == (ntok, nqh * hs if gate else 0) and (not gate or torch.equal(g.cpu(), t["gate"].reshape(g.shape)))
+
+
+# (tokens, q heads, kv heads, head_size, rope_dim, section, interleaved, gate, bias, cos_sin dtype, dtype)
+MROPE_CASES = [
+    (300, 16, 2, 128, 128, [24, 20, 20], True, False, False, torch.bfloat16, torch.bfloat16),    # Qwen2.5-VL-like sections
+    (300, 16, 2, 128, 128, [16, 24, 24], False, False, True, torch.float32, torch.bfloat16),
+    (33, 8, 2, 256, 64, [11, 11, 10], True, True, False, torch.float16, torch.float16),          # partial rotary, gate (Qwen3.5-like)
+    (5, 4, 1, 64, 20, [4, 3, 3], False, True, True, torch.bfloat16, torch.bfloat16),              # scalar kernel
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", MROPE_CASES, ids=lambda c: "t%d_h%d_%d_hs%d_r%d_%s" % (c[:5] + ("".join(str(int(x)) for x in c[6:9]),)))
+def test_cuda_mrope_vs_oracle(case, cuda_device):
+    from sgl_kernel_npu.norm.split_qkv_rmsnorm_mrope import triton_split_qkv_rmsnorm_mrope as fn
+    ntok, nqh, nkh, hs, rd, section, inter, gate, bias, cdt, dt = case
+    g = torch.Generator().manual_seed(ntok + hs + rd)
+    x = torch.randn(ntok, nqh * hs * (2 if gate else 1) + 2 * nkh * hs, generator=g).to(dt)
+    cs = (torch.rand(3, ntok, rd, generator=g) * 2 - 1).to(cdt)
+    rn = lambda: torch.randn(hs, generator=g).to(dt)
+    qw, kw = rn(), rn()
+    qb, kb = (rn(), rn()) if bias else (None, None)
+    wq, wk, wv, wg, mq, mk = sq.split_qkv_rmsnorm_mrope(x, qw, kw, cs, nqh, nkh, hs, 1e-6, section, inter, rd, qb, kb, gate, with_scale=True)
+    dev = lambda t: None if t is None else t.to(cuda_device)
+    q, k, v, gt = fn(dev(x), dev(qw), dev(kw), dev(cs), nqh, nkh, hs, 1e-6, section, inter, rope_dim=rd, q_bias=dev(qb), k_bias=dev(kb), has_gate=gate)
+    mant = 8 if dt == torch.bfloat16 else 11
+    for got, want, m in ((q, wq, mq), (k, wk, mk)):
+        assert close(got, want)[0] >= 0.99
+        assert within_summed_ulp(got, want.float().numpy(), m, mant)
+    assert torch.equal(v.cpu(), wv) and torch.equal(gt.cpu(), wg)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("ci", [0, 1, 2])
 def test_cuda_pos_cache_vs_golden_fixture(ci, cuda_device):
