@@ -182,6 +182,20 @@ int split_qkv_rmsnorm_mrope_launch(const void* qkv, const void* cos_sin, int32_t
                                    int32_t is_interleaved, int32_t act_dtype, void* stream);
 
 /*
+ * split_qkv_tp_rmsnorm_rope (python/sgl_kernel_npu/sgl_kernel_npu/norm/split_qkv_tp_rmsnorm_rope.py:172-288): the RMSNorm spans the
+ * whole q (k) row, whose columns are sharded over tp_world ranks: var = sum over ranks of mean_local(x^2), divided by tp_world;
+ * y = act_rne(x / sqrt(var + eps) * weight[col]); the first rotary_dim dims of every head rotated neox style with cos[t, i],
+ * sin[t, i], i < rotary_dim / 2; v copied.  mode 0: one pass, tp_world == 1.  mode 1: write the local means to qk_var f32
+ * [batch, 2]; the caller all-reduces (sums) qk_var over the tensor-parallel group (the reference's dist.all_reduce, :253-254);
+ * mode 2: one-pass apply with the reduced qk_var.  q_weight act [q_hidden], k_weight act [kv_hidden]; head_dim 32..256,
+ * rotary_dim a multiple of 8, pointers 16-byte aligned.
+ */
+int split_qkv_tp_rmsnorm_rope_launch(const void* qkv, const void* cos, const void* sin, void* q_out, void* k_out, void* v_out,
+                                     const void* q_weight, const void* k_weight, void* qk_var, int64_t batch, int32_t q_hidden,
+                                     int32_t kv_hidden, int32_t head_dim, int32_t rotary_dim, float eps, int32_t tp_world, int32_t mode,
+                                     int32_t act_dtype, void* stream);
+
+/*
  * split_qkvgate_gemma_rmsnorm_rope (same reference module, split_qkv_rmsnorm_rope.py:441-747): the fused row is
  * [q_0 | gate_0 | q_1 | gate_1 ... | k | v] (every q head followed by a gate head of head_dim), q and k heads are normalised with
  * (1 + weight) and no bias, the first rope_dim dims rotated neox style, v and the gate heads copied.

@@ -117,6 +117,23 @@ def main():
             rec[f"m{ci}_{name}"] = bits(t)
         rec[f"m{ci}_q"], rec[f"m{ci}_k"] = gq.numpy().astype(np.float32), gk.numpy().astype(np.float32)
         rec[f"m{ci}_meta"] = np.array([ntok, nqh, nkh, hs, rope_dim, int(inter), int(gate), int(bias)] + section)
+    # the tensor-parallel variant at tp_world = 1 through the reference test's rms_norm_tp / custom_rope
+    # (test_split_qkv_tp_rmsnorm_rope.py:7-45), applied as that test does (:78-86), on a scaled-down copy of its case
+    tp = load_named("test_split_qkv_tp_rmsnorm_rope.py", "sgl_kernel_npu.norm.split_qkv_tp_rmsnorm_rope", "split_qkv_tp_rmsnorm_rope")
+    qh, kvh, hd, bsz = 1024, 256, 128, 6
+    g = torch.Generator().manual_seed(500)
+    bf = lambda *s: torch.randn(*s, generator=g).to(torch.bfloat16)
+    x, qw, kw = bf(bsz, qh + 2 * kvh), bf(qh), bf(kvh)
+    sin = torch.rand(bsz, 1, 1, hd, generator=g).to(torch.bfloat16)
+    cos = torch.rand(bsz, 1, 1, hd, generator=g).to(torch.bfloat16)
+    _q, _k, _v = x.split([qh, kvh, kvh], dim=-1)
+    nq = tp.rms_norm_tp(_q, qw, eps, 1).reshape(bsz, 1, -1, hd)
+    nk = tp.rms_norm_tp(_k, kw, eps, 1).reshape(bsz, 1, -1, hd)
+    cq, ck = tp.custom_rope(nq, nk, sin, cos)
+    for name, t in (("qkv", x), ("qw", qw), ("kw", kw), ("sin", sin), ("cos", cos)):
+        rec[f"tp_{name}"] = bits(t)
+    rec["tp_q"], rec["tp_k"] = cq.reshape(bsz, -1).astype(np.float32), ck.reshape(bsz, -1).astype(np.float32)
+    rec["tp_meta"] = np.array([qh, kvh, hd, bsz])
     np.savez_compressed(OUT, **rec)
     print("wrote", OUT, os.path.getsize(OUT), "bytes")
 

@@ -114,3 +114,30 @@ def split_qkv_rmsnorm_mrope(qkv, q_weight, k_weight, cos_sin, num_q_heads, num_k
     out = split_qkv_rmsnorm_rope(plain, _F32(torch.cat((sin, sin), 1)), _F32(torch.cat((cos, cos), 1)), qh, kvh, head_size, eps, q_weight, k_weight,
                                  q_bias, k_bias, True, with_scale)
     return out[:3] + (gate,) + out[3:]
+
+
+def split_qkv_tp_rmsnorm_rope(inputs, cos, sin, q_hidden, kv_hidden, head_dim, eps, q_weights, k_weights, rotary_dim):
+    """The tensor-parallel variant (reference split_qkv_tp_rmsnorm_rope.py:8-170; golden helpers rms_norm_tp / custom_rope,
+    test_split_qkv_tp_rmsnorm_rope.py:7-45).  `inputs`, `q_weights`, `k_weights`: one tensor per rank (a single rank: lists of one).
+    var = sum over ranks of mean_local(x^2) / tp_world; y = act(x / sqrt(var + eps) * w[col]) rounded to the tensor dtype, then the
+    first rotary_dim dims of every head rotated with cos[t, :half], sin[t, :half], rounded again.  -> [(q, k, v)] per rank."""
+    tp = len(inputs)
+    dt = inputs[0].dtype
+    f = lambda t: t.to(torch.float32).numpy().astype(np.float32)
+    b = inputs[0].shape[0]
+    half = rotary_dim // 2
+    c, s = f(cos).reshape(b, -1)[:, None, :half], f(sin).reshape(b, -1)[:, None, :half]
+    var = [sum(np.mean(f(x)[:, lo:hi] ** 2, axis=-1, keepdims=True, dtype=np.float32) for x in inputs) * np.float32(1.0 / tp)
+           for lo, hi in ((0, q_hidden), (q_hidden, q_hidden + kv_hidden))]
+    rnd = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).to(dt)
+    outs = []
+    for x, qw, kw in zip(inputs, q_weights, k_weights):
+        res = []
+        for (lo, hi), v_, w in (((0, q_hidden), var[0], qw), ((q_hidden, q_hidden + kv_hidden), var[1], kw)):
+            y = f(x)[:, lo:hi] * (np.float32(1) / np.sqrt(v_ + np.float32(eps), dtype=np.float32)) * f(w)
+            y = rnd(y).to(torch.float32).numpy().reshape(b, -1, head_dim)
+            x1, x2 = y[..., :half], y[..., half:2 * half]
+            y = np.concatenate((x1 * c - x2 * s, x2 * c + x1 * s, y[..., 2 * half:]), axis=-1)
+            res.append(rnd(y.reshape(b, -1)))
+        outs.append((res[0], res[1], x[:, q_hidden + kv_hidden:].clone()))
+    return outs

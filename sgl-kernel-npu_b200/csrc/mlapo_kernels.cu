@@ -42,6 +42,7 @@
 #include "mlapo_bmt.cuh"
 #include "mlapo_slots.cuh"
 #include "mlapo_split_qkv.cuh"
+#include "mlapo_split_qkv_tp.cuh"
 
 namespace mlapo {
 
@@ -770,6 +771,49 @@ int split_qkv_rmsnorm_mrope_launch(const void* qkv, const void* cos_sin, int32_t
   const SplitPosCache pc{nullptr, workspace, rope_dim, 0, cos_sin_is_f32, (int)batch, 0};
   return split_qkv_impl(qkv, nullptr, nullptr, q_out, k_out, v_out, gate_out, q_weight, k_weight, q_bias, k_bias, batch, num_q_heads * head_size,
                         num_kv_heads * head_size, head_size, rope_dim, eps, 1, 1, 0, act_dtype, stream, &pc);
+}
+
+int split_qkv_tp_rmsnorm_rope_launch(const void* qkv, const void* cos, const void* sin, void* q_out, void* k_out, void* v_out,
+                                     const void* q_weight, const void* k_weight, void* qk_var, int64_t batch, int32_t q_hidden,
+                                     int32_t kv_hidden, int32_t head_dim, int32_t rotary_dim, float eps, int32_t tp_world, int32_t mode,
+                                     int32_t act_dtype, void* stream) {
+  if (!qkv) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: null qkv");
+  if (mode != kTpFused && mode != kTpSums && mode != kTpApply) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: mode %d", mode);
+  if (mode != kTpSums && (!cos || !sin || !q_out || !k_out || !v_out || !q_weight || !k_weight))
+    return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: null pointer");
+  if (mode != kTpFused && !qk_var) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: qk_var is needed for the two-phase modes");
+  if (mode == kTpFused && tp_world != 1) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: the one-pass mode is for tp_world == 1");
+  if (batch <= 0 || batch > (1LL << 31) || tp_world < 1 || (head_dim != 32 && head_dim != 64 && head_dim != 128 && head_dim != 256) ||
+      q_hidden <= 0 || kv_hidden <= 0 || q_hidden % head_dim || kv_hidden % head_dim || rotary_dim <= 0 || rotary_dim > head_dim || rotary_dim % 8)
+    return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: batch=%lld q_hidden=%d kv_hidden=%d head_dim=%d (32..256) rotary_dim=%d (multiple of 8)",
+                (long long)batch, q_hidden, kv_hidden, head_dim, rotary_dim);
+  if (act_dtype != MLAPO_ACT_BF16 && act_dtype != MLAPO_ACT_FP16) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: tensors must be fp16 or bf16");
+  uintptr_t align = 0;
+  for (const void* p : {qkv, cos, sin, (const void*)q_out, (const void*)k_out, (const void*)v_out, q_weight, k_weight}) align |= reinterpret_cast<uintptr_t>(p);
+  if (align & 15) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: pointers must be 16-byte aligned");
+  const int row = q_hidden + 2 * kv_hidden;
+  int stages = 4;
+  while (stages > 1 && tp_smem_bytes(row, rotary_dim, q_hidden, kv_hidden, stages) > 100 * 1024) --stages;  // two CTAs per SM
+  if (stages < 2) {
+    stages = 2;
+    if (tp_smem_bytes(row, rotary_dim, q_hidden, kv_hidden, stages) > 200 * 1024)
+      return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: a row of %d elements does not fit shared memory twice", row);
+  }
+  SplitTpArgs a{qkv, cos, sin, q_out, k_out, v_out, q_weight, k_weight, static_cast<float*>(qk_var), batch, q_hidden, kv_hidden, head_dim,
+                rotary_dim, eps, 1.f / (float)tp_world, mode, stages};
+  const int smem = tp_smem_bytes(row, rotary_dim, q_hidden, kv_hidden, stages);
+  const unsigned blocks = batch < 148 * 2 ? (unsigned)batch : 148u * 2u;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaError_t e;
+  if (act_dtype == MLAPO_ACT_BF16) {
+    e = cudaFuncSetAttribute(split_qkv_tp_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess) split_qkv_tp_kernel<__nv_bfloat16><<<blocks, kTpThreads, smem, st>>>(a);
+  } else {
+    e = cudaFuncSetAttribute(split_qkv_tp_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess) split_qkv_tp_kernel<__half><<<blocks, kTpThreads, smem, st>>>(a);
+  }
+  if (e == cudaSuccess) e = cudaGetLastError();
+  return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "split_qkv_tp_rmsnorm_rope launch: %s", cudaGetErrorString(e));
 }
 
 int split_qkvgate_gemma_rmsnorm_rope_launch(const void* qkvgate, const void* sin, const void* cos, void* q_out, void* k_out, void* v_out,

@@ -1,0 +1,200 @@
+// split_qkv_tp_rmsnorm_rope (the tensor-parallel member of the family).  Reference: the two Triton kernels and
+// the all-reduce between them in python/sgl_kernel_npu/sgl_kernel_npu/norm/split_qkv_tp_rmsnorm_rope.py:8-170 (wrapper :172-288).
+// Contract restated from it: the RMSNorm runs over the WHOLE q (and k) row of a token, whose columns are sharded over the
+// tensor-parallel ranks:  var = (sum over ranks of  mean_local(x^2)) / tp_world;  y = act_rne(x * (1/sqrt(var + eps)) * w[col])
+// with a weight per column; the first rotary_dim dims of every head of y are rotated neox style with cos[t, i], sin[t, i],
+// i < rotary_dim/2 (one value per pair), rounded once more; v is copied.
+//
+// The reference makes three passes over q and k in global memory (split + local sums, normalise in place, rotate in place).
+// Here a token's fused row is brought into shared memory ONCE by a bulk copy (ring of stages, producer warp), the sums are taken
+// from there, and the normalised, rotated row goes straight to q / k / v: 4 bytes of HBM traffic per element.  Modes:
+//   kTpFused  tp_world == 1: sums and apply in one pass;
+//   kTpSums   writes the local means to qk_var [batch, 2] (the host all-reduces them: NCCL, 8 bytes per token);
+//   kTpApply  the one-pass apply with the reduced qk_var.
+#pragma once
+#include "mlapo_split_qkv.cuh"
+
+namespace mlapo {
+
+enum { kTpFused = 0, kTpSums = 1, kTpApply = 2 };
+
+struct SplitTpArgs {
+  const void* qkv;       // act [batch, q_hidden + 2 kv_hidden]
+  const void* cos;       // act [batch, rotary_dim] (first half used)
+  const void* sin;
+  void* q_out;           // act [batch, q_hidden]
+  void* k_out;           // act [batch, kv_hidden]
+  void* v_out;
+  const void* q_weight;  // act [q_hidden]
+  const void* k_weight;  // act [kv_hidden]
+  float* qk_var;         // f32 [batch, 2]: written by kTpSums, read by kTpApply
+  long long batch;
+  int q_hidden, kv_hidden, head_dim, rotary_dim;
+  float eps, inv_tp_world;
+  int mode, stages;
+};
+
+constexpr int kTpWarps = 8;
+constexpr int kTpThreads = (kTpWarps + 1) * 32;
+
+// shared memory: stages x [row | cos row | sin row], then the weights as fp32?  no: as act (2 bytes) to keep 14 KB, then partials
+__host__ __device__ inline int tp_stage_bytes(int row, int rd) { return 2 * row + 4 * rd; }
+__host__ __device__ inline int tp_smem_bytes(int row, int rd, int qh, int kvh, int stages) {
+  return stages * tp_stage_bytes(row, rd) + 2 * (qh + kvh) + 16;
+}
+
+template <class T>
+__global__ void __launch_bounds__(kTpThreads, 2) split_qkv_tp_kernel(SplitTpArgs a) {
+  using namespace ptx;
+  constexpr int V = 8, W = 4, PW = 2;
+  extern __shared__ __align__(16) uint8_t smem[];
+  __shared__ __align__(8) uint64_t s_full[8], s_empty[8];
+  __shared__ float s_part[kTpWarps][2];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qh = a.q_hidden, kvh = a.kv_hidden, row = qh + 2 * kvh, hd = a.head_dim;
+  const int rd = a.rotary_dim, half = rd / 2;
+  const int S = a.stages, stage_bytes = tp_stage_bytes(row, rd);
+  const T* s_w = reinterpret_cast<const T*>(smem + S * stage_bytes);  // [q_hidden | kv_hidden] norm weights
+  const unsigned batch = (unsigned)a.batch;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), kTpWarps); }
+    fence_mbar_init();
+  }
+  if (a.mode != kTpSums) {
+    uint32_t* dst = reinterpret_cast<uint32_t*>(smem + S * stage_bytes);
+    for (int i = threadIdx.x; i < qh / 2; i += kTpThreads) dst[i] = reinterpret_cast<const uint32_t*>(a.q_weight)[i];
+    for (int i = threadIdx.x; i < kvh / 2; i += kTpThreads) dst[qh / 2 + i] = reinterpret_cast<const uint32_t*>(a.k_weight)[i];
+  }
+  __syncthreads();
+
+  if (warp == kTpWarps) {  // producer: one token per stage
+    if (lane == 0) {
+      unsigned it = 0;
+      for (unsigned t = blockIdx.x; t < batch; t += gridDim.x, ++it) {
+        const int stage = (int)(it % S);
+        if (it >= (unsigned)S) mbar_wait_light(smem_u32(&s_empty[stage]), ((it / S) - 1) & 1);
+        const uint32_t bar = smem_u32(&s_full[stage]);
+        const uint32_t dst = smem_u32(smem + stage * stage_bytes);
+        const bool rope = a.mode != kTpSums;
+        mbar_arrive_expect_tx(bar, 2u * row + (rope ? 4u * rd : 0u));
+        bulk_load_1d(dst, reinterpret_cast<const T*>(a.qkv) + (long long)t * row, 2u * row, bar);
+        if (rope) {
+          bulk_load_1d(dst + 2 * row, reinterpret_cast<const T*>(a.cos) + (long long)t * rd, 2u * rd, bar);
+          bulk_load_1d(dst + 2 * row + 2 * rd, reinterpret_cast<const T*>(a.sin) + (long long)t * rd, 2u * rd, bar);
+        }
+      }
+    }
+    return;
+  }
+
+  // a head is hd / 8 lanes; a lane owns two 4-element slices chosen so that a neox pair sits in one lane (as in the vector kernel)
+  const int L = hd / V, heads_per_warp = 32 / L;
+  const int j = lane % L;
+  const bool in_rope = j * W < half;
+  const int oA = in_rope ? j * W : rd + V * (j - half / W);
+  const int oB = in_rope ? half + j * W : oA + W;
+  const int nq = qh / hd, nk = kvh / hd;
+  const uint32_t full0 = smem_u32(&s_full[0]), empty0 = smem_u32(&s_empty[0]);
+
+  unsigned it = 0;
+  for (unsigned t = blockIdx.x; t < batch; t += gridDim.x, ++it) {
+    const int stage = (int)(it % S);
+    mbar_wait_light(full0 + 8 * stage, (it / S) & 1);
+    const uint8_t* st = smem + stage * stage_bytes;
+    float var_q, var_k;
+    if (a.mode != kTpApply) {
+      // local sums of squares over the q and the k columns: 16-byte vectors, fp32, two-wide accumulation
+      float2 aq = make_float2(0.f, 0.f), ak = make_float2(0.f, 0.f);
+      const int nvq = qh / V, nvk = kvh / V;
+      for (int v = threadIdx.x; v < nvq + nvk; v += kTpWarps * 32) {
+        const uint4 r = *reinterpret_cast<const uint4*>(st + v * 16);
+        const uint32_t w4[4] = {r.x, r.y, r.z, r.w};
+        float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          const float2 x = make_float2(Act<T>::lo(w4[p]), Act<T>::hi(w4[p]));
+          acc = fma2(x, x, acc);
+        }
+        if (v < nvq) { aq.x += acc.x; aq.y += acc.y; } else { ak.x += acc.x; ak.y += acc.y; }
+      }
+      float sq = aq.x + aq.y, sk = ak.x + ak.y;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        sq += __shfl_xor_sync(0xffffffffu, sq, o);
+        sk += __shfl_xor_sync(0xffffffffu, sk, o);
+      }
+      if (lane == 0) { s_part[warp][0] = sq; s_part[warp][1] = sk; }
+      named_bar_sync(1, kTpWarps * 32);
+      sq = sk = 0.f;
+#pragma unroll
+      for (int w = 0; w < kTpWarps; ++w) { sq += s_part[w][0]; sk += s_part[w][1]; }
+      var_q = sq / (float)qh;
+      var_k = sk / (float)kvh;
+      if (a.mode == kTpSums) {
+        if (threadIdx.x == 0) { a.qk_var[2 * (long long)t] = var_q; a.qk_var[2 * (long long)t + 1] = var_k; }
+        named_bar_sync(1, kTpWarps * 32);  // s_part and the stage are free again
+        if (lane == 0) mbar_arrive(empty0 + 8 * stage);
+        continue;
+      }
+    } else {
+      var_q = a.qk_var[2 * (long long)t];
+      var_k = a.qk_var[2 * (long long)t + 1];
+    }
+    const float scale_q = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var_q * a.inv_tp_world, a.eps)));
+    const float scale_k = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var_k * a.inv_tp_world, a.eps)));
+
+    // v: copy
+    {
+      const uint4* src = reinterpret_cast<const uint4*>(st + 2 * (qh + kvh));
+      uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<T*>(a.v_out) + (long long)t * kvh);
+      for (int v = threadIdx.x; v < kvh / V; v += kTpWarps * 32) dst[v] = src[v];
+    }
+    // cos / sin of the lane's pairs (one value per pair), sign folded into the first slice's sin
+    float2 cs[PW], snA[PW], snB[PW];
+    if (in_rope) {
+      const uint2 rc = *reinterpret_cast<const uint2*>(st + 2 * row + oA * 2), rs = *reinterpret_cast<const uint2*>(st + 2 * row + 2 * rd + oA * 2);
+      cs[0] = make_float2(Act<T>::lo(rc.x), Act<T>::hi(rc.x));
+      cs[1] = make_float2(Act<T>::lo(rc.y), Act<T>::hi(rc.y));
+      snB[0] = make_float2(Act<T>::lo(rs.x), Act<T>::hi(rs.x));
+      snB[1] = make_float2(Act<T>::lo(rs.y), Act<T>::hi(rs.y));
+      snA[0] = make_float2(-snB[0].x, -snB[0].y);
+      snA[1] = make_float2(-snB[1].x, -snB[1].y);
+    }
+    for (int h0 = warp * heads_per_warp; h0 < nq + nk; h0 += kTpWarps * heads_per_warp) {
+      const int head = h0 + lane / L;
+      if (head >= nq + nk) continue;
+      const bool is_q = head < nq;
+      const int col = head * hd;  // in the fused row and in [q weights | k weights]
+      const float sc = is_q ? scale_q : scale_k;
+      const float2 s2 = make_float2(sc, sc);
+      const uint2 ra = *reinterpret_cast<const uint2*>(st + (col + oA) * 2), rb = *reinterpret_cast<const uint2*>(st + (col + oB) * 2);
+      const uint2 wa = *reinterpret_cast<const uint2*>(s_w + col + oA), wb = *reinterpret_cast<const uint2*>(s_w + col + oB);
+      const uint32_t xa[2] = {ra.x, ra.y}, xb[2] = {rb.x, rb.y}, wwa[2] = {wa.x, wa.y}, wwb[2] = {wb.x, wb.y};
+      uint32_t oa[2], ob[2];
+#pragma unroll
+      for (int p = 0; p < PW; ++p) {
+        // y = act_rne(x * scale * w): the reference stores the normalised row before it rotates it
+        float2 ya = mul2(mul2(make_float2(Act<T>::lo(xa[p]), Act<T>::hi(xa[p])), s2), make_float2(Act<T>::lo(wwa[p]), Act<T>::hi(wwa[p])));
+        float2 yb = mul2(mul2(make_float2(Act<T>::lo(xb[p]), Act<T>::hi(xb[p])), s2), make_float2(Act<T>::lo(wwb[p]), Act<T>::hi(wwb[p])));
+        oa[p] = Act<T>::pack(ya.x, ya.y);
+        ob[p] = Act<T>::pack(yb.x, yb.y);
+        if (in_rope) {
+          ya = make_float2(Act<T>::lo(oa[p]), Act<T>::hi(oa[p]));
+          yb = make_float2(Act<T>::lo(ob[p]), Act<T>::hi(ob[p]));
+          const float2 na = fma2(yb, snA[p], mul2(ya, cs[p]));
+          const float2 nb = fma2(ya, snB[p], mul2(yb, cs[p]));
+          oa[p] = Act<T>::pack(na.x, na.y);
+          ob[p] = Act<T>::pack(nb.x, nb.y);
+        }
+      }
+      T* dst = is_q ? reinterpret_cast<T*>(a.q_out) + (long long)t * qh + col : reinterpret_cast<T*>(a.k_out) + (long long)t * kvh + (col - qh);
+      *reinterpret_cast<uint2*>(dst + oA) = make_uint2(oa[0], oa[1]);
+      *reinterpret_cast<uint2*>(dst + oB) = make_uint2(ob[0], ob[1]);
+    }
+    named_bar_sync(1, kTpWarps * 32);  // every warp is done with the stage (and with s_part)
+    if (lane == 0) mbar_arrive(empty0 + 8 * stage);
+  }
+}
+
+}  // namespace mlapo

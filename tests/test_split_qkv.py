@@ -122,7 +122,84 @@ def test_oracle_mrope_matches_reference_golden(ci):
     assert g.shape == (ntok, nqh * hs if gate else 0) and (not gate or torch.equal(g, t["gate"].reshape(g.shape)))
 
 
+def tp_fixture():
+    z = np.load(GOLD)
+    qh, kvh, hd, bsz = (int(v) for v in z["tp_meta"])
+    t = {k: bf(z[f"tp_{k}"]) for k in ("qkv", "qw", "kw", "sin", "cos")}
+    t["sin"], t["cos"] = t["sin"].reshape(bsz, hd), t["cos"].reshape(bsz, hd)
+    return qh, kvh, hd, bsz, t, z["tp_q"], z["tp_k"]
+
+
+def test_oracle_tp_matches_reference_golden():
+    qh, kvh, hd, bsz, t, gq, gk = tp_fixture()
+    (q, k, v), = sq.split_qkv_tp_rmsnorm_rope([t["qkv"]], t["cos"], t["sin"], qh, kvh, hd, 1e-6, [t["qw"]], [t["kw"]], hd)
+    for got, want in ((q, gq), (k, gk)):
+        same, worst = close(got, want)
+        assert same >= 0.995 and worst <= 2, (same, worst)   # the intermediate rounding can flip on an fp32 ulp of the norm
+        np.testing.assert_allclose(got.float().numpy(), want, atol=5e-2)
+    assert torch.equal(v, t["qkv"][:, qh + kvh:])
+
+
+def tp_close(got, want, dt):
+    """tp variant: two roundings, the first one can flip on an fp32 ulp of the norm -> nearly all identical, none beyond 2 ulp of the
+    largest magnitude a rotation pair holds (bounded here by the row's maximum)"""
+    same, _ = close(got, want)
+    ulp = float(np.exp2(np.floor(np.log2(float(want.float().abs().max()))) - (7 if dt == torch.bfloat16 else 10)))
+    err = float((got.float().cpu() - want.float()).abs().max())
+    return same >= 0.99 and err <= 2 * ulp, (same, err, ulp)
+
+
 # ------------------------------------------------------------------------------------------------ CUDA
+@pytest.mark.gpu
+def test_cuda_tp_single_rank_vs_golden_fixture(cuda_device):
+    from sgl_kernel_npu.norm.split_qkv_tp_rmsnorm_rope import split_qkv_tp_rmsnorm_rope as fn
+    qh, kvh, hd, bsz, t, gq, gk = tp_fixture()
+    d = {k: v.to(cuda_device) for k, v in t.items()}
+    q, k, v = fn(d["qkv"], d["cos"], d["sin"], qh, kvh, hd, 1e-6, d["qw"], d["kw"], hd, 1, None)
+    for got, want in ((q, gq), (k, gk)):
+        same, worst = close(got, want)
+        assert same >= 0.99 and worst <= 2, (same, worst)
+        np.testing.assert_allclose(got.float().cpu().numpy(), want, atol=5e-2)
+    assert torch.equal(v.cpu(), t["qkv"][:, qh + kvh:])
+
+
+# (batch, q_hidden, kv_hidden, head_dim, rotary_dim, dtype, ranks)
+TP_CASES = [(12, 6144, 1024, 128, 128, torch.bfloat16, 1), (300, 2048, 512, 128, 64, torch.bfloat16, 1), (7, 512, 256, 64, 32, torch.float16, 1),
+            (40, 1024, 256, 256, 64, torch.bfloat16, 2), (12, 6144, 1024, 128, 128, torch.bfloat16, 4), (5, 256, 64, 32, 16, torch.float16, 2)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", TP_CASES, ids=lambda c: "b%d_q%d_kv%d_hd%d_r%d_%s_tp%d" % (c[:5] + (str(c[5])[6:], c[6])))
+def test_cuda_tp_vs_oracle(case, cuda_device):
+    """ranks > 1: the ranks' shards run one after the other on this GPU through the two-phase modes of the C ABI, the sum of the
+    per-rank means (the all-reduce) taken in between; tests/test_split_qkv_tp_nccl.py does the same over NCCL when two GPUs are there"""
+    from sgl_kernel_npu.norm import split_qkv_tp_rmsnorm_rope as m
+    b, qh, kvh, hd, rd, dt, tp = case
+    g = torch.Generator().manual_seed(b + qh + rd + tp)
+    xs = [torch.randn(b, qh + 2 * kvh, generator=g).to(dt) * (r + 1) for r in range(tp)]
+    qws, kws = [torch.randn(qh, generator=g).to(dt) for _ in range(tp)], [torch.randn(kvh, generator=g).to(dt) for _ in range(tp)]
+    cos, sin = torch.rand(b, rd, generator=g).to(dt), torch.rand(b, rd, generator=g).to(dt)
+    want = sq.split_qkv_tp_rmsnorm_rope(xs, cos, sin, qh, kvh, hd, 1e-6, qws, kws, rd)
+    dev = lambda t: t.to(cuda_device)
+    if tp == 1:
+        got = [m.split_qkv_tp_rmsnorm_rope(dev(xs[0]), dev(cos), dev(sin), qh, kvh, hd, 1e-6, dev(qws[0]), dev(kws[0]), rd, 1, None)]
+    else:
+        new = lambda w: torch.empty(b, w, device=cuda_device, dtype=dt)
+        bufs = [(dev(xs[r]), dev(cos), dev(sin), new(qh), new(kvh), new(kvh), dev(qws[r]), dev(kws[r])) for r in range(tp)]
+        means = [torch.empty(b, 2, device=cuda_device) for _ in range(tp)]
+        for r in range(tp):
+            m._launch(m.MODE_SUMS, *bufs[r], means[r], qh, kvh, hd, rd, 1e-6, tp)
+        total = torch.stack(means).sum(0)
+        for r in range(tp):
+            m._launch(m.MODE_APPLY, *bufs[r], total, qh, kvh, hd, rd, 1e-6, tp)
+        got = [bufs[r][3:6] for r in range(tp)]
+    for r in range(tp):
+        for name, g_, w_ in zip("qk", got[r][:2], want[r][:2]):
+            ok, info = tp_close(g_, w_, dt)
+            assert ok, (r, name, info)
+        assert torch.equal(got[r][2].cpu(), want[r][2])
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("ci", [0, 1])
 def test_cuda_mrope_vs_golden_fixture(ci, cuda_device):

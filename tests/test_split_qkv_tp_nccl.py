@@ -1,0 +1,55 @@
+"""split_qkv_tp_rmsnorm_rope over a real tensor-parallel group: two ranks, one GPU each, NCCL all-reduce of the per-token means
+between the two kernel launches (the reference's dist.all_reduce, split_qkv_tp_rmsnorm_rope.py:253-254).  Needs two GPUs; on a
+one-GPU box the same arithmetic is covered by tests/test_split_qkv.py::test_cuda_tp_vs_oracle (ranks run one after the other)."""
+import os
+
+import pytest
+import torch
+
+from oracle import split_qkv_oracle as sq
+
+
+def _rank(rank, world, port, case, ret):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world)
+    try:
+        from sgl_kernel_npu.norm.split_qkv_tp_rmsnorm_rope import split_qkv_tp_rmsnorm_rope as fn
+        b, qh, kvh, hd, rd = case
+        g = torch.Generator().manual_seed(77)
+        dt = torch.bfloat16
+        xs = [torch.randn(b, qh + 2 * kvh, generator=g).to(dt) * (r + 1) for r in range(world)]
+        qws, kws = [torch.randn(qh, generator=g).to(dt) for _ in range(world)], [torch.randn(kvh, generator=g).to(dt) for _ in range(world)]
+        cos, sin = torch.rand(b, rd, generator=g).to(dt), torch.rand(b, rd, generator=g).to(dt)
+        want = sq.split_qkv_tp_rmsnorm_rope(xs, cos, sin, qh, kvh, hd, 1e-6, qws, kws, rd)[rank]
+        dev = lambda t: t.cuda(rank)
+        q, k, v = fn(dev(xs[rank]), dev(cos), dev(sin), qh, kvh, hd, 1e-6, dev(qws[rank]), dev(kws[rank]), rd, world, dist.group.WORLD)
+        torch.cuda.synchronize()
+        ok = torch.equal(v.cpu(), want[2])
+        for got, w in ((q, want[0]), (k, want[1])):
+            same = float((got.cpu().view(torch.int16) == w.view(torch.int16)).float().mean())
+            err = float((got.float().cpu() - w.float()).abs().max())
+            ok = ok and same >= 0.99 and err <= 2 * 2.0 ** (torch.floor(torch.log2(w.float().abs().max())).item() - 7)
+        ret[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_two_ranks_nccl():
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    procs = [ctx.Process(target=_rank, args=(r, 2, 29517, (96, 2048, 512, 128, 64), ret)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=240)
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+            pytest.fail("rank did not finish")
+    assert dict(ret) == {0: True, 1: True}
