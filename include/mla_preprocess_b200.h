@@ -196,6 +196,20 @@ int split_qkv_tp_rmsnorm_rope_launch(const void* qkv, const void* cos, const voi
                                      int32_t act_dtype, void* stream);
 
 /*
+ * The same operator for tp_world > 1 as ONE kernel: the ranks exchange the per-token means inside the kernel, through buffers in
+ * each other's memory (NVLink peer stores of 8-byte {value, epoch} records), instead of an all-reduce between two launches.  No
+ * reference counterpart (the reference calls dist.all_reduce, split_qkv_tp_rmsnorm_rope.py:253-254).  peer_buffers: host array of
+ * tp_world device pointers, entry r = rank r's exchange buffer as mapped in THIS process (entry tp_rank is this GPU's own), each
+ * 2 * tp_world * capacity * 16 bytes, zeroed once before the first call.  epoch: the same non-zero value on every rank,
+ * incremented by one per call (its parity picks the buffer half).  Every rank must make the same sequence of calls with the same
+ * batch <= capacity; a peer that never arrives becomes a trap (launch failure) after a bounded wait.
+ */
+int split_qkv_tp_rmsnorm_rope_peer_launch(const void* qkv, const void* cos, const void* sin, void* q_out, void* k_out, void* v_out,
+                                          const void* q_weight, const void* k_weight, int64_t batch, int32_t q_hidden, int32_t kv_hidden,
+                                          int32_t head_dim, int32_t rotary_dim, float eps, const void* const* peer_buffers, int32_t tp_rank,
+                                          int32_t tp_world, uint32_t epoch, int32_t capacity, int32_t act_dtype, void* stream);
+
+/*
  * split_qkvgate_gemma_rmsnorm_rope (same reference module, split_qkv_rmsnorm_rope.py:441-747): the fused row is
  * [q_0 | gate_0 | q_1 | gate_1 ... | k | v] (every q head followed by a gate head of head_dim), q and k heads are normalised with
  * (1 + weight) and no bias, the first rope_dim dims rotated neox style, v and the gate heads copied.

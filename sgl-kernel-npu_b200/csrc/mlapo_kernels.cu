@@ -773,15 +773,18 @@ int split_qkv_rmsnorm_mrope_launch(const void* qkv, const void* cos_sin, int32_t
                         num_kv_heads * head_size, head_size, rope_dim, eps, 1, 1, 0, act_dtype, stream, &pc);
 }
 
-int split_qkv_tp_rmsnorm_rope_launch(const void* qkv, const void* cos, const void* sin, void* q_out, void* k_out, void* v_out,
-                                     const void* q_weight, const void* k_weight, void* qk_var, int64_t batch, int32_t q_hidden,
-                                     int32_t kv_hidden, int32_t head_dim, int32_t rotary_dim, float eps, int32_t tp_world, int32_t mode,
-                                     int32_t act_dtype, void* stream) {
+static int split_qkv_tp_impl(const void* qkv, const void* cos, const void* sin, void* q_out, void* k_out, void* v_out,
+                             const void* q_weight, const void* k_weight, void* qk_var, int64_t batch, int32_t q_hidden,
+                             int32_t kv_hidden, int32_t head_dim, int32_t rotary_dim, float eps, int32_t tp_world, int32_t mode,
+                             int32_t act_dtype, void* stream, const void* const* peers, int32_t tp_rank, uint32_t epoch, int32_t capacity) {
   if (!qkv) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: null qkv");
-  if (mode != kTpFused && mode != kTpSums && mode != kTpApply) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: mode %d", mode);
+  if (mode != kTpFused && mode != kTpSums && mode != kTpApply && mode != kTpPeer) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: mode %d", mode);
+  if (mode == kTpPeer && (!peers || tp_world < 2 || tp_world > kTpMaxRanks || tp_rank < 0 || tp_rank >= tp_world || epoch == 0 || batch > capacity))
+    return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope (peer exchange): tp_rank=%d tp_world=%d (2..%d) epoch=%u batch=%lld capacity=%d",
+                tp_rank, tp_world, kTpMaxRanks, epoch, (long long)batch, capacity);
   if (mode != kTpSums && (!cos || !sin || !q_out || !k_out || !v_out || !q_weight || !k_weight))
     return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: null pointer");
-  if (mode != kTpFused && !qk_var) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: qk_var is needed for the two-phase modes");
+  if ((mode == kTpSums || mode == kTpApply) && !qk_var) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: qk_var is needed for the two-phase modes");
   if (mode == kTpFused && tp_world != 1) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: the one-pass mode is for tp_world == 1");
   if (batch <= 0 || batch > (1LL << 31) || tp_world < 1 || (head_dim != 32 && head_dim != 64 && head_dim != 128 && head_dim != 256) ||
       q_hidden <= 0 || kv_hidden <= 0 || q_hidden % head_dim || kv_hidden % head_dim || rotary_dim <= 0 || rotary_dim > head_dim || rotary_dim % 8)
@@ -800,9 +803,16 @@ int split_qkv_tp_rmsnorm_rope_launch(const void* qkv, const void* cos, const voi
       return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: a row of %d elements does not fit shared memory twice", row);
   }
   SplitTpArgs a{qkv, cos, sin, q_out, k_out, v_out, q_weight, k_weight, static_cast<float*>(qk_var), batch, q_hidden, kv_hidden, head_dim,
-                rotary_dim, eps, 1.f / (float)tp_world, mode, stages};
+                rotary_dim, eps, 1.f / (float)tp_world, mode, stages, {}, tp_rank, tp_world, capacity, epoch};
+  if (mode == kTpPeer)
+    for (int r = 0; r < tp_world; ++r) {
+      if (!peers[r]) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope (peer exchange): null buffer of rank %d", r);
+      a.peer[r] = reinterpret_cast<unsigned long long>(peers[r]);
+    }
   const int smem = tp_smem_bytes(row, rotary_dim, q_hidden, kv_hidden, stages);
-  const unsigned blocks = batch < 148 * 2 ? (unsigned)batch : 148u * 2u;
+  // the peer-exchange mode needs every CTA resident at once: 2 per SM fit when a CTA takes <= 100 KB, else 1
+  const unsigned resident = 148u * (smem <= 100 * 1024 ? 2u : 1u);
+  const unsigned blocks = batch < resident ? (unsigned)batch : resident;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaError_t e;
   if (act_dtype == MLAPO_ACT_BF16) {
@@ -814,6 +824,23 @@ int split_qkv_tp_rmsnorm_rope_launch(const void* qkv, const void* cos, const voi
   }
   if (e == cudaSuccess) e = cudaGetLastError();
   return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "split_qkv_tp_rmsnorm_rope launch: %s", cudaGetErrorString(e));
+}
+
+int split_qkv_tp_rmsnorm_rope_launch(const void* qkv, const void* cos, const void* sin, void* q_out, void* k_out, void* v_out,
+                                     const void* q_weight, const void* k_weight, void* qk_var, int64_t batch, int32_t q_hidden,
+                                     int32_t kv_hidden, int32_t head_dim, int32_t rotary_dim, float eps, int32_t tp_world, int32_t mode,
+                                     int32_t act_dtype, void* stream) {
+  if (mode == kTpPeer) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: the peer-exchange mode has its own entry point");
+  return split_qkv_tp_impl(qkv, cos, sin, q_out, k_out, v_out, q_weight, k_weight, qk_var, batch, q_hidden, kv_hidden, head_dim, rotary_dim, eps,
+                           tp_world, mode, act_dtype, stream, nullptr, 0, 0, 0);
+}
+
+int split_qkv_tp_rmsnorm_rope_peer_launch(const void* qkv, const void* cos, const void* sin, void* q_out, void* k_out, void* v_out,
+                                          const void* q_weight, const void* k_weight, int64_t batch, int32_t q_hidden, int32_t kv_hidden,
+                                          int32_t head_dim, int32_t rotary_dim, float eps, const void* const* peer_buffers, int32_t tp_rank,
+                                          int32_t tp_world, uint32_t epoch, int32_t capacity, int32_t act_dtype, void* stream) {
+  return split_qkv_tp_impl(qkv, cos, sin, q_out, k_out, v_out, q_weight, k_weight, nullptr, batch, q_hidden, kv_hidden, head_dim, rotary_dim, eps,
+                           tp_world, kTpPeer, act_dtype, stream, peer_buffers, tp_rank, epoch, capacity);
 }
 
 int split_qkvgate_gemma_rmsnorm_rope_launch(const void* qkvgate, const void* sin, const void* cos, void* q_out, void* k_out, void* v_out,

@@ -10,13 +10,21 @@
 // from there, and the normalised, rotated row goes straight to q / k / v: 4 bytes of HBM traffic per element.  Modes:
 //   kTpFused  tp_world == 1: sums and apply in one pass;
 //   kTpSums   writes the local means to qk_var [batch, 2] (the host all-reduces them: NCCL, 8 bytes per token);
-//   kTpApply  the one-pass apply with the reduced qk_var.
+//   kTpApply  the one-pass apply with the reduced qk_var;
+//   kTpPeer   ONE kernel for tp_world > 1: each CTA publishes a token's local means straight into every rank's exchange buffer over
+//             NVLink (plain peer stores of 8-byte {value, epoch} records: data and flag arrive together, no fence needed), works on
+//             the next tokens' sums meanwhile, then picks up the peers' records for the token from its OWN GPU's memory and applies.
+//             The row never leaves shared memory in between, so the collective costs no extra HBM pass and no kernel boundary.
+//             Every rank adds the records in rank order: all ranks get the same bits.  Needs all CTAs co-resident (the host sizes
+//             the grid so) and the same batch on every rank; records of call e live in half (e & 1) of the buffer, and a rank can
+//             only be one call ahead of a peer (its next call waits for the peer's records of this one), so halves never collide.
 #pragma once
 #include "mlapo_split_qkv.cuh"
 
 namespace mlapo {
 
-enum { kTpFused = 0, kTpSums = 1, kTpApply = 2 };
+enum { kTpFused = 0, kTpSums = 1, kTpApply = 2, kTpPeer = 3 };
+constexpr int kTpMaxRanks = 8;
 
 struct SplitTpArgs {
   const void* qkv;       // act [batch, q_hidden + 2 kv_hidden]
@@ -32,15 +40,34 @@ struct SplitTpArgs {
   int q_hidden, kv_hidden, head_dim, rotary_dim;
   float eps, inv_tp_world;
   int mode, stages;
+  // kTpPeer: exchange buffer of every rank as mapped here, [2 halves][tp_world sources][capacity tokens][2 records of 8 bytes]
+  unsigned long long peer[kTpMaxRanks];
+  int tp_rank, tp_world, capacity;
+  unsigned epoch;  // of this call, never 0 (the buffer starts zeroed)
 };
 
 constexpr int kTpWarps = 8;
 constexpr int kTpThreads = (kTpWarps + 1) * 32;
 
-// shared memory: stages x [row | cos row | sin row], then the weights as fp32?  no: as act (2 bytes) to keep 14 KB, then partials
+// dynamic shared memory: stages x [row | cos row | sin row], then the norm weights [q_hidden | kv_hidden] in the tensor dtype
 __host__ __device__ inline int tp_stage_bytes(int row, int rd) { return 2 * row + 4 * rd; }
 __host__ __device__ inline int tp_smem_bytes(int row, int rd, int qh, int kvh, int stages) {
   return stages * tp_stage_bytes(row, rd) + 2 * (qh + kvh) + 16;
+}
+
+__device__ __forceinline__ void st_record(unsigned long long addr, float v, unsigned epoch) {
+  asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(addr), "r"(__float_as_uint(v)), "r"(epoch) : "memory");
+}
+// waits (bounded: a peer that never publishes becomes a trap, not a hung GPU) for a record of this call's epoch
+__device__ __forceinline__ float ld_record(unsigned long long addr, unsigned epoch) {
+  unsigned v, e;
+  for (unsigned n = 0;; ++n) {
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(addr) : "memory");
+    if (e == epoch) break;
+    if (n > 64) __nanosleep(200);
+    if (n > (1u << 23)) __trap();
+  }
+  return __uint_as_float(v);
 }
 
 template <class T>
@@ -97,50 +124,40 @@ __global__ void __launch_bounds__(kTpThreads, 2) split_qkv_tp_kernel(SplitTpArgs
   const int nq = qh / hd, nk = kvh / hd;
   const uint32_t full0 = smem_u32(&s_full[0]), empty0 = smem_u32(&s_empty[0]);
 
-  unsigned it = 0;
-  for (unsigned t = blockIdx.x; t < batch; t += gridDim.x, ++it) {
-    const int stage = (int)(it % S);
-    mbar_wait_light(full0 + 8 * stage, (it / S) & 1);
-    const uint8_t* st = smem + stage * stage_bytes;
-    float var_q, var_k;
-    if (a.mode != kTpApply) {
-      // local sums of squares over the q and the k columns: 16-byte vectors, fp32, two-wide accumulation
-      float2 aq = make_float2(0.f, 0.f), ak = make_float2(0.f, 0.f);
-      const int nvq = qh / V, nvk = kvh / V;
-      for (int v = threadIdx.x; v < nvq + nvk; v += kTpWarps * 32) {
-        const uint4 r = *reinterpret_cast<const uint4*>(st + v * 16);
-        const uint32_t w4[4] = {r.x, r.y, r.z, r.w};
-        float2 acc = make_float2(0.f, 0.f);
+  __shared__ float s_gather[kTpMaxRanks][2];
+  // means of x^2 over this rank's q and k columns of the row in stage `st` (all 8 warps; ends with every thread past s_part)
+  auto local_means = [&](const uint8_t* st, float& var_q, float& var_k) {
+    // local sums of squares over the q and the k columns: 16-byte vectors, fp32, two-wide accumulation
+    float2 aq = make_float2(0.f, 0.f), ak = make_float2(0.f, 0.f);
+    const int nvq = qh / V, nvk = kvh / V;
+    for (int v = threadIdx.x; v < nvq + nvk; v += kTpWarps * 32) {
+      const uint4 r = *reinterpret_cast<const uint4*>(st + v * 16);
+      const uint32_t w4[4] = {r.x, r.y, r.z, r.w};
+      float2 acc = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int p = 0; p < 4; ++p) {
-          const float2 x = make_float2(Act<T>::lo(w4[p]), Act<T>::hi(w4[p]));
-          acc = fma2(x, x, acc);
-        }
-        if (v < nvq) { aq.x += acc.x; aq.y += acc.y; } else { ak.x += acc.x; ak.y += acc.y; }
+      for (int p = 0; p < 4; ++p) {
+        const float2 x = make_float2(Act<T>::lo(w4[p]), Act<T>::hi(w4[p]));
+        acc = fma2(x, x, acc);
       }
-      float sq = aq.x + aq.y, sk = ak.x + ak.y;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        sq += __shfl_xor_sync(0xffffffffu, sq, o);
-        sk += __shfl_xor_sync(0xffffffffu, sk, o);
-      }
-      if (lane == 0) { s_part[warp][0] = sq; s_part[warp][1] = sk; }
-      named_bar_sync(1, kTpWarps * 32);
-      sq = sk = 0.f;
-#pragma unroll
-      for (int w = 0; w < kTpWarps; ++w) { sq += s_part[w][0]; sk += s_part[w][1]; }
-      var_q = sq / (float)qh;
-      var_k = sk / (float)kvh;
-      if (a.mode == kTpSums) {
-        if (threadIdx.x == 0) { a.qk_var[2 * (long long)t] = var_q; a.qk_var[2 * (long long)t + 1] = var_k; }
-        named_bar_sync(1, kTpWarps * 32);  // s_part and the stage are free again
-        if (lane == 0) mbar_arrive(empty0 + 8 * stage);
-        continue;
-      }
-    } else {
-      var_q = a.qk_var[2 * (long long)t];
-      var_k = a.qk_var[2 * (long long)t + 1];
+      if (v < nvq) { aq.x += acc.x; aq.y += acc.y; } else { ak.x += acc.x; ak.y += acc.y; }
     }
+    float sq = aq.x + aq.y, sk = ak.x + ak.y;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      sq += __shfl_xor_sync(0xffffffffu, sq, o);
+      sk += __shfl_xor_sync(0xffffffffu, sk, o);
+    }
+    if (lane == 0) { s_part[warp][0] = sq; s_part[warp][1] = sk; }
+    named_bar_sync(1, kTpWarps * 32);
+    sq = sk = 0.f;
+#pragma unroll
+    for (int w = 0; w < kTpWarps; ++w) { sq += s_part[w][0]; sk += s_part[w][1]; }
+    var_q = sq / (float)qh;
+    var_k = sk / (float)kvh;
+    named_bar_sync(1, kTpWarps * 32);  // s_part may be rewritten
+  };
+  // normalise, rotate and store token t from the row in stage `st`, copy v; then hand the stage back
+  auto apply = [&](const uint8_t* st, int stage, unsigned t, float var_q, float var_k) {
     const float scale_q = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var_q * a.inv_tp_world, a.eps)));
     const float scale_k = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var_k * a.inv_tp_world, a.eps)));
 
@@ -192,8 +209,63 @@ __global__ void __launch_bounds__(kTpThreads, 2) split_qkv_tp_kernel(SplitTpArgs
       *reinterpret_cast<uint2*>(dst + oA) = make_uint2(oa[0], oa[1]);
       *reinterpret_cast<uint2*>(dst + oB) = make_uint2(ob[0], ob[1]);
     }
-    named_bar_sync(1, kTpWarps * 32);  // every warp is done with the stage (and with s_part)
+    named_bar_sync(1, kTpWarps * 32);  // every warp is done with the stage
     if (lane == 0) mbar_arrive(empty0 + 8 * stage);
+  };
+
+  if (a.mode == kTpPeer) {
+    const int tp = a.tp_world, D = S > 2 ? S - 2 : 1;  // tokens between a token's sums and its apply: hides the exchange
+    const unsigned n_local = blockIdx.x < batch ? (batch - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const unsigned long long half_bytes = (unsigned long long)tp * a.capacity * 16ull;
+    const unsigned long long rec0 = (a.epoch & 1u) * half_bytes;
+    for (unsigned i = 0; i < n_local + D; ++i) {
+      if (i < n_local) {
+        const unsigned t = blockIdx.x + i * gridDim.x;
+        const int stage = (int)(i % S);
+        mbar_wait_light(full0 + 8 * stage, (i / S) & 1);
+        float vq, vk;
+        local_means(smem + stage * stage_bytes, vq, vk);
+        if ((int)threadIdx.x < tp) {  // one thread per destination rank
+          const unsigned long long dst = a.peer[threadIdx.x] + rec0 + ((unsigned long long)a.tp_rank * a.capacity + t) * 16ull;
+          st_record(dst, vq, a.epoch);
+          st_record(dst + 8, vk, a.epoch);
+        }
+      }
+      if (i >= (unsigned)D) {
+        const unsigned jn = i - D, t = blockIdx.x + jn * gridDim.x;
+        const int stage = (int)(jn % S);
+        if ((int)threadIdx.x < tp) {  // one thread per source rank, records in this GPU's own buffer
+          const unsigned long long src = a.peer[a.tp_rank] + rec0 + ((unsigned long long)threadIdx.x * a.capacity + t) * 16ull;
+          s_gather[threadIdx.x][0] = ld_record(src, a.epoch);
+          s_gather[threadIdx.x][1] = ld_record(src + 8, a.epoch);
+        }
+        named_bar_sync(1, kTpWarps * 32);
+        float vq = 0.f, vk = 0.f;
+        for (int r = 0; r < tp; ++r) { vq += s_gather[r][0]; vk += s_gather[r][1]; }  // rank order: the same bits on every rank
+        apply(smem + stage * stage_bytes, stage, t, vq, vk);  // its closing barrier also frees s_gather
+      }
+    }
+    return;
+  }
+
+  unsigned it = 0;
+  for (unsigned t = blockIdx.x; t < batch; t += gridDim.x, ++it) {
+    const int stage = (int)(it % S);
+    mbar_wait_light(full0 + 8 * stage, (it / S) & 1);
+    const uint8_t* st = smem + stage * stage_bytes;
+    float var_q, var_k;
+    if (a.mode != kTpApply) {
+      local_means(st, var_q, var_k);
+      if (a.mode == kTpSums) {
+        if (threadIdx.x == 0) { a.qk_var[2 * (long long)t] = var_q; a.qk_var[2 * (long long)t + 1] = var_k; }
+        if (lane == 0) mbar_arrive(empty0 + 8 * stage);
+        continue;
+      }
+    } else {
+      var_q = a.qk_var[2 * (long long)t];
+      var_k = a.qk_var[2 * (long long)t + 1];
+    }
+    apply(st, stage, t, var_q, var_k);
   }
 }
 
