@@ -796,7 +796,9 @@ static int split_qkv_tp_impl(const void* qkv, const void* cos, const void* sin, 
   if (align & 15) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: pointers must be 16-byte aligned");
   const int row = q_hidden + 2 * kv_hidden;
   int stages = 4;
-  while (stages > 1 && tp_smem_bytes(row, rotary_dim, q_hidden, kv_hidden, stages) > 100 * 1024) --stages;  // two CTAs per SM
+  while (stages > 3 && tp_smem_bytes(row, rotary_dim, q_hidden, kv_hidden, stages) > 72 * 1024) --stages;   // three CTAs per SM if a 3-deep ring allows
+  while (stages > 1 && tp_smem_bytes(row, rotary_dim, q_hidden, kv_hidden, stages) > 72 * 1024 &&
+         tp_smem_bytes(row, rotary_dim, q_hidden, kv_hidden, stages) > 110 * 1024) --stages;                  // else two
   if (stages < 2) {
     stages = 2;
     if (tp_smem_bytes(row, rotary_dim, q_hidden, kv_hidden, stages) > 200 * 1024)
@@ -810,8 +812,8 @@ static int split_qkv_tp_impl(const void* qkv, const void* cos, const void* sin, 
       a.peer[r] = reinterpret_cast<unsigned long long>(peers[r]);
     }
   const int smem = tp_smem_bytes(row, rotary_dim, q_hidden, kv_hidden, stages);
-  // the peer-exchange mode needs every CTA resident at once: 2 per SM fit when a CTA takes <= 100 KB, else 1
-  const unsigned resident = 148u * (smem <= 100 * 1024 ? 2u : 1u);
+  // the peer-exchange mode needs every CTA resident at once: 3 per SM fit when a CTA takes <= 72 KB, 2 up to 110 KB, else 1
+  const unsigned resident = 148u * (smem <= 72 * 1024 ? 3u : smem <= 110 * 1024 ? 2u : 1u);
   const unsigned blocks = batch < resident ? (unsigned)batch : resident;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaError_t e;

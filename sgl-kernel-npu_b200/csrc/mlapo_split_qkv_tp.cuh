@@ -13,7 +13,8 @@
 //   kTpApply  the one-pass apply with the reduced qk_var;
 //   kTpPeer   ONE kernel for tp_world > 1: each CTA publishes a token's local means straight into every rank's exchange buffer over
 //             NVLink (plain peer stores of 8-byte {value, epoch} records: data and flag arrive together, no fence needed), works on
-//             the next tokens' sums meanwhile, then picks up the peers' records for the token from its OWN GPU's memory and applies.
+//             the next tokens' sums meanwhile, then applies with the peers' records, which a gather warp has meanwhile collected
+//             from this GPU's OWN memory into shared memory.
 //             The row never leaves shared memory in between, so the collective costs no extra HBM pass and no kernel boundary.
 //             Every rank adds the records in rank order: all ranks get the same bits.  Needs all CTAs co-resident (the host sizes
 //             the grid so) and the same batch on every rank; records of call e live in half (e & 1) of the buffer, and a rank can
@@ -46,8 +47,10 @@ struct SplitTpArgs {
   unsigned epoch;  // of this call, never 0 (the buffer starts zeroed)
 };
 
-constexpr int kTpWarps = 8;
-constexpr int kTpThreads = (kTpWarps + 1) * 32;
+// warps of a CTA: apply warps, sum warps, one producer warp, one gather warp (peer mode)
+constexpr int kTpApplyWarps = 5, kTpSumWarps = 2;
+constexpr int kTpProducerWarp = kTpApplyWarps + kTpSumWarps, kTpGatherWarp = kTpProducerWarp + 1;
+constexpr int kTpThreads = (kTpGatherWarp + 1) * 32;
 
 // dynamic shared memory: stages x [row | cos row | sin row], then the norm weights [q_hidden | kv_hidden] in the tensor dtype
 __host__ __device__ inline int tp_stage_bytes(int row, int rd) { return 2 * row + 4 * rd; }
@@ -70,43 +73,57 @@ __device__ __forceinline__ float ld_record(unsigned long long addr, unsigned epo
   return __uint_as_float(v);
 }
 
+// Roles run on different tokens at the same time, coupled only by per-stage mbarriers (no CTA-wide barrier in the loop):
+//   producer warp  bulk-copies token rows (+ cos / sin rows) into the ring                          -> full[s]
+//   sum warps      means of x^2 over the q and k columns of a row                                   -> summed[s]  (or publish / qk_var)
+//   gather warp    (peer mode) collects every rank's records of the token from this GPU's buffer    -> gathered[s]
+//   apply warps    normalise with the (global) means, round, rotate, store q / k, copy v            -> empty[s] (with the sum warps)
 template <class T>
-__global__ void __launch_bounds__(kTpThreads, 2) split_qkv_tp_kernel(SplitTpArgs a) {
+__global__ void __launch_bounds__(kTpThreads, 3) split_qkv_tp_kernel(SplitTpArgs a) {
   using namespace ptx;
   constexpr int V = 8, W = 4, PW = 2;
   extern __shared__ __align__(16) uint8_t smem[];
-  __shared__ __align__(8) uint64_t s_full[8], s_empty[8];
-  __shared__ float s_part[kTpWarps][2];
+  __shared__ __align__(8) uint64_t s_full[8], s_empty[8], s_summed[8], s_gathered[8];
+  __shared__ float s_part[kTpSumWarps][2];
+  __shared__ float s_sum[8][2];                   // per stage: this rank's means of the stage's token
+  __shared__ float s_gather[8][kTpMaxRanks][2];   // per stage: every rank's means (peer mode)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qh = a.q_hidden, kvh = a.kv_hidden, row = qh + 2 * kvh, hd = a.head_dim;
   const int rd = a.rotary_dim, half = rd / 2;
   const int S = a.stages, stage_bytes = tp_stage_bytes(row, rd);
   const T* s_w = reinterpret_cast<const T*>(smem + S * stage_bytes);  // [q_hidden | kv_hidden] norm weights
   const unsigned batch = (unsigned)a.batch;
+  const bool do_sums = a.mode != kTpApply, do_apply = a.mode != kTpSums;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < S; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), kTpWarps); }
+    const int readers = (do_sums ? kTpSumWarps : 0) + (do_apply ? kTpApplyWarps : 0);
+    for (int s = 0; s < S; ++s) {
+      mbar_init(smem_u32(&s_full[s]), 1);
+      mbar_init(smem_u32(&s_empty[s]), readers);
+      mbar_init(smem_u32(&s_summed[s]), 1);
+      mbar_init(smem_u32(&s_gathered[s]), 1);
+    }
     fence_mbar_init();
   }
-  if (a.mode != kTpSums) {
+  if (do_apply) {
     uint32_t* dst = reinterpret_cast<uint32_t*>(smem + S * stage_bytes);
     for (int i = threadIdx.x; i < qh / 2; i += kTpThreads) dst[i] = reinterpret_cast<const uint32_t*>(a.q_weight)[i];
     for (int i = threadIdx.x; i < kvh / 2; i += kTpThreads) dst[qh / 2 + i] = reinterpret_cast<const uint32_t*>(a.k_weight)[i];
   }
   __syncthreads();
+  const uint32_t full0 = smem_u32(&s_full[0]), empty0 = smem_u32(&s_empty[0]);
 
-  if (warp == kTpWarps) {  // producer: one token per stage
+  if (warp == kTpProducerWarp) {  // one token per stage
     if (lane == 0) {
       unsigned it = 0;
       for (unsigned t = blockIdx.x; t < batch; t += gridDim.x, ++it) {
         const int stage = (int)(it % S);
-        if (it >= (unsigned)S) mbar_wait_light(smem_u32(&s_empty[stage]), ((it / S) - 1) & 1);
-        const uint32_t bar = smem_u32(&s_full[stage]);
+        if (it >= (unsigned)S) mbar_wait_light(empty0 + 8 * stage, ((it / S) - 1) & 1);
+        const uint32_t bar = full0 + 8 * stage;
         const uint32_t dst = smem_u32(smem + stage * stage_bytes);
-        const bool rope = a.mode != kTpSums;
-        mbar_arrive_expect_tx(bar, 2u * row + (rope ? 4u * rd : 0u));
+        mbar_arrive_expect_tx(bar, 2u * row + (do_apply ? 4u * rd : 0u));
         bulk_load_1d(dst, reinterpret_cast<const T*>(a.qkv) + (long long)t * row, 2u * row, bar);
-        if (rope) {
+        if (do_apply) {
           bulk_load_1d(dst + 2 * row, reinterpret_cast<const T*>(a.cos) + (long long)t * rd, 2u * rd, bar);
           bulk_load_1d(dst + 2 * row + 2 * rd, reinterpret_cast<const T*>(a.sin) + (long long)t * rd, 2u * rd, bar);
         }
@@ -115,57 +132,107 @@ __global__ void __launch_bounds__(kTpThreads, 2) split_qkv_tp_kernel(SplitTpArgs
     return;
   }
 
-  // a head is hd / 8 lanes; a lane owns two 4-element slices chosen so that a neox pair sits in one lane (as in the vector kernel)
+  if (warp == kTpGatherWarp) {  // peer mode: lane r waits for rank r's records of the CTA's tokens, in order, in this GPU's own
+    if (a.mode == kTpPeer) {    // buffer (a poll costs an L2 round trip: kept off the working warps)
+      const unsigned long long rec0 = (a.epoch & 1u) * ((unsigned long long)a.tp_world * a.capacity * 16ull);
+      unsigned it = 0;
+      for (unsigned t = blockIdx.x; t < batch; t += gridDim.x, ++it) {
+        const int stage = (int)(it % S);
+        if (it >= (unsigned)S) mbar_wait_light(empty0 + 8 * stage, ((it / S) - 1) & 1);  // s_gather[stage] has been read
+        if (lane < a.tp_world) {
+          const unsigned long long src = a.peer[a.tp_rank] + rec0 + ((unsigned long long)lane * a.capacity + t) * 16ull;
+          s_gather[stage][lane][0] = ld_record(src, a.epoch);
+          s_gather[stage][lane][1] = ld_record(src + 8, a.epoch);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&s_gathered[stage]));
+      }
+    }
+    return;
+  }
+
+  if (warp >= kTpApplyWarps) {  // sum warps
+    if (!do_sums) return;
+    const int sw = warp - kTpApplyWarps, tid = sw * 32 + lane;
+    const int nvq = qh / V, nvk = kvh / V;
+    const unsigned long long rec0 = (a.epoch & 1u) * ((unsigned long long)a.tp_world * a.capacity * 16ull);
+    unsigned it = 0;
+    for (unsigned t = blockIdx.x; t < batch; t += gridDim.x, ++it) {
+      const int stage = (int)(it % S);
+      mbar_wait_light(full0 + 8 * stage, (it / S) & 1);
+      const uint8_t* st = smem + stage * stage_bytes;
+      // 16-byte vectors, fp32, two-wide accumulation; q and k columns apart
+      float2 aq = make_float2(0.f, 0.f), ak = make_float2(0.f, 0.f);
+      for (int v = tid; v < nvq + nvk; v += kTpSumWarps * 32) {
+        const uint4 r = *reinterpret_cast<const uint4*>(st + v * 16);
+        const uint32_t w4[4] = {r.x, r.y, r.z, r.w};
+        float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          const float2 x = make_float2(Act<T>::lo(w4[p]), Act<T>::hi(w4[p]));
+          acc = fma2(x, x, acc);
+        }
+        if (v < nvq) { aq.x += acc.x; aq.y += acc.y; } else { ak.x += acc.x; ak.y += acc.y; }
+      }
+      float sq = aq.x + aq.y, sk = ak.x + ak.y;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        sq += __shfl_xor_sync(0xffffffffu, sq, o);
+        sk += __shfl_xor_sync(0xffffffffu, sk, o);
+      }
+      if (lane == 0) { s_part[sw][0] = sq; s_part[sw][1] = sk; }
+      named_bar_sync(1, kTpSumWarps * 32);
+      sq = sk = 0.f;
+#pragma unroll
+      for (int w = 0; w < kTpSumWarps; ++w) { sq += s_part[w][0]; sk += s_part[w][1]; }
+      const float var_q = sq / (float)qh, var_k = sk / (float)kvh;
+      if (a.mode == kTpPeer) {
+        if (tid < a.tp_world) {  // one thread per destination rank (this rank's own buffer included)
+          const unsigned long long dst = a.peer[tid] + rec0 + ((unsigned long long)a.tp_rank * a.capacity + t) * 16ull;
+          st_record(dst, var_q, a.epoch);
+          st_record(dst + 8, var_k, a.epoch);
+        }
+      } else if (tid == 0) {
+        if (a.mode == kTpSums) { a.qk_var[2 * (long long)t] = var_q; a.qk_var[2 * (long long)t + 1] = var_k; }
+        else { s_sum[stage][0] = var_q; s_sum[stage][1] = var_k; mbar_arrive(smem_u32(&s_summed[stage])); }
+      }
+      named_bar_sync(1, kTpSumWarps * 32);  // s_part may be rewritten; both warps are done with the stage
+      if (lane == 0) mbar_arrive(empty0 + 8 * stage);
+    }
+    return;
+  }
+
+  // apply warps.  A head is hd / 8 lanes; a lane owns two 4-element slices chosen so that a neox pair sits in one lane.
+  if (!do_apply) return;
   const int L = hd / V, heads_per_warp = 32 / L;
   const int j = lane % L;
   const bool in_rope = j * W < half;
   const int oA = in_rope ? j * W : rd + V * (j - half / W);
   const int oB = in_rope ? half + j * W : oA + W;
   const int nq = qh / hd, nk = kvh / hd;
-  const uint32_t full0 = smem_u32(&s_full[0]), empty0 = smem_u32(&s_empty[0]);
-
-  __shared__ float s_gather[kTpMaxRanks][2];
-  // means of x^2 over this rank's q and k columns of the row in stage `st` (all 8 warps; ends with every thread past s_part)
-  auto local_means = [&](const uint8_t* st, float& var_q, float& var_k) {
-    // local sums of squares over the q and the k columns: 16-byte vectors, fp32, two-wide accumulation
-    float2 aq = make_float2(0.f, 0.f), ak = make_float2(0.f, 0.f);
-    const int nvq = qh / V, nvk = kvh / V;
-    for (int v = threadIdx.x; v < nvq + nvk; v += kTpWarps * 32) {
-      const uint4 r = *reinterpret_cast<const uint4*>(st + v * 16);
-      const uint32_t w4[4] = {r.x, r.y, r.z, r.w};
-      float2 acc = make_float2(0.f, 0.f);
-#pragma unroll
-      for (int p = 0; p < 4; ++p) {
-        const float2 x = make_float2(Act<T>::lo(w4[p]), Act<T>::hi(w4[p]));
-        acc = fma2(x, x, acc);
-      }
-      if (v < nvq) { aq.x += acc.x; aq.y += acc.y; } else { ak.x += acc.x; ak.y += acc.y; }
+  unsigned it = 0;
+  for (unsigned t = blockIdx.x; t < batch; t += gridDim.x, ++it) {
+    const int stage = (int)(it % S);
+    const uint8_t* st = smem + stage * stage_bytes;
+    mbar_wait_light(full0 + 8 * stage, (it / S) & 1);
+    float var_q = 0.f, var_k = 0.f;
+    if (a.mode == kTpFused) {
+      mbar_wait_light(smem_u32(&s_summed[stage]), (it / S) & 1);
+      var_q = s_sum[stage][0];
+      var_k = s_sum[stage][1];
+    } else if (a.mode == kTpPeer) {
+      mbar_wait_light(smem_u32(&s_gathered[stage]), (it / S) & 1);
+      for (int r = 0; r < a.tp_world; ++r) { var_q += s_gather[stage][r][0]; var_k += s_gather[stage][r][1]; }  // rank order: same bits everywhere
+    } else {
+      var_q = a.qk_var[2 * (long long)t];
+      var_k = a.qk_var[2 * (long long)t + 1];
     }
-    float sq = aq.x + aq.y, sk = ak.x + ak.y;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      sq += __shfl_xor_sync(0xffffffffu, sq, o);
-      sk += __shfl_xor_sync(0xffffffffu, sk, o);
-    }
-    if (lane == 0) { s_part[warp][0] = sq; s_part[warp][1] = sk; }
-    named_bar_sync(1, kTpWarps * 32);
-    sq = sk = 0.f;
-#pragma unroll
-    for (int w = 0; w < kTpWarps; ++w) { sq += s_part[w][0]; sk += s_part[w][1]; }
-    var_q = sq / (float)qh;
-    var_k = sk / (float)kvh;
-    named_bar_sync(1, kTpWarps * 32);  // s_part may be rewritten
-  };
-  // normalise, rotate and store token t from the row in stage `st`, copy v; then hand the stage back
-  auto apply = [&](const uint8_t* st, int stage, unsigned t, float var_q, float var_k) {
     const float scale_q = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var_q * a.inv_tp_world, a.eps)));
     const float scale_k = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var_k * a.inv_tp_world, a.eps)));
-
-    // v: copy
-    {
+    {  // v: copy
       const uint4* src = reinterpret_cast<const uint4*>(st + 2 * (qh + kvh));
       uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<T*>(a.v_out) + (long long)t * kvh);
-      for (int v = threadIdx.x; v < kvh / V; v += kTpWarps * 32) dst[v] = src[v];
+      for (int v = threadIdx.x; v < kvh / V; v += kTpApplyWarps * 32) dst[v] = src[v];
     }
     // cos / sin of the lane's pairs (one value per pair), sign folded into the first slice's sin
     float2 cs[PW], snA[PW], snB[PW];
@@ -178,7 +245,7 @@ __global__ void __launch_bounds__(kTpThreads, 2) split_qkv_tp_kernel(SplitTpArgs
       snA[0] = make_float2(-snB[0].x, -snB[0].y);
       snA[1] = make_float2(-snB[1].x, -snB[1].y);
     }
-    for (int h0 = warp * heads_per_warp; h0 < nq + nk; h0 += kTpWarps * heads_per_warp) {
+    for (int h0 = warp * heads_per_warp; h0 < nq + nk; h0 += kTpApplyWarps * heads_per_warp) {
       const int head = h0 + lane / L;
       if (head >= nq + nk) continue;
       const bool is_q = head < nq;
@@ -209,63 +276,8 @@ __global__ void __launch_bounds__(kTpThreads, 2) split_qkv_tp_kernel(SplitTpArgs
       *reinterpret_cast<uint2*>(dst + oA) = make_uint2(oa[0], oa[1]);
       *reinterpret_cast<uint2*>(dst + oB) = make_uint2(ob[0], ob[1]);
     }
-    named_bar_sync(1, kTpWarps * 32);  // every warp is done with the stage
+    __syncwarp();  // the warp is done with the stage
     if (lane == 0) mbar_arrive(empty0 + 8 * stage);
-  };
-
-  if (a.mode == kTpPeer) {
-    const int tp = a.tp_world, D = S > 2 ? S - 2 : 1;  // tokens between a token's sums and its apply: hides the exchange
-    const unsigned n_local = blockIdx.x < batch ? (batch - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-    const unsigned long long half_bytes = (unsigned long long)tp * a.capacity * 16ull;
-    const unsigned long long rec0 = (a.epoch & 1u) * half_bytes;
-    for (unsigned i = 0; i < n_local + D; ++i) {
-      if (i < n_local) {
-        const unsigned t = blockIdx.x + i * gridDim.x;
-        const int stage = (int)(i % S);
-        mbar_wait_light(full0 + 8 * stage, (i / S) & 1);
-        float vq, vk;
-        local_means(smem + stage * stage_bytes, vq, vk);
-        if ((int)threadIdx.x < tp) {  // one thread per destination rank
-          const unsigned long long dst = a.peer[threadIdx.x] + rec0 + ((unsigned long long)a.tp_rank * a.capacity + t) * 16ull;
-          st_record(dst, vq, a.epoch);
-          st_record(dst + 8, vk, a.epoch);
-        }
-      }
-      if (i >= (unsigned)D) {
-        const unsigned jn = i - D, t = blockIdx.x + jn * gridDim.x;
-        const int stage = (int)(jn % S);
-        if ((int)threadIdx.x < tp) {  // one thread per source rank, records in this GPU's own buffer
-          const unsigned long long src = a.peer[a.tp_rank] + rec0 + ((unsigned long long)threadIdx.x * a.capacity + t) * 16ull;
-          s_gather[threadIdx.x][0] = ld_record(src, a.epoch);
-          s_gather[threadIdx.x][1] = ld_record(src + 8, a.epoch);
-        }
-        named_bar_sync(1, kTpWarps * 32);
-        float vq = 0.f, vk = 0.f;
-        for (int r = 0; r < tp; ++r) { vq += s_gather[r][0]; vk += s_gather[r][1]; }  // rank order: the same bits on every rank
-        apply(smem + stage * stage_bytes, stage, t, vq, vk);  // its closing barrier also frees s_gather
-      }
-    }
-    return;
-  }
-
-  unsigned it = 0;
-  for (unsigned t = blockIdx.x; t < batch; t += gridDim.x, ++it) {
-    const int stage = (int)(it % S);
-    mbar_wait_light(full0 + 8 * stage, (it / S) & 1);
-    const uint8_t* st = smem + stage * stage_bytes;
-    float var_q, var_k;
-    if (a.mode != kTpApply) {
-      local_means(st, var_q, var_k);
-      if (a.mode == kTpSums) {
-        if (threadIdx.x == 0) { a.qk_var[2 * (long long)t] = var_q; a.qk_var[2 * (long long)t + 1] = var_k; }
-        if (lane == 0) mbar_arrive(empty0 + 8 * stage);
-        continue;
-      }
-    } else {
-      var_q = a.qk_var[2 * (long long)t];
-      var_k = a.qk_var[2 * (long long)t + 1];
-    }
-    apply(st, stage, t, var_q, var_k);
   }
 }
 
