@@ -1,7 +1,7 @@
-"""split_qkv_tp_rmsnorm_rope over a real tensor-parallel group: two ranks, one GPU each.  Both exchanges: the one-kernel form
+"""split_qkv_tp_rmsnorm_rope over a real tensor-parallel group: 2 and 4 ranks, one GPU each.  Both exchanges: the one-kernel form
 (per-token means exchanged inside the kernel through symmetric memory over NVLink; several calls back to back so that both
 buffer halves and the epoch logic are exercised) and the NCCL all-reduce of the means between the two kernel launches (the
-reference's dist.all_reduce, split_qkv_tp_rmsnorm_rope.py:253-254).  Needs two GPUs; on a
+reference's dist.all_reduce, split_qkv_tp_rmsnorm_rope.py:253-254).  Needs two (four) GPUs; on a
 one-GPU box the same arithmetic is covered by tests/test_split_qkv.py::test_cuda_tp_vs_oracle (ranks run one after the other)."""
 import os
 
@@ -49,13 +49,14 @@ def _rank(rank, world, port, case, ret):
 
 
 @pytest.mark.gpu
-def test_two_ranks_nccl():
-    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
-        pytest.skip("needs two GPUs")
+@pytest.mark.parametrize("world", [2, 4])
+def test_ranks_nccl(world):
+    if not torch.cuda.is_available() or torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     ret = ctx.Manager().dict()
-    procs = [ctx.Process(target=_rank, args=(r, 2, 29517, (96, 2048, 512, 128, 64), ret)) for r in range(2)]
+    procs = [ctx.Process(target=_rank, args=(r, world, 29517 + world, (96, 2048, 512, 128, 64), ret)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
@@ -64,5 +65,5 @@ def test_two_ranks_nccl():
         if p.is_alive():
             p.kill()
             pytest.fail("rank did not finish")
-    assert ret.get(0) is True and ret.get(1) is True, dict(ret)
-    assert not ret.get("notes0") and not ret.get("notes1"), dict(ret)
+    assert all(ret.get(r) is True for r in range(world)), dict(ret)
+    assert not any(ret.get("notes%d" % r) for r in range(world)), dict(ret)
