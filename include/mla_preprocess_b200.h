@@ -200,14 +200,15 @@ int split_qkv_tp_rmsnorm_rope_launch(const void* qkv, const void* cos, const voi
  * each other's memory (NVLink peer stores of 8-byte {value, epoch} records), instead of an all-reduce between two launches.  No
  * reference counterpart (the reference calls dist.all_reduce, split_qkv_tp_rmsnorm_rope.py:253-254).  peer_buffers: host array of
  * tp_world device pointers, entry r = rank r's exchange buffer as mapped in THIS process (entry tp_rank is this GPU's own), each
- * 2 * tp_world * capacity * 16 bytes, zeroed once before the first call.  epoch: the same non-zero value on every rank,
- * incremented by one per call (its parity picks the buffer half).  Every rank must make the same sequence of calls with the same
- * batch <= capacity; a peer that never arrives becomes a trap (launch failure) after a bounded wait.
+ * 2 * tp_world * capacity * 16 bytes, zeroed once before the first call.  epoch_state: two uint32 in THIS GPU's memory, set to
+ * {1, 0} once on every rank; the kernel reads the call's epoch there and its last CTA advances it (its parity picks the buffer
+ * half), so replays of a captured CUDA graph work like eager calls.  Every rank must make the same sequence of calls with the
+ * same batch <= capacity; a peer that never arrives becomes a trap (launch failure) after a bounded wait.
  */
 int split_qkv_tp_rmsnorm_rope_peer_launch(const void* qkv, const void* cos, const void* sin, void* q_out, void* k_out, void* v_out,
                                           const void* q_weight, const void* k_weight, int64_t batch, int32_t q_hidden, int32_t kv_hidden,
                                           int32_t head_dim, int32_t rotary_dim, float eps, const void* const* peer_buffers, int32_t tp_rank,
-                                          int32_t tp_world, uint32_t epoch, int32_t capacity, int32_t act_dtype, void* stream);
+                                          int32_t tp_world, void* epoch_state, int32_t capacity, int32_t act_dtype, void* stream);
 
 /*
  * split_qkvgate_gemma_rmsnorm_rope (same reference module, split_qkv_rmsnorm_rope.py:441-747): the fused row is

@@ -776,12 +776,12 @@ int split_qkv_rmsnorm_mrope_launch(const void* qkv, const void* cos_sin, int32_t
 static int split_qkv_tp_impl(const void* qkv, const void* cos, const void* sin, void* q_out, void* k_out, void* v_out,
                              const void* q_weight, const void* k_weight, void* qk_var, int64_t batch, int32_t q_hidden,
                              int32_t kv_hidden, int32_t head_dim, int32_t rotary_dim, float eps, int32_t tp_world, int32_t mode,
-                             int32_t act_dtype, void* stream, const void* const* peers, int32_t tp_rank, uint32_t epoch, int32_t capacity) {
+                             int32_t act_dtype, void* stream, const void* const* peers, int32_t tp_rank, void* epoch_state, int32_t capacity) {
   if (!qkv) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: null qkv");
   if (mode != kTpFused && mode != kTpSums && mode != kTpApply && mode != kTpPeer) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: mode %d", mode);
-  if (mode == kTpPeer && (!peers || tp_world < 2 || tp_world > kTpMaxRanks || tp_rank < 0 || tp_rank >= tp_world || epoch == 0 || batch > capacity))
-    return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope (peer exchange): tp_rank=%d tp_world=%d (2..%d) epoch=%u batch=%lld capacity=%d",
-                tp_rank, tp_world, kTpMaxRanks, epoch, (long long)batch, capacity);
+  if (mode == kTpPeer && (!peers || tp_world < 2 || tp_world > kTpMaxRanks || tp_rank < 0 || tp_rank >= tp_world || !epoch_state || batch > capacity))
+    return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope (peer exchange): tp_rank=%d tp_world=%d (2..%d) epoch_state=%p batch=%lld capacity=%d",
+                tp_rank, tp_world, kTpMaxRanks, epoch_state, (long long)batch, capacity);
   if (mode != kTpSums && (!cos || !sin || !q_out || !k_out || !v_out || !q_weight || !k_weight))
     return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: null pointer");
   if ((mode == kTpSums || mode == kTpApply) && !qk_var) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: qk_var is needed for the two-phase modes");
@@ -805,7 +805,7 @@ static int split_qkv_tp_impl(const void* qkv, const void* cos, const void* sin, 
       return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: a row of %d elements does not fit shared memory twice", row);
   }
   SplitTpArgs a{qkv, cos, sin, q_out, k_out, v_out, q_weight, k_weight, static_cast<float*>(qk_var), batch, q_hidden, kv_hidden, head_dim,
-                rotary_dim, eps, 1.f / (float)tp_world, mode, stages, {}, tp_rank, tp_world, capacity, epoch};
+                rotary_dim, eps, 1.f / (float)tp_world, mode, stages, {}, tp_rank, tp_world, capacity, static_cast<unsigned*>(epoch_state)};
   if (mode == kTpPeer)
     for (int r = 0; r < tp_world; ++r) {
       if (!peers[r]) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope (peer exchange): null buffer of rank %d", r);
@@ -834,15 +834,15 @@ int split_qkv_tp_rmsnorm_rope_launch(const void* qkv, const void* cos, const voi
                                      int32_t act_dtype, void* stream) {
   if (mode == kTpPeer) return fail(MLAPO_ERR_INVALID_ARG, "split_qkv_tp_rmsnorm_rope: the peer-exchange mode has its own entry point");
   return split_qkv_tp_impl(qkv, cos, sin, q_out, k_out, v_out, q_weight, k_weight, qk_var, batch, q_hidden, kv_hidden, head_dim, rotary_dim, eps,
-                           tp_world, mode, act_dtype, stream, nullptr, 0, 0, 0);
+                           tp_world, mode, act_dtype, stream, nullptr, 0, nullptr, 0);
 }
 
 int split_qkv_tp_rmsnorm_rope_peer_launch(const void* qkv, const void* cos, const void* sin, void* q_out, void* k_out, void* v_out,
                                           const void* q_weight, const void* k_weight, int64_t batch, int32_t q_hidden, int32_t kv_hidden,
                                           int32_t head_dim, int32_t rotary_dim, float eps, const void* const* peer_buffers, int32_t tp_rank,
-                                          int32_t tp_world, uint32_t epoch, int32_t capacity, int32_t act_dtype, void* stream) {
+                                          int32_t tp_world, void* epoch_state, int32_t capacity, int32_t act_dtype, void* stream) {
   return split_qkv_tp_impl(qkv, cos, sin, q_out, k_out, v_out, q_weight, k_weight, nullptr, batch, q_hidden, kv_hidden, head_dim, rotary_dim, eps,
-                           tp_world, kTpPeer, act_dtype, stream, peer_buffers, tp_rank, epoch, capacity);
+                           tp_world, kTpPeer, act_dtype, stream, peer_buffers, tp_rank, epoch_state, capacity);
 }
 
 int split_qkvgate_gemma_rmsnorm_rope_launch(const void* qkvgate, const void* sin, const void* cos, void* q_out, void* k_out, void* v_out,

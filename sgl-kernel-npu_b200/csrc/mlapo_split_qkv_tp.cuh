@@ -44,7 +44,8 @@ struct SplitTpArgs {
   // kTpPeer: exchange buffer of every rank as mapped here, [2 halves][tp_world sources][capacity tokens][2 records of 8 bytes]
   unsigned long long peer[kTpMaxRanks];
   int tp_rank, tp_world, capacity;
-  unsigned epoch;  // of this call, never 0 (the buffer starts zeroed)
+  unsigned* epoch_state;  // device memory {epoch of the next call (never 0: the buffer starts zeroed), CTAs done}: read at kernel
+                          // start, advanced by the last CTA to finish, so that replays of a captured graph get fresh epochs too
 };
 
 // warps of a CTA: apply warps, sum warps, one producer warp, one gather warp (peer mode)
@@ -94,6 +95,10 @@ __global__ void __launch_bounds__(kTpThreads, 3) split_qkv_tp_kernel(SplitTpArgs
   const T* s_w = reinterpret_cast<const T*>(smem + S * stage_bytes);  // [q_hidden | kv_hidden] norm weights
   const unsigned batch = (unsigned)a.batch;
   const bool do_sums = a.mode != kTpApply, do_apply = a.mode != kTpSums;
+  // every thread reads the call's epoch before any CTA can have finished (the last CTA to finish advances it)
+  const unsigned epoch = a.mode == kTpPeer ? *reinterpret_cast<volatile unsigned*>(a.epoch_state) : 0u;
+  __shared__ unsigned s_exited;
+  if (threadIdx.x == 0) s_exited = 0;
 
   if (threadIdx.x == 0) {
     const int readers = (do_sums ? kTpSumWarps : 0) + (do_apply ? kTpApplyWarps : 0);
@@ -113,6 +118,7 @@ __global__ void __launch_bounds__(kTpThreads, 3) split_qkv_tp_kernel(SplitTpArgs
   __syncthreads();
   const uint32_t full0 = smem_u32(&s_full[0]), empty0 = smem_u32(&s_empty[0]);
 
+  auto role = [&]() {
   if (warp == kTpProducerWarp) {  // one token per stage
     if (lane == 0) {
       unsigned it = 0;
@@ -134,15 +140,15 @@ __global__ void __launch_bounds__(kTpThreads, 3) split_qkv_tp_kernel(SplitTpArgs
 
   if (warp == kTpGatherWarp) {  // peer mode: lane r waits for rank r's records of the CTA's tokens, in order, in this GPU's own
     if (a.mode == kTpPeer) {    // buffer (a poll costs an L2 round trip: kept off the working warps)
-      const unsigned long long rec0 = (a.epoch & 1u) * ((unsigned long long)a.tp_world * a.capacity * 16ull);
+      const unsigned long long rec0 = (epoch & 1u) * ((unsigned long long)a.tp_world * a.capacity * 16ull);
       unsigned it = 0;
       for (unsigned t = blockIdx.x; t < batch; t += gridDim.x, ++it) {
         const int stage = (int)(it % S);
         if (it >= (unsigned)S) mbar_wait_light(empty0 + 8 * stage, ((it / S) - 1) & 1);  // s_gather[stage] has been read
         if (lane < a.tp_world) {
           const unsigned long long src = a.peer[a.tp_rank] + rec0 + ((unsigned long long)lane * a.capacity + t) * 16ull;
-          s_gather[stage][lane][0] = ld_record(src, a.epoch);
-          s_gather[stage][lane][1] = ld_record(src + 8, a.epoch);
+          s_gather[stage][lane][0] = ld_record(src, epoch);
+          s_gather[stage][lane][1] = ld_record(src + 8, epoch);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&s_gathered[stage]));
@@ -155,7 +161,7 @@ __global__ void __launch_bounds__(kTpThreads, 3) split_qkv_tp_kernel(SplitTpArgs
     if (!do_sums) return;
     const int sw = warp - kTpApplyWarps, tid = sw * 32 + lane;
     const int nvq = qh / V, nvk = kvh / V;
-    const unsigned long long rec0 = (a.epoch & 1u) * ((unsigned long long)a.tp_world * a.capacity * 16ull);
+    const unsigned long long rec0 = (epoch & 1u) * ((unsigned long long)a.tp_world * a.capacity * 16ull);
     unsigned it = 0;
     for (unsigned t = blockIdx.x; t < batch; t += gridDim.x, ++it) {
       const int stage = (int)(it % S);
@@ -189,8 +195,8 @@ __global__ void __launch_bounds__(kTpThreads, 3) split_qkv_tp_kernel(SplitTpArgs
       if (a.mode == kTpPeer) {
         if (tid < a.tp_world) {  // one thread per destination rank (this rank's own buffer included)
           const unsigned long long dst = a.peer[tid] + rec0 + ((unsigned long long)a.tp_rank * a.capacity + t) * 16ull;
-          st_record(dst, var_q, a.epoch);
-          st_record(dst + 8, var_k, a.epoch);
+          st_record(dst, var_q, epoch);
+          st_record(dst + 8, var_k, epoch);
         }
       } else if (tid == 0) {
         if (a.mode == kTpSums) { a.qk_var[2 * (long long)t] = var_q; a.qk_var[2 * (long long)t + 1] = var_k; }
@@ -278,6 +284,17 @@ __global__ void __launch_bounds__(kTpThreads, 3) split_qkv_tp_kernel(SplitTpArgs
     }
     __syncwarp();  // the warp is done with the stage
     if (lane == 0) mbar_arrive(empty0 + 8 * stage);
+  }
+  };
+  role();
+  // peer mode: the last warp of the last CTA to finish advances the epoch for the next call (0xFFFFFFFE -> 1 keeps the parity alternating)
+  if (a.mode == kTpPeer && lane == 0 && atomicAdd(&s_exited, 1u) == kTpThreads / 32 - 1) {
+    __threadfence();
+    if (atomicAdd(a.epoch_state + 1, 1u) == gridDim.x - 1) {
+      a.epoch_state[1] = 0;
+      __threadfence();
+      *reinterpret_cast<volatile unsigned*>(a.epoch_state) = epoch >= 0xFFFFFFFEu ? 1u : epoch + 1u;
+    }
   }
 }
 

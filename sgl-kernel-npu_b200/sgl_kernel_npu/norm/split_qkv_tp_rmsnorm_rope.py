@@ -18,7 +18,7 @@ CAPACITY = 16384  # tokens per call the exchange buffer holds (2 * tp_world * CA
 _state = {}
 
 cabi.lib.split_qkv_tp_rmsnorm_rope_peer_launch.argtypes = [ctypes.c_void_p] * 8 + [ctypes.c_int64] + [ctypes.c_int32] * 4 + [ctypes.c_float] + \
-    [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_uint32, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
+    [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p]
 
 
 def _exchange_state(tp_group, tp_world, device):
@@ -30,11 +30,12 @@ def _exchange_state(tp_group, tp_world, device):
             import torch.distributed._symmetric_memory as symm_mem
             buf = symm_mem.empty(2 * tp_world * CAPACITY * 4, dtype=torch.float32, device=device)
             buf.zero_()
+            epoch = torch.tensor([1, 0], dtype=torch.int32, device=device)  # {next call's epoch, CTAs done}: advanced by the kernel
             hdl = symm_mem.rendezvous(buf, group)
             torch.cuda.synchronize(device)
             dist.barrier(group=group)  # every rank's buffer is zeroed before any rank publishes into it
             ptrs = (ctypes.c_void_p * tp_world)(*[int(p) for p in hdl.buffer_ptrs])
-            _state[key] = dict(buf=buf, hdl=hdl, ptrs=ptrs, epoch=0, rank=dist.get_rank(group))
+            _state[key] = dict(buf=buf, hdl=hdl, ptrs=ptrs, epoch=epoch, rank=dist.get_rank(group))
         except Exception as e:  # no peer access / no symmetric memory here: the all-reduce path is the reference's own
             warnings.warn(f"split_qkv_tp_rmsnorm_rope: symmetric memory unavailable ({e!r}); using dist.all_reduce")
             _state[key] = None
@@ -81,12 +82,11 @@ def split_qkv_tp_rmsnorm_rope(input, cos, sin, q_hidden_size, kv_hidden_size, he
         return q, k, v
     st = _exchange_state(tp_group, tp_world, input.device) if EXCHANGE == "peer" and batch <= CAPACITY and tp_world <= 8 else None
     if st is not None:
-        st["epoch"] = st["epoch"] % 0xFFFFFFFF + 1  # never 0; the same sequence on every rank
         with torch.cuda.device(input.device):
             cabi._check(cabi.lib.split_qkv_tp_rmsnorm_rope_peer_launch(
                 input.data_ptr(), cos.data_ptr(), sin.data_ptr(), q.data_ptr(), k.data_ptr(), v.data_ptr(), q_weight.data_ptr(),
                 k_weight.data_ptr(), batch, q_hidden_size, kv_hidden_size, head_dim, rotary_dim, float(eps), st["ptrs"], st["rank"], tp_world,
-                st["epoch"], CAPACITY, 0 if input.dtype == torch.bfloat16 else 1, cabi._stream_ptr(input)), "split_qkv_tp_rmsnorm_rope_peer_launch")
+                st["epoch"].data_ptr(), CAPACITY, 0 if input.dtype == torch.bfloat16 else 1, cabi._stream_ptr(input)), "split_qkv_tp_rmsnorm_rope_peer_launch")
         return q, k, v
     qk_var = torch.empty(batch, 2, dtype=torch.float32, device=input.device)
     _launch(MODE_SUMS, input, cos, sin, q, k, v, q_weight, k_weight, qk_var, *args)

@@ -42,6 +42,33 @@ def _rank(rank, world, port, case, ret):
                     same = float((got.cpu().view(torch.int16) == w.view(torch.int16)).float().mean())
                     err = float((got.float().cpu() - w.float()).abs().max())
                     ok = ok and same >= 0.99 and err <= 2 * 2.0 ** (torch.floor(torch.log2(w.float().abs().max())).item() - 7)
+        # the one-kernel form under a CUDA graph: replays must behave like eager calls (the epoch lives in device memory)
+        m.EXCHANGE = "peer"
+        b, qh, kvh, hd, rd = case
+        dev = lambda t: t.cuda(rank)
+        static_x = torch.zeros(b, qh + 2 * kvh, dtype=dt, device="cuda")
+        g = torch.Generator().manual_seed(991)
+        qws, kws = [torch.randn(qh, generator=g).to(dt) for _ in range(world)], [torch.randn(kvh, generator=g).to(dt) for _ in range(world)]
+        cos, sin = torch.rand(b, rd, generator=g).to(dt), torch.rand(b, rd, generator=g).to(dt)
+        dqw, dkw, dcos, dsin = dev(qws[rank]), dev(kws[rank]), dev(cos), dev(sin)
+        graph, stream = torch.cuda.CUDAGraph(), torch.cuda.Stream()
+        torch.cuda.synchronize()
+        with torch.cuda.stream(stream):
+            with torch.cuda.graph(graph, stream=stream):
+                gq, gk, gv = m.split_qkv_tp_rmsnorm_rope(static_x, dcos, dsin, qh, kvh, hd, 1e-6, dqw, dkw, rd, world, dist.group.WORLD)
+        for rep in range(3):
+            xs = [torch.randn(b, qh + 2 * kvh, generator=g).to(dt) * (r + 1) for r in range(world)]
+            want = sq.split_qkv_tp_rmsnorm_rope(xs, cos, sin, qh, kvh, hd, 1e-6, qws, kws, rd)[rank]
+            static_x.copy_(dev(xs[rank]))
+            torch.cuda.synchronize()
+            graph.replay()
+            torch.cuda.synchronize()
+            ok = ok and torch.equal(gv.cpu(), want[2])
+            for got, w in ((gq, want[0]), (gk, want[1])):
+                same = float((got.cpu().view(torch.int16) == w.view(torch.int16)).float().mean())
+                if same < 0.99:
+                    notes.append("graph replay %d: identical fraction %.4f" % (rep, same))
+                ok = ok and same >= 0.99
         ret["notes%d" % rank] = notes
         ret[rank] = bool(ok)
     finally:
