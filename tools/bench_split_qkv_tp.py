@@ -24,7 +24,7 @@ def main():
         xs = [torch.randn(b, qh + 2 * kvh, device=dev).to(dt) for _ in range(sets)]
         cos, sin = torch.rand(b, rd, device=dev).to(dt), torch.rand(b, rd, device=dev).to(dt)
         qw, kw = torch.randn(qh, device=dev).to(dt), torch.randn(kvh, device=dev).to(dt)
-        line = {"shape": [b, qh, kvh, hd, rd], "tp_world": world}
+        line = {"shape": [b, qh, kvh, hd, rd], "tp_world": world, "launch": "graph" if "--graph" in sys.argv else "eager"}
         for exchange in (("peer", "allreduce") if world > 1 else ("single",)):
             m.EXCHANGE = exchange
             call = lambda i: m.split_qkv_tp_rmsnorm_rope(xs[i % sets], cos, sin, qh, kvh, hd, 1e-6, qw, kw, rd, world, dist.group.WORLD)
@@ -32,12 +32,28 @@ def main():
                 call(i)
             torch.cuda.synchronize()
             dist.barrier()
-            reps = 5 * sets
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            for i in range(reps):
-                call(i)
-            e1.record()
+            if "--graph" in sys.argv:  # device time without the host's share: `sets` calls per graph, outputs kept alive
+                graph, stream, outs = torch.cuda.CUDAGraph(), torch.cuda.Stream(), []
+                with torch.cuda.stream(stream):
+                    with torch.cuda.graph(graph, stream=stream):
+                        for i in range(sets):
+                            outs.append(call(i))
+                    graph.replay()
+                    torch.cuda.synchronize()
+                    dist.barrier()
+                    reps = 20
+                    e0.record(stream)
+                    for _ in range(reps):
+                        graph.replay()
+                    e1.record(stream)
+                reps *= sets
+            else:
+                reps = 5 * sets
+                e0.record()
+                for i in range(reps):
+                    call(i)
+                e1.record()
             torch.cuda.synchronize()
             us = torch.tensor([e0.elapsed_time(e1) * 1e3 / reps], device=dev)
             dist.all_reduce(us, op=dist.ReduceOp.MAX)
@@ -45,6 +61,9 @@ def main():
             line[exchange + "_GBps_per_gpu"] = round(4 * b * (qh + 2 * kvh) / float(us) / 1e3, 1)
         if rank == 0:
             print(json.dumps(line), flush=True)
+    if "--graph" in sys.argv:  # captured graphs hold the communicator: tearing the group down under them stalls for minutes
+        sys.stdout.flush()
+        os._exit(0)
     dist.destroy_process_group()
 
 
