@@ -233,8 +233,11 @@ __global__ void __launch_bounds__(kTpThreads, 3) split_qkv_tp_kernel(SplitTpArgs
       var_q = a.qk_var[2 * (long long)t];
       var_k = a.qk_var[2 * (long long)t + 1];
     }
-    const float scale_q = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var_q * a.inv_tp_world, a.eps)));
-    const float scale_k = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var_k * a.inv_tp_world, a.eps)));
+    // 1/sqrt by the hardware approximation and one Newton step (below one fp32 ulp), as in the vector kernel
+    const float mq = __fadd_rn(var_q * a.inv_tp_world, a.eps), mk = __fadd_rn(var_k * a.inv_tp_world, a.eps);
+    const float yq = rsqrtf(mq), yk = rsqrtf(mk);
+    const float scale_q = fmaf(yq, fmaf(-(0.5f * mq) * yq, yq, 0.5f), yq);
+    const float scale_k = fmaf(yk, fmaf(-(0.5f * mk) * yk, yk, 0.5f), yk);
     {  // v: copy
       const uint4* src = reinterpret_cast<const uint4*>(st + 2 * (qh + kvh));
       uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<T*>(a.v_out) + (long long)t * kvh);
