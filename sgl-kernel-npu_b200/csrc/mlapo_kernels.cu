@@ -812,19 +812,26 @@ static int split_qkv_tp_impl(const void* qkv, const void* cos, const void* sin, 
       a.peer[r] = reinterpret_cast<unsigned long long>(peers[r]);
     }
   const int smem = tp_smem_bytes(row, rotary_dim, q_hidden, kv_hidden, stages);
-  // the peer-exchange mode needs every CTA resident at once: 3 per SM fit when a CTA takes <= 72 KB, 2 up to 110 KB, else 1
-  const unsigned resident = 148u * (smem <= 72 * 1024 ? 3u : smem <= 110 * 1024 ? 2u : 1u);
-  const unsigned blocks = batch < resident ? (unsigned)batch : resident;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  cudaError_t e;
-  if (act_dtype == MLAPO_ACT_BF16) {
-    e = cudaFuncSetAttribute(split_qkv_tp_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e == cudaSuccess) split_qkv_tp_kernel<__nv_bfloat16><<<blocks, kTpThreads, smem, st>>>(a);
-  } else {
-    e = cudaFuncSetAttribute(split_qkv_tp_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e == cudaSuccess) split_qkv_tp_kernel<__half><<<blocks, kTpThreads, smem, st>>>(a);
+  const bool bf = act_dtype == MLAPO_ACT_BF16;
+  cudaError_t e = bf ? cudaFuncSetAttribute(split_qkv_tp_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                     : cudaFuncSetAttribute(split_qkv_tp_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  // The grid is what the device holds at once (asked of the runtime, not assumed): the peer-exchange mode needs every CTA resident,
+  // since a CTA waits for records that the same CTA index publishes on the other ranks.
+  int per_sm = 0, dev = 0, sms = 0;
+  if (e == cudaSuccess)
+    e = bf ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, split_qkv_tp_kernel<__nv_bfloat16>, kTpThreads, smem)
+           : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, split_qkv_tp_kernel<__half>, kTpThreads, smem);
+  if (e == cudaSuccess) e = cudaGetDevice(&dev);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (e == cudaSuccess && (per_sm < 1 || sms < 1)) return fail(MLAPO_ERR_CUDA, "split_qkv_tp_rmsnorm_rope: the kernel does not fit an SM (%d bytes of shared memory)", smem);
+  if (e == cudaSuccess) {
+    const unsigned resident = (unsigned)per_sm * (unsigned)sms;
+    const unsigned blocks = batch < resident ? (unsigned)batch : resident;
+    if (bf) split_qkv_tp_kernel<__nv_bfloat16><<<blocks, kTpThreads, smem, st>>>(a);
+    else split_qkv_tp_kernel<__half><<<blocks, kTpThreads, smem, st>>>(a);
+    e = cudaGetLastError();
   }
-  if (e == cudaSuccess) e = cudaGetLastError();
   return e == cudaSuccess ? MLAPO_OK : fail(MLAPO_ERR_CUDA, "split_qkv_tp_rmsnorm_rope launch: %s", cudaGetErrorString(e));
 }
 
