@@ -467,7 +467,7 @@ static cudaError_t split_vec_launch(const SplitQkvArgs& a, cudaStream_t st) {
   const unsigned cpt = (unsigned)((row + G::CHUNK - 1) / G::CHUNK);
   const long long last_len = row - (long long)(cpt - 1) * G::CHUNK;
   const long long w_full = G::CHUNK + 512, w_last = last_len + 512;
-  const unsigned ctas = 148u * 3u;
+  const unsigned ctas = (unsigned)num_sms() * 3u;
   unsigned g_last = (unsigned)((ctas * w_last + ((cpt - 1) * w_full + w_last) / 2) / ((cpt - 1) * w_full + w_last));
   if (g_last < 1) g_last = 1;
   unsigned g_full = cpt > 1 ? (ctas - g_last) / (cpt - 1) : 0;
@@ -722,7 +722,7 @@ static int split_qkv_impl(const void* qkv, const void* sin, const void* cos, voi
   } else {
     const long long items = batch * (((gated ? 2LL : 1LL) * q_hidden + 2LL * kv_hidden) / head_dim);
     long long blocks = (items + kSplitWarps - 1) / kSplitWarps;
-    if (blocks > 148 * 32) blocks = 148 * 32;
+    if (blocks > num_sms() * 32) blocks = num_sms() * 32;
     if (bf) split_qkv_scalar_kernel<__nv_bfloat16><<<(unsigned)blocks, kSplitWarps * 32, 0, st>>>(a);
     else split_qkv_scalar_kernel<__half><<<(unsigned)blocks, kSplitWarps * 32, 0, st>>>(a);
   }
