@@ -8,7 +8,7 @@ import torch
 
 from sgl_kernel_npu.norm.split_qkv_rmsnorm_rope import split_qkv_rmsnorm_rope
 
-b, qh, kvh, hd, rd = 8192, 6144, 1024, 128, 128
+b, qh, kvh, hd, rd = (int(x) for x in (sys.argv[1:6] if len(sys.argv) > 5 else (8192, 6144, 1024, 128, 128)))
 dev = torch.device("cuda:0")
 dt = torch.bfloat16
 qkv = torch.randn(b, qh + 2 * kvh, device=dev).to(dt)
