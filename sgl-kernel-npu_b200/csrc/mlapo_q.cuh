@@ -233,7 +233,12 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
         s_cst[c] = make_int2(qa.bias1 ? qa.bias1[head * MLAPO_Q_HEAD + c] : 0, __float_as_int(dsc));
       }
     }
-    if (kStandalone) ptx::griddep_wait();  // tok_scale1 comes from the norm kernel (and keeps the PDL completion chain transitive)
+    if (kStandalone) {
+      ptx::griddep_wait();  // tok_scale1 comes from the norm kernel (and keeps the PDL completion chain transitive)
+      // dependents (the next call's quantise kernel, which stores to a0 without waiting) are signalled only now: the norm kernel, and
+      // with it this call's MM1, the last reader of a0, are complete
+      ptx::griddep_launch_dependents();
+    }
     ptx::named_bar_sync(3, 256);
 
     if (g < num_mt) {
@@ -464,7 +469,6 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
   __syncthreads();
   ptx::tc_fence_after();
   c.tmem = *tmem_slot;
-  ptx::griddep_launch_dependents();
   if (threadIdx.x == 0) tl_mark(tl, 2);  // prologue done
   if (threadIdx.x == 0 && tl) {  // which SM ran this CTA (timeline analysis only)
     unsigned smid;
@@ -546,7 +550,6 @@ q_stream_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  ptx::griddep_launch_dependents();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA: a1 + W_UQ k-blocks
@@ -665,6 +668,7 @@ q_stream_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant
       ptx::named_bar_sync(bar_id, 128);
     };
     ptx::griddep_wait();  // per-token scales come from the norm kernel
+    ptx::griddep_launch_dependents();  // only after the wait: see q_fused
 
     uint32_t it = 0;
     for (int u = blockIdx.x; u < total_units; u += gridDim.x, ++it) {

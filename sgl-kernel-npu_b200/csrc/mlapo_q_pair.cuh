@@ -90,7 +90,6 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
   ptx::cluster_wait();
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  ptx::griddep_launch_dependents();
   if (threadIdx.x == 0) tl_mark(tl, 2);
 
   if (warp == 0) {
@@ -214,6 +213,7 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
     const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
     const bool per_token = qa.tok_scale1 != nullptr;
     ptx::griddep_wait();  // per-token scales come from the norm kernel
+    ptx::griddep_launch_dependents();  // only after the wait: see q_fused
 
     if (eg < 2) {
       // ---------------- dequant set.  Group g: nope columns [64g, 64g+64) -> q_nope tile g (absorb A operand, k-block g);

@@ -98,10 +98,15 @@ __global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict_
   prefetch_weights_l2(wp);
   QuantScale qs;
   qs.load(scale, offset);
-  ptx::griddep_wait();  // a0 may still be read by the previous call's MM1 until its successors have completed
+  // No wait before the stores: this kernel runs under the tail of whatever precedes it.  When that is the previous call's q kernel,
+  // a0's last reader (that call's MM1) is complete by the time this grid can start, because every q kernel signals its dependents
+  // only AFTER its own griddepcontrol.wait (norm complete => MM1 complete, the chain being transitive); any other predecessor
+  // signals at its completion.  The wait at the END keeps the chain transitive: this grid is not complete, and so MM1 does not pass
+  // its wait and write the split-K slabs, before the predecessor is.
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 14);
   quant_vectors<T, U>(x, q, qs, n_vec8, blockIdx.x * (long long)blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 15);
+  ptx::griddep_wait();
 }
 
 // per-token symmetric (UNPINNED restatement of bf16.hpp:437-475): one row, executed by the whole CTA (any block size)

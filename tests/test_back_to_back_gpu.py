@@ -1,0 +1,50 @@
+"""Calls launched back to back on one stream with one workspace.  Consecutive calls overlap on the GPU (programmatic dependent
+launch: a call's quantise kernel stores its a0 while the previous call's q kernel is still running, its MM1 has its weight tiles in
+flight), so what one call leaves in the workspace must never reach another's results: two different inputs alternate, every
+call has its own outputs and caches, and each result must equal, bit for bit, what the same input gives when it runs alone."""
+import pytest
+import torch
+
+from oracle import mla_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+def _params(cabi, g, case):
+    return cabi.build_params(g["hiddenState"], g["wdqkv_km"], g["descale0"], g["gamma1"], g["beta1"], g["wuq_km"], g["descale1"],
+                             g["gamma2"], g["cos"], g["sin"], g["wuk"], g["kv_cache"], g["kv_cache_rope"], g["slotmapping"],
+                             g["quant_scale0"], g["quant_offset0"], g["bias0"], g["quant_scale1"], g["quant_offset1"], g["bias1"],
+                             g["ctkv_scale"], g["q_nope_scale"], case.cache_mode, "per_tensor_quant_asymm", g["q_out0"], g["q_out1"])
+
+
+@pytest.mark.parametrize("shape", [(256, 128, 7168, "krope_ctkv"), (64, 16, 7168, "int8_nzcache"), (1100, 40, 7168, "nzcache")],
+                         ids=lambda s: "n%d_h%d_d%d_%s" % s)
+def test_alternating_inputs_back_to_back(shape, cuda_device):
+    import mla_harness as hz
+    from sgl_kernel_npu import cabi
+    n, h, d, mode = shape
+    cases = [orc.gen_case(N=n, H=h, D=d, dtype=torch.bfloat16, cache_mode=mode, seed=s, num_blocks=max(12, n // 64)) for s in (11, 12)]
+    # what each input gives alone
+    alone = []
+    for c in cases:
+        g, _ = hz.run_cuda(c, cuda_device, debug=False, cache_fill=0)
+        alone.append({k: g[k].clone() for k in ("q_out0", "q_out1", "kv_cache", "kv_cache_rope")})
+    rounds = 6
+    runs = []
+    for r in range(2 * rounds):
+        c = cases[r % 2]
+        g = hz.to_device(c, cuda_device)
+        g["kv_cache"].zero_()
+        g["kv_cache_rope"].zero_()
+        g["wdqkv_km"] = cabi.repack_nz_weight(g["wdqkv"])
+        g["wuq_km"] = cabi.repack_nz_weight(g["wuq"])
+        runs.append((g, _params(cabi, g, c)))
+    lay = cabi.workspace_layout(runs[0][1])
+    ws = torch.zeros(lay.total_bytes, dtype=torch.uint8, device=cuda_device)
+    torch.cuda.synchronize(cuda_device)
+    for _, p in runs:  # no synchronisation in between
+        cabi.launch(p, ws)
+    torch.cuda.synchronize(cuda_device)
+    for r, (g, _) in enumerate(runs):
+        for k, want in alone[r % 2].items():
+            assert torch.equal(g[k], want), (r, k, int((g[k] != want).sum()))
