@@ -183,7 +183,9 @@ __device__ __forceinline__ double warp_sum_f64(double v) {
 }
 
 // One token row, executed by every thread of the CTA (threads beyond the first 288 only take part in the barriers).
-template <class T, int kMaxSplits>
+// kPdlWait: the kernel form; everything that does not come from the MM1 kernel (descale, bias, gamma / beta, cos / sin, the slot)
+// is loaded BEFORE griddepcontrol.wait, i.e. while MM1 is still running, so that only the partial sums are waited for.
+template <class T, int kMaxSplits, bool kPdlWait = false>
 __device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const int tid) {
   __shared__ double s_sum[9];
   __shared__ float s_max[9];
@@ -200,18 +202,8 @@ __device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const
   // All global loads are issued before anything is consumed (the kernel is latency-, not bandwidth-bound).
   float x[8];
   uint4 g_vec = make_uint4(0, 0, 0, 0), b_vec = make_uint4(0, 0, 0, 0);  // gamma (+beta) or cos/sin of this thread's 8 columns
+  const int slot = a.slots[t];
   {
-    int4 pu[kMaxSplits], pv[kMaxSplits];
-#pragma unroll
-    for (int s = 0; s < kMaxSplits; ++s) {
-      pu[s] = make_int4(0, 0, 0, 0);
-      pv[s] = make_int4(0, 0, 0, 0);
-      if (active && s < a.splits) {
-        const int4* p = reinterpret_cast<const int4*>(a.partial + ((long long)s * a.n_tokens + t) * MLAPO_MM1_OUT + col);
-        pu[s] = p[0];
-        pv[s] = p[1];
-      }
-    }
     float d[8];
     int bias[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (a.descale_is_i64) {
@@ -234,6 +226,21 @@ __device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const
     } else if (is_q) {
       g_vec = reinterpret_cast<const uint4*>(a.gamma1)[tid - 96];
       b_vec = reinterpret_cast<const uint4*>(a.beta1)[tid - 96];
+    }
+    if constexpr (kPdlWait) {
+      ptx::griddep_wait();  // partial sums (and the per-token scales of a0) come from the kernels before
+      if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 14);
+    }
+    int4 pu[kMaxSplits], pv[kMaxSplits];
+#pragma unroll
+    for (int s = 0; s < kMaxSplits; ++s) {
+      pu[s] = make_int4(0, 0, 0, 0);
+      pv[s] = make_int4(0, 0, 0, 0);
+      if (active && s < a.splits) {
+        const int4* p = reinterpret_cast<const int4*>(a.partial + ((long long)s * a.n_tokens + t) * MLAPO_MM1_OUT + col);
+        pu[s] = p[0];
+        pv[s] = p[1];
+      }
     }
     const float ts0 = a.tok_scale0 ? a.tok_scale0[t] : 1.f;
     int acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -267,7 +274,6 @@ __device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const
   const double tot_nope = s_sum[0] + s_sum[1];
   const double tot_q = ((s_sum[3] + s_sum[4]) + (s_sum[5] + s_sum[6])) + (s_sum[7] + s_sum[8]);
 
-  const int slot = a.slots[t];
   const bool slot_ok = slot >= 0 && (long long)slot < a.cache_slots;
   const int blk = slot >> 7, r128 = slot & 127;  // NZ modes: block size 128
 
@@ -369,9 +375,7 @@ __global__ void __launch_bounds__(kNormThreads, kMaxSplits == 1 ? 4 : 2) norm_ro
   const int tid = threadIdx.x;
   if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 0);
   ptx::griddep_launch_dependents();
-  ptx::griddep_wait();  // partial sums come from the MM1 kernel
-  if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 14);
-  norm_token<T, kMaxSplits>(a, blockIdx.x, tid);
+  norm_token<T, kMaxSplits, true>(a, blockIdx.x, tid);  // waits for the MM1 kernel inside, after its own parameter loads
   if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 15);
 }
 
