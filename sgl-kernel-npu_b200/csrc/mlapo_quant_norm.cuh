@@ -101,12 +101,13 @@ __global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict_
   // No wait before the stores: this kernel runs under the tail of whatever precedes it.  When that is the previous call's q kernel,
   // a0's last reader (that call's MM1) is complete by the time this grid can start, because every q kernel signals its dependents
   // only AFTER its own griddepcontrol.wait (norm complete => MM1 complete, the chain being transitive); any other predecessor
-  // signals at its completion.  The wait at the END keeps the chain transitive: this grid is not complete, and so MM1 does not pass
-  // its wait and write the split-K slabs, before the predecessor is.
+  // signals at its completion.  A wait at the END keeps the chain transitive: this grid is not complete, and so MM1 does not pass
+  // its wait and write the split-K slabs, before the predecessor is.  ONE CTA waiting is enough for that (the last one, which is
+  // dispatched last); CTAs that all waited would sit on the few idle SMs and keep the rest of the grid from starting.
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 14);
   quant_vectors<T, U>(x, q, qs, n_vec8, blockIdx.x * (long long)blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 15);
-  ptx::griddep_wait();
+  if (blockIdx.x == gridDim.x - 1) ptx::griddep_wait();
 }
 
 // per-token symmetric (UNPINNED restatement of bf16.hpp:437-475): one row, executed by the whole CTA (any block size)

@@ -67,6 +67,12 @@ def main(workload="c2", pdl=False, persistent=False, legacy=False):
         for name, (a0, am, a1, w, wm, em) in spans.items():
             extra = f"  upstream-wait passed: median {(wm - t0) / 1e3:7.2f} last {(w - t0) / 1e3:7.2f}; median CTA end {(em - t0) / 1e3:7.2f}" if w else ""
             print(f"   {name:16s} {(a0 - t0) / 1e3:7.2f} {(am - t0) / 1e3:7.2f} {(a1 - t0) / 1e3:7.2f}{extra}")
+    if os.environ.get("MLAPO_TL_QUANT"):  # when do the quantise kernel's CTAs start, against the previous q kernel's CTA ends?
+        qs_ = tl[2][tl[2][:, 0] != 0][:, 0]
+        qe_ = tl[1][tl[1][:, 0] != 0][:, 15]
+        t0_ = qs_.min()
+        print("quant CTA starts (us), percentiles 0/10/25/50/75/90/100: " + " ".join(f"{(np.percentile(qs_, p) - t0_) / 1e3:.2f}" for p in (0, 10, 25, 50, 75, 90, 100)), "of", qs_.size)
+        print("q CTA ends of the SAME call (us, same origin), percentiles 0/50/100: " + " ".join(f"{(np.percentile(qe_, p) - t0_) / 1e3:.2f}" for p in (0, 50, 100)))
     QS = ["gtimer", "start"] + [f"u{i}:{w}" for i in range(4) for w in ("mm2_done", "acc2_released", "drained")]
     QP = ["gtimer", "start", "prologue", "upstream", "first_full"] + [f"u{i}:{w}" for i in range(3) for w in ("mm2_done", "acc_read", "drained")] + ["end"]
     stream = n > 256 and h * ((n + 255) // 256) > 148
@@ -112,3 +118,4 @@ def main(workload="c2", pdl=False, persistent=False, legacy=False):
 if __name__ == "__main__":
     main(sys.argv[1] if len(sys.argv) > 1 else "c2", pdl=len(sys.argv) > 2 and ("pdl" in sys.argv[2:] or "persistent" in sys.argv[2:]),
          persistent=len(sys.argv) > 2 and sys.argv[2] == "persistent", legacy="legacy" in sys.argv[2:])
+
