@@ -232,6 +232,13 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device (the product path has no CPU fallback)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    try:  # run on the CPUs next to this GPU, so that the pinned host buffers of the e2e leg are allocated on its NUMA node
+        import pynvml
+        pynvml.nvmlInit()
+        idx = torch.cuda._get_nvml_device_index(dev) if hasattr(torch.cuda, "_get_nvml_device_index") else local
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(idx))
+    except Exception:
+        pass
     ranks = Ranks("nccl", dev)
     sharding = "tp" if args.workload in TP_WORKLOADS else "replica"
 
