@@ -45,6 +45,21 @@ extern "C" {
 #define MLAPO_QUANT_PER_TENSOR_ASYMM 0
 #define MLAPO_QUANT_PER_TOKEN_SYMM 1
 
+/*
+ * MlapoParams.flags.
+ * MLAPO_FLAG_INPUT_COMPLETE: the caller states that everything the call reads (hidden_state above all) and everything it
+ * writes (outputs, caches, workspace) is free of pending work by the time the PREVIOUS kernel on `stream` lets its
+ * dependents start.  That holds when the previous kernel on the stream is one of this library's own mla_preprocess
+ * kernels, or any kernel that does not use programmatic dependent launch (griddepcontrol.launch_dependents /
+ * cudaTriggerProgrammaticLaunchCompletion) — torch's own kernels, cuBLAS, NCCL today.  It does NOT hold behind a
+ * producer that triggers its dependents early, before its last store (CUTLASS / TensorRT-LLM / flashinfer kernels with
+ * PDL enabled).  With the flag set the first kernel of the call (the quantiser) reads hidden_state and writes the
+ * workspace without waiting for the previous kernel to complete, so that it runs under that kernel's tail (about 2.5 us
+ * per call at 256 tokens x 128 heads when calls follow one another); without it (the default) every CTA of that kernel
+ * waits for the previous kernel's completion first, which is always safe.
+ */
+#define MLAPO_FLAG_INPUT_COMPLETE 1
+
 /* Fixed dimensions of the path (op_kernel/mla_preprocess.h:55-64). */
 #define MLAPO_MM1_OUT 2112           /* [k_nope 512 | k_pe 64 | q_a 1536] */
 #define MLAPO_KV_LORA 512
@@ -69,7 +84,7 @@ typedef struct MlapoParams {
   int32_t num_cache_blocks;     /* B of the cache tensors                                                 */
   int32_t cache_block_size;     /* bs; must be 128 in the NZ modes (mla_preprocess_mix_bf16.hpp:2549-2550)*/
   int32_t descale_is_int64;     /* 1: descale0/1 are int64 carrying fp32 bits in the low word (fp16 path) */
-  int32_t reserved0;
+  int32_t flags;                /* MLAPO_FLAG_* (0 = none)                                                */
 
   const void* hidden_state;     /* act  [N, D]                                                            */
   const void* wdqkv_km;         /* int8 [2112, D]   K-major, from mlapo_repack_nz_weight()                */
@@ -299,8 +314,11 @@ int mla_preprocess_launch_static(const MlapoParams* p, void* stream);
 int mlapo_launches_per_call(const MlapoParams* p);
 
 /*
- * Debug / profiling hooks (process-wide; no reference counterpart — the reference has DEBUG_MODE printf builds only,
- * CMakeLists.txt:48-53).  flags: bit0 = synchronise and check after every kernel (errors name the kernel),
+ * Debug / profiling hooks (no reference counterpart — the reference has DEBUG_MODE printf builds only,
+ * CMakeLists.txt:48-53).  TEST AND PROFILING ONLY: the flags are one process-wide word; set them from one thread while
+ * no call is being enqueued by another.  Bits 1 and 3 enlarge the workspace, so mlapo_get_workspace_size() and the launch
+ * must see the same flags (a launch takes one snapshot of the word and refuses a workspace that is too small for it).
+ * flags: bit0 = synchronise and check after every kernel (errors name the kernel),
  * bit1 = also write the dequantised MM1 rows y0 (act [N,2112]) after the last workspace region,
  * bit2 = record CUDA events around every kernel of the next launches, bit3 = per-CTA clock marks (timeline region),
  * bit6 = keep the one-CTA-per-unit q-path kernel where the streaming form would be used,

@@ -141,7 +141,8 @@ class MlaCase:
 
 
 def gen_case(N=1, H=16, D=7168, dtype=torch.bfloat16, cache_mode="krope_ctkv", seed=42,
-             num_blocks=1078, block_size=NZ_BLOCK, neg_slot_frac=0.0, full_range_weights=False) -> MlaCase:
+             num_blocks=1078, block_size=NZ_BLOCK, neg_slot_frac=0.0, full_range_weights=False,
+             slot_runs=False) -> MlaCase:
     """Synthetic inputs with the reference generator's distributions and draw order.
 
     Follows test_mla:140-321 draw by draw (same ``np.random.seed``, same sequence of
@@ -152,7 +153,9 @@ def gen_case(N=1, H=16, D=7168, dtype=torch.bfloat16, cache_mode="krope_ctkv", s
     ``wuq_nd``) and in the FRACTAL_NZ layout the op consumes (``wdqkv``, ``wuq``;
     test_mla:537-544).  Extensions beyond the reference (applied after all reference
     draws, so they do not disturb them): ``neg_slot_frac`` marks a fraction of tokens
-    with slot -1; ``full_range_weights`` redraws int8 weights over [-128, 127].
+    with slot -1; ``full_range_weights`` redraws int8 weights over [-128, 127];
+    ``slot_runs`` replaces the unique random slots by per-request contiguous runs at
+    random block offsets (a decode batch of requests of ragged length, SURVEY.md §8d "C5").
     """
     torch.manual_seed(seed)
     np.random.seed(seed)
@@ -196,6 +199,22 @@ def gen_case(N=1, H=16, D=7168, dtype=torch.bfloat16, cache_mode="krope_ctkv", s
     if full_range_weights:
         t["wdqkv_nd"] = as_t(rnd.randint(-128, 128, (MM1_OUT, D)).astype(np.int8), torch.int8)
         t["wuq_nd"] = as_t(rnd.randint(-128, 128, (H * Q_HEAD, Q_LORA)).astype(np.int8), torch.int8)
+    if slot_runs:
+        # requests of 1..32 tokens; each takes a run of consecutive slots that starts at a random offset of a block of
+        # its own (so runs never collide and may straddle a block boundary into the request's second block)
+        lens, left = [], N
+        while left > 0:
+            n_req = int(min(left, rnd.randint(1, 33)))
+            lens.append(n_req)
+            left -= n_req
+        if 2 * len(lens) > num_blocks:
+            raise ValueError(f"slot_runs: {len(lens)} requests need {2 * len(lens)} cache blocks, have {num_blocks}")
+        first_blocks = rnd.permutation(num_blocks // 2)[:len(lens)] * 2
+        pos = 0
+        for n_req, blk in zip(lens, first_blocks):
+            start = int(blk) * block_size + int(rnd.randint(0, block_size))
+            slots[pos:pos + n_req] = np.arange(start, start + n_req, dtype=np.int32)
+            pos += n_req
     if neg_slot_frac > 0 and N > 1:
         k = max(1, int(round(N * neg_slot_frac)))
         slots[rnd.choice(N, k, replace=False)] = -1

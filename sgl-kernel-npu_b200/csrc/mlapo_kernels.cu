@@ -27,7 +27,10 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <atomic>
+#include <map>
 #include <mutex>
+#include <tuple>
 #include <type_traits>
 
 #include "../../include/mla_preprocess_b200.h"
@@ -49,21 +52,40 @@ namespace mlapo {
 
 // ============================================================================================ host side
 thread_local char g_err[512] = "";
-static int g_debug_flags = 0;  // bit0: sync + check after each kernel; bit1: write the y0 tap; bit2: time each kernel
+// Debug flags (test / profiling only, see the header): one process-wide word; every entry point takes ONE snapshot of it into the
+// calling thread's copy, so a call sees a single consistent value from its workspace layout to its last launch.
+static std::atomic<int> g_debug_flags_word{0};
+thread_local int g_debug_flags = 0;  // bit0: sync + check after each kernel; bit1: write the y0 tap; bit2: time each kernel
+static inline void snapshot_debug_flags() { g_debug_flags = g_debug_flags_word.load(std::memory_order_relaxed); }
 static unsigned* g_wait_log_host = nullptr;  // host-mapped log of stuck barrier waits (debug flag bit11)
 constexpr int kMaxKernels = 8;
-static cudaEvent_t g_ev[kMaxKernels + 1];
-static bool g_ev_ready = false;
-static int g_ev_count = 0;  // events recorded by the last launch
-static const char* g_kernel_names[kMaxKernels] = {"quant_hidden", "mm1_splitk", "norm_rope_cache", "q_fused", "", "", "", ""};
+constexpr int kMaxDevices = 64;
+// Per-kernel timing events (debug bit2) belong to the device they were created on; the names and the count of the last launch
+// belong to the thread that made it.
+static cudaEvent_t g_ev[kMaxDevices][kMaxKernels + 1];
+static std::atomic<bool> g_ev_ready[kMaxDevices];
+static std::mutex g_ev_mutex;
+thread_local int g_ev_count = 0;  // events recorded by the last launch of this thread
+thread_local int g_ev_dev = 0;    // ... on this device
+thread_local const char* g_kernel_names[kMaxKernels] = {"quant_hidden", "mm1_splitk", "norm_rope_cache", "q_fused", "", "", "", ""};
+static int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return (dev >= 0 && dev < kMaxDevices) ? dev : 0;
+}
 static void record_event(int i, cudaStream_t st) {
   if (!(g_debug_flags & 4)) return;
-  if (!g_ev_ready) {
-    for (int k = 0; k <= kMaxKernels; ++k) cudaEventCreate(&g_ev[k]);
-    g_ev_ready = true;
+  const int dev = current_device();
+  if (!g_ev_ready[dev].load(std::memory_order_acquire)) {
+    std::lock_guard<std::mutex> lock(g_ev_mutex);
+    if (!g_ev_ready[dev].load(std::memory_order_relaxed)) {
+      for (int k = 0; k <= kMaxKernels; ++k) cudaEventCreate(&g_ev[dev][k]);
+      g_ev_ready[dev].store(true, std::memory_order_release);
+    }
   }
-  cudaEventRecord(g_ev[i], st);
+  cudaEventRecord(g_ev[dev][i], st);
   g_ev_count = i + 1;
+  g_ev_dev = dev;
 }
 
 static int fail(int code, const char* fmt, ...) {
@@ -112,15 +134,17 @@ static int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int elem_bytes, con
 
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// SM count of the CURRENT device (cached per device ordinal; the write is idempotent, so a benign race at first use is harmless)
 static int num_sms() {
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (sms <= 0) sms = 148;
+  static std::atomic<int> sms[kMaxDevices];
+  const int dev = current_device();
+  int v = sms[dev].load(std::memory_order_relaxed);
+  if (!v) {
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    if (v <= 0) v = 148;
+    sms[dev].store(v, std::memory_order_relaxed);
   }
-  return sms;
+  return v;
 }
 
 // Launch with the programmatic-dependent-launch attribute: the kernel may start while its predecessor drains;
@@ -144,7 +168,7 @@ static int choose_splits0(int n_tokens, int hidden_dim) {
   const int m_super = n_tokens > 0 ? (n_tokens + 2 * kBlockM - 1) / (2 * kBlockM) : 1;  // CTAs cover up to 256 tokens
   const int n_tiles = (MLAPO_MM1_OUT + kMm1BlockN - 1) / kMm1BlockN;                     // 17
   const int kb_total = hidden_dim / kBlockKBytes;
-  int s = 148 / (n_tiles * m_super);  // one wave of CTAs
+  int s = num_sms() / (n_tiles * m_super);  // one wave of CTAs
   if (s < 1) s = 1;
   if (s > 8) s = 8;
   if (s > kb_total) s = kb_total;
@@ -191,12 +215,15 @@ static int compute_layout(const MlapoParams* p, MlapoWorkspaceLayout* l) {
     if (e__ != cudaSuccess) return fail(MLAPO_ERR_CUDA, "%s: %s", name, cudaGetErrorString(e__));   \
   } while (0)
 
+// Shared-memory opt-in of one kernel instantiation, once per device.  `done` is a per-call-site latch indexed by device ordinal;
+// two threads racing on the first call both set the (idempotent) attribute and both store `true`.
+using DoneFlag = std::atomic<bool>;
 template <class K>
-static int set_smem_attr(K kern, int bytes, bool* done, const char* name) {
-  if (*done) return MLAPO_OK;
+static int set_smem_attr(K kern, int bytes, DoneFlag* done, const char* name) {
+  if (done->load(std::memory_order_acquire)) return MLAPO_OK;
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess)
     return fail(MLAPO_ERR_CUDA, "cudaFuncSetAttribute(%s, %d): %s", name, bytes, cudaGetErrorString(cudaGetLastError()));
-  *done = true;
+  done->store(true, std::memory_order_release);
   return MLAPO_OK;
 }
 
@@ -223,6 +250,7 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   const bool per_token = p->quant_mode == MLAPO_QUANT_PER_TOKEN_SYMM;
   const bool int8_out = p->cache_mode == MLAPO_CACHE_INT8_NZ;
   const bool pdl = (g_debug_flags & 5) == 0;  // per-kernel sync/timing wants serialised kernels
+  const int input_complete = (p->flags & MLAPO_FLAG_INPUT_COMPLETE) ? 1 : 0;
   long long* tl1 = (g_debug_flags & 8) ? reinterpret_cast<long long*>(ws + l.timeline) : nullptr;
   long long* tl4 = tl1 ? tl1 + 4096 * 16 : nullptr;
   long long* tl0 = tl1 ? tl1 + 2 * 4096 * 16 : nullptr;
@@ -234,9 +262,7 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   const CUtensorMapDataType act_dt = std::is_same<T, __nv_bfloat16>::value ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   int rc;
   cudaError_t e__ = cudaSuccess;
-  int dev = 0;
-  cudaGetDevice(&dev);
-  dev &= 63;
+  const int dev = current_device();
   const bool persistent = decode_persistent_eligible(p, l.splits0);
 
   // ---- tensor maps and argument blocks shared by both launch shapes
@@ -278,6 +304,7 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   na.cache_mode = p->cache_mode;
   na.cache_slots = (long long)p->num_cache_blocks * p->cache_block_size;
   na.tl = tl3;
+  na.input_complete = input_complete;
 
   QArgs qa{};
   qa.descale1 = p->descale1; qa.descale_is_i64 = p->descale_is_int64;
@@ -309,7 +336,7 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     record_event(0, st);
 #define MLAPO_LAUNCH_DECODE(I8, MT)                                                                                        \
   do {                                                                                                                     \
-    static bool done[64] = {};                                                                                             \
+    static DoneFlag done[kMaxDevices];                                                                                             \
     if ((rc = set_smem_attr(mla_decode_persistent_kernel<T, I8, MT>, kDecodeSmemBytes, &done[dev], "decode_persistent"))) return rc; \
     e__ = cudaLaunchKernelEx(&cfg, mla_decode_persistent_kernel<T, I8, MT>, tm_a0, tm_wdqkv, tm_part, tm_a1, tm_wuq, tm_wuk, tm_o0,  \
                              tm_o1, da);                                                                                   \
@@ -346,15 +373,15 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     if (nvec <= wave) {  // one 16-byte vector per thread
       e__ = launch_k(quant_hidden_kernel<T, 1>, dim3((unsigned)((nvec + 255) / 256)), dim3(256), 0, st, pdl,
                      reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
-                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0);
+                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0, input_complete);
     } else if (nvec <= 2 * wave) {  // two vectors per thread, both loads in flight
       e__ = launch_k(quant_hidden_kernel<T, 2>, dim3((unsigned)((nvec + 511) / 512)), dim3(256), 0, st, pdl,
                      reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
-                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0);
+                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0, input_complete);
     } else {                 // prefill sizes: grid-stride, 4 independent loads in flight per thread
       e__ = launch_k(quant_hidden_kernel<T, 4>, dim3(num_sms() * 8), dim3(256), 0, st, pdl,
                      reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
-                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0);
+                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0, input_complete);
     }
   }
   MLAPO_CHECK_LAUNCH("quant_hidden");
@@ -364,17 +391,17 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   {
     const int n_tiles = (MLAPO_MM1_OUT + bn - 1) / bn;
     if (wide) {
-      static bool done[64] = {};
+      static DoneFlag done[kMaxDevices];
       if ((rc = set_smem_attr(mm1_splitk_kernel<2, kMm1BlockNWide>, mm1_smem_bytes<2, kMm1BlockNWide>(), &done[dev], "mm1<2,256>"))) return rc;
       e__ = launch_k(mm1_splitk_kernel<2, kMm1BlockNWide>, dim3(n_tiles, 1, (n + 255) / 256), dim3(kGemmThreads),
                      mm1_smem_bytes<2, kMm1BlockNWide>(), st, pdl, tm_a0, tm_wdqkv, tm_part, n, d / kBlockKBytes, tl1);
     } else if (n > kBlockM) {
-      static bool done[64] = {};
+      static DoneFlag done[kMaxDevices];
       if ((rc = set_smem_attr(mm1_splitk_kernel<2, kMm1BlockN>, mm1_smem_bytes<2, kMm1BlockN>(), &done[dev], "mm1<2,128>"))) return rc;
       e__ = launch_k(mm1_splitk_kernel<2, kMm1BlockN>, dim3(n_tiles, l.splits0, (n + 255) / 256), dim3(kGemmThreads),
                      mm1_smem_bytes<2, kMm1BlockN>(), st, pdl, tm_a0, tm_wdqkv, tm_part, n, d / kBlockKBytes, tl1);
     } else {
-      static bool done[64] = {};
+      static DoneFlag done[kMaxDevices];
       if ((rc = set_smem_attr(mm1_splitk_kernel<1, kMm1BlockN>, mm1_smem_bytes<1, kMm1BlockN>(), &done[dev], "mm1<1,128>"))) return rc;
       e__ = launch_k(mm1_splitk_kernel<1, kMm1BlockN>, dim3(n_tiles, l.splits0, 1), dim3(kGemmThreads), mm1_smem_bytes<1, kMm1BlockN>(),
                      st, pdl, tm_a0, tm_wdqkv, tm_part, n, d / kBlockKBytes, tl1);
@@ -405,11 +432,11 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     const int max_pairs = num_sms() / 2;
     dim3 grid(2 * (q_units < max_pairs ? q_units : max_pairs));
     if (int8_out) {
-      static bool done[64] = {};
+      static DoneFlag done[kMaxDevices];
       if ((rc = set_smem_attr(q_pair_kernel<T, true>, kPSmemBytes, &done[dev], "q_pair<int8>"))) return rc;
       e__ = launch_k(q_pair_kernel<T, true>, grid, dim3(kPThreads), kPSmemBytes, st, pdl, tm_a1p, tm_wuqp, tm_wuk, tm_o0, qa, p->q_out1, q_units, tl4);
     } else {
-      static bool done[64] = {};
+      static DoneFlag done[kMaxDevices];
       if ((rc = set_smem_attr(q_pair_kernel<T, false>, kPSmemBytes, &done[dev], "q_pair"))) return rc;
       e__ = launch_k(q_pair_kernel<T, false>, grid, dim3(kPThreads), kPSmemBytes, st, pdl, tm_a1p, tm_wuqp, tm_wuk, tm_o0, qa, p->q_out1, q_units, tl4);
     }
@@ -421,11 +448,11 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     if ((rcx = make_tmap(&tm_a1s, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a1, n, MLAPO_Q_LORA, MLAPO_Q_LORA, 2 * kBlockM, 128))) return rcx;
     dim3 grid(num_sms() < q_units ? num_sms() : q_units);
     if (int8_out) {
-      static bool done[64] = {};
+      static DoneFlag done[kMaxDevices];
       if ((rc = set_smem_attr(q_stream_kernel<T, true>, kSSmemBytes, &done[dev], "q_stream<int8>"))) return rc;
       e__ = launch_k(q_stream_kernel<T, true>, grid, dim3(kSThreads), kSSmemBytes, st, pdl, tm_a1s, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, q_units, tl4);
     } else {
-      static bool done[64] = {};
+      static DoneFlag done[kMaxDevices];
       if ((rc = set_smem_attr(q_stream_kernel<T, false>, kSSmemBytes, &done[dev], "q_stream"))) return rc;
       e__ = launch_k(q_stream_kernel<T, false>, grid, dim3(kSThreads), kSSmemBytes, st, pdl, tm_a1s, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, q_units, tl4);
     }
@@ -435,11 +462,11 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     g_kernel_names[3] = "q_fused";
     dim3 grid(h, q_tok_tiles);
     if (int8_out) {
-      static bool done[64] = {};
+      static DoneFlag done[kMaxDevices];
       if ((rc = set_smem_attr(q_fused_kernel<T, true>, kQSmemBytes, &done[dev], "q_fused<int8>"))) return rc;
       e__ = launch_k(q_fused_kernel<T, true>, grid, dim3(kQThreads), kQSmemBytes, st, pdl, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, tl4);
     } else {
-      static bool done[64] = {};
+      static DoneFlag done[kMaxDevices];
       if ((rc = set_smem_attr(q_fused_kernel<T, false>, kQSmemBytes, &done[dev], "q_fused"))) return rc;
       e__ = launch_k(q_fused_kernel<T, false>, grid, dim3(kQThreads), kQSmemBytes, st, pdl, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, tl4);
     }
@@ -453,14 +480,13 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
 template <class T, int HD, bool NEOX>
 static cudaError_t split_vec_launch(const SplitQkvArgs& a, cudaStream_t st) {
   using G = SplitGeom<HD>;
-  static bool opted[64] = {};
-  int dev = 0;
-  cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess) return e;
-  if (dev < 0 || dev >= 64 || !opted[dev]) {
+  static DoneFlag opted[kMaxDevices];
+  const int dev = current_device();
+  cudaError_t e = cudaSuccess;
+  if (!opted[dev].load(std::memory_order_acquire)) {
     e = cudaFuncSetAttribute(split_qkv_vec_kernel<T, HD, NEOX>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM_BYTES);
     if (e != cudaSuccess) return e;
-    if (dev >= 0 && dev < 64) opted[dev] = true;
+    opted[dev].store(true, std::memory_order_release);
   }
   // CTAs per chunk index of the row, in proportion to the chunk's cost (its length plus a fixed part per token), 3 CTAs per SM
   const long long row = (a.gated ? 2LL : 1LL) * a.q_hidden + 2LL * a.kv_hidden;
@@ -487,28 +513,27 @@ static int bmt_launch_impl(const void* a, const void* b, void* c, int64_t m, int
   const bool tc = !b_is_nz && k % 64 == 0 && n % 64 == 0 && m < (1ll << 31) && batch <= 65535 &&
                   ((uintptr_t)a % 16 == 0) && ((uintptr_t)b % 16 == 0) && ((uintptr_t)c % 16 == 0);
   if (tc) {
-    int rc, dev = 0;
-    cudaGetDevice(&dev);
-    dev &= 63;
+    int rc;
+    const int dev = current_device();
     CUtensorMap tm_a, tm_b, tm_c;  // coordinates (inner, rows, batch); the op's "transposes" are just these stride orders
     if ((rc = make_tmap(&tm_a, dt, 2, a, (uint64_t)m, (uint64_t)k, (uint64_t)batch * k * 2, kBlockM, 64, (uint64_t)batch, (uint64_t)k * 2))) return rc;
     if ((rc = make_tmap(&tm_b, dt, 2, b, (uint64_t)k, (uint64_t)n, (uint64_t)n * 2, 64, 64, (uint64_t)batch, (uint64_t)k * n * 2))) return rc;
     if ((rc = make_tmap(&tm_c, dt, 2, c, (uint64_t)m, (uint64_t)n, (uint64_t)batch * n * 2, kBlockM, 64, (uint64_t)batch, (uint64_t)n * 2))) return rc;
     const unsigned m_tiles = (unsigned)((m + 2 * kBlockM - 1) / (2 * kBlockM));
     if (n % 128 == 0) {
-      static bool done[64] = {};
+      static DoneFlag done[kMaxDevices];
       if ((rc = set_smem_attr(bmt_tc_kernel<T, 128>, bmt_smem_bytes<128>(), &done[dev], "bmt<128>"))) return rc;
       e = launch_k(bmt_tc_kernel<T, 128>, dim3((unsigned)(n / 128), m_tiles, (unsigned)batch), dim3(kBmtThreads), bmt_smem_bytes<128>(), st, false,
                    tm_a, tm_b, tm_c, (int)m, (int)k);
     } else {
-      static bool done[64] = {};
+      static DoneFlag done[kMaxDevices];
       if ((rc = set_smem_attr(bmt_tc_kernel<T, 64>, bmt_smem_bytes<64>(), &done[dev], "bmt<64>"))) return rc;
       e = launch_k(bmt_tc_kernel<T, 64>, dim3((unsigned)(n / 64), m_tiles, (unsigned)batch), dim3(kBmtThreads), bmt_smem_bytes<64>(), st, false,
                    tm_a, tm_b, tm_c, (int)m, (int)k);
     }
   } else {
     long long blocks = (m * batch * n + 255) / 256;
-    if (blocks > 148 * 64) blocks = 148 * 64;
+    if (blocks > (long long)num_sms() * 64) blocks = (long long)num_sms() * 64;
     bmt_generic_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(reinterpret_cast<const T*>(a), reinterpret_cast<const T*>(b), reinterpret_cast<T*>(c),
                                                            m, batch, k, n, b_is_nz);
     e = cudaGetLastError();
@@ -533,7 +558,7 @@ const char* mlapo_version(void) { return "mla_preprocess_b200 0.1.0 (sm_100a; tc
 const char* mlapo_last_error(void) { return g_err; }
 
 int mlapo_set_debug_flags(int flags) {
-  const int old = g_debug_flags;
+  const int old = g_debug_flags_word.exchange(flags);
   g_debug_flags = flags;
   if ((flags & 2048) && !g_wait_log_host) {  // bit11: register a host-mapped log for stuck barrier waits
     unsigned* dptr = nullptr;
@@ -554,16 +579,18 @@ int mlapo_debug_read_wait_log(unsigned* out, int cap_words) {
 }
 // Debug/profiling hook (flag bit2): per-kernel durations of the last mla_preprocess_launch on this thread's device.
 int mlapo_get_kernel_times_ms(float* out_ms, int cap) {
-  if (!g_ev_ready || g_ev_count < 2) return 0;
-  if (cudaEventSynchronize(g_ev[g_ev_count - 1]) != cudaSuccess) return fail(MLAPO_ERR_CUDA, "event sync failed");
+  const int dev = g_ev_dev;
+  if (!g_ev_ready[dev].load(std::memory_order_acquire) || g_ev_count < 2) return 0;
+  if (cudaEventSynchronize(g_ev[dev][g_ev_count - 1]) != cudaSuccess) return fail(MLAPO_ERR_CUDA, "event sync failed");
   int n = g_ev_count - 1;
   if (n > cap) n = cap;
-  for (int i = 0; i < n; ++i) cudaEventElapsedTime(&out_ms[i], g_ev[i], g_ev[i + 1]);
+  for (int i = 0; i < n; ++i) cudaEventElapsedTime(&out_ms[i], g_ev[dev][i], g_ev[dev][i + 1]);
   return n;
 }
 const char* mlapo_kernel_name(int i) { return (i >= 0 && i < kMaxKernels) ? g_kernel_names[i] : ""; }
 
 int mlapo_get_workspace_layout(const MlapoParams* p, MlapoWorkspaceLayout* layout) {
+  snapshot_debug_flags();
   int rc = check_params(p);
   if (rc) return rc;
   if (!layout) return fail(MLAPO_ERR_INVALID_ARG, "layout is null");
@@ -580,6 +607,7 @@ int mlapo_get_workspace_size(const MlapoParams* p, size_t* bytes) {
 }
 
 int mlapo_launches_per_call(const MlapoParams* p) {
+  snapshot_debug_flags();
   if (check_params(p)) return 0;
   return decode_persistent_eligible(p, choose_splits0(p->num_tokens, p->hidden_dim)) ? 1 : 4;
 }
@@ -814,16 +842,34 @@ static int split_qkv_tp_impl(const void* qkv, const void* cos, const void* sin, 
   const int smem = tp_smem_bytes(row, rotary_dim, q_hidden, kv_hidden, stages);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool bf = act_dtype == MLAPO_ACT_BF16;
-  cudaError_t e = bf ? cudaFuncSetAttribute(split_qkv_tp_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
-                     : cudaFuncSetAttribute(split_qkv_tp_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   // The grid is what the device holds at once (asked of the runtime, not assumed): the peer-exchange mode needs every CTA resident,
-  // since a CTA waits for records that the same CTA index publishes on the other ranks.
-  int per_sm = 0, dev = 0, sms = 0;
-  if (e == cudaSuccess)
-    e = bf ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, split_qkv_tp_kernel<__nv_bfloat16>, kTpThreads, smem)
-           : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, split_qkv_tp_kernel<__half>, kTpThreads, smem);
-  if (e == cudaSuccess) e = cudaGetDevice(&dev);
-  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  // since a CTA waits for records that the same CTA index publishes on the other ranks.  The shared-memory opt-in and the occupancy
+  // answer are cached per (dtype, shared-memory size, device): this is a decode-path operator and both are host round trips.
+  static std::mutex tp_mutex;
+  static std::map<std::tuple<int, int, int>, int> tp_per_sm;
+  cudaError_t e = cudaSuccess;
+  int per_sm = 0;
+  const int sms = num_sms();
+  {
+    std::lock_guard<std::mutex> lock(tp_mutex);
+    const auto key = std::make_tuple(bf ? 1 : 0, smem, current_device());
+    auto it = tp_per_sm.find(key);
+    if (it != tp_per_sm.end()) {
+      per_sm = it->second;
+    } else {
+      // the attribute is a high-water mark per function and device: never lower it below an earlier, larger request
+      int prev = 0;
+      for (const auto& kv : tp_per_sm)
+        if (std::get<0>(kv.first) == (bf ? 1 : 0) && std::get<2>(kv.first) == current_device() && std::get<1>(kv.first) > prev) prev = std::get<1>(kv.first);
+      if (smem > prev)
+        e = bf ? cudaFuncSetAttribute(split_qkv_tp_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+               : cudaFuncSetAttribute(split_qkv_tp_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      if (e == cudaSuccess)
+        e = bf ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, split_qkv_tp_kernel<__nv_bfloat16>, kTpThreads, smem)
+               : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, split_qkv_tp_kernel<__half>, kTpThreads, smem);
+      if (e == cudaSuccess) tp_per_sm.emplace(key, per_sm);
+    }
+  }
   if (e == cudaSuccess && (per_sm < 1 || sms < 1)) return fail(MLAPO_ERR_CUDA, "split_qkv_tp_rmsnorm_rope: the kernel does not fit an SM (%d bytes of shared memory)", smem);
   if (e == cudaSuccess) {
     const unsigned resident = (unsigned)per_sm * (unsigned)sms;
@@ -897,12 +943,13 @@ int mlapo_gather_nz_cache_rows(const void* cache, const int32_t* slots, void* ro
 }
 
 int mlapo_repack_nz_weight(const void* w_nz, void* w_km, int32_t k, int32_t n_out, void* stream) {
+  snapshot_debug_flags();
   if (!w_nz || !w_km) return fail(MLAPO_ERR_INVALID_ARG, "repack: null pointer");
   if (k <= 0 || k % 32 != 0 || n_out <= 0) return fail(MLAPO_ERR_INVALID_ARG, "repack: k must be a multiple of 32");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const long long chunks = (long long)n_out * (k / 32) * 2;
   int blocks = (int)((chunks + 255) / 256);
-  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks > num_sms() * 16) blocks = num_sms() * 16;
   repack_nz_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<const int8_t*>(w_nz), reinterpret_cast<int8_t*>(w_km), k, n_out);
   cudaError_t e__ = cudaSuccess;
   MLAPO_CHECK_LAUNCH("repack_nz");
@@ -914,6 +961,7 @@ int mlapo_repack_nz_weight(const void* w_nz, void* w_km, int32_t k, int32_t n_ou
 // earlier in the same call for exactly the rows and columns that are read, so stale contents from the previous call are
 // never observed and nothing is cleared here.  Calls that overlap on the GPU share the array and would race.
 int mla_preprocess_launch_static(const MlapoParams* p, void* stream) {
+  snapshot_debug_flags();
   int rc = check_params(p);
   if (rc) return rc;
   if (p->num_tokens == 0) return MLAPO_OK;
@@ -945,6 +993,7 @@ int mla_preprocess_launch_static(const MlapoParams* p, void* stream) {
 }
 
 int mla_preprocess_launch(const MlapoParams* p, void* workspace, size_t workspace_bytes, void* stream) {
+  snapshot_debug_flags();
   int rc = check_params(p);
   if (rc) return rc;
   if (p->num_tokens == 0) return MLAPO_OK;

@@ -92,22 +92,30 @@ __device__ __forceinline__ void prefetch_weights_l2(const WeightPrefetch& wp) {
 
 template <class T, int U>
 __global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict__ q, const T* __restrict__ scale,
-                                    const int8_t* __restrict__ offset, long long n_vec8, WeightPrefetch wp, long long* tl) {
+                                    const int8_t* __restrict__ offset, long long n_vec8, WeightPrefetch wp, long long* tl,
+                                    int input_complete) {
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 0);
   ptx::griddep_launch_dependents();
   prefetch_weights_l2(wp);
+  // Default: every CTA waits for the previous kernel on the stream to COMPLETE before it reads hiddenState or writes a0.  That
+  // is what makes the call safe behind any producer, including one that lets its dependents start before its last store
+  // (programmatic dependent launch).
+  //
+  // MLAPO_FLAG_INPUT_COMPLETE (the caller's statement that nothing this call touches is still pending when the previous kernel
+  // releases its dependents; see the header): no wait before the stores, this kernel runs under the tail of whatever precedes it.
+  // When that is the previous call's q kernel, a0's last reader (that call's MM1) is complete by the time this grid can start,
+  // because every q kernel signals its dependents only AFTER its own griddepcontrol.wait (norm complete => MM1 complete, the
+  // chain being transitive); a kernel that does not use programmatic launch signals at its completion.  A wait at the END keeps
+  // the chain transitive: this grid is not complete, and so MM1 does not pass its wait and write the split-K slabs, before the
+  // predecessor is.  ONE CTA waiting is enough for that (the last one, which is dispatched last); CTAs that all waited would sit
+  // on the few idle SMs and keep the rest of the grid from starting.
+  if (!input_complete) ptx::griddep_wait();
   QuantScale qs;
   qs.load(scale, offset);
-  // No wait before the stores: this kernel runs under the tail of whatever precedes it.  When that is the previous call's q kernel,
-  // a0's last reader (that call's MM1) is complete by the time this grid can start, because every q kernel signals its dependents
-  // only AFTER its own griddepcontrol.wait (norm complete => MM1 complete, the chain being transitive); any other predecessor
-  // signals at its completion.  A wait at the END keeps the chain transitive: this grid is not complete, and so MM1 does not pass
-  // its wait and write the split-K slabs, before the predecessor is.  ONE CTA waiting is enough for that (the last one, which is
-  // dispatched last); CTAs that all waited would sit on the few idle SMs and keep the rest of the grid from starting.
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 14);
   quant_vectors<T, U>(x, q, qs, n_vec8, blockIdx.x * (long long)blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 15);
-  if (blockIdx.x == gridDim.x - 1) ptx::griddep_wait();
+  if (input_complete && blockIdx.x == gridDim.x - 1) ptx::griddep_wait();
 }
 
 // per-token symmetric (UNPINNED restatement of bf16.hpp:437-475): one row, executed by the whole CTA (any block size)
@@ -173,6 +181,7 @@ struct NormArgs {
   int cache_mode;
   long long cache_slots;    // num_blocks * block_size
   long long* tl;            // debug timeline or null
+  int input_complete;       // MLAPO_FLAG_INPUT_COMPLETE: the per-call inputs (cos, sin, slots) may be read before the upstream wait
 };
 
 constexpr int kNormThreads = 288;  // warps 0-1: k_nope (512), warp 2 lanes 0-7: k_pe (64), warps 3-8: q_a (1536)
@@ -184,8 +193,10 @@ __device__ __forceinline__ double warp_sum_f64(double v) {
 }
 
 // One token row, executed by every thread of the CTA (threads beyond the first 288 only take part in the barriers).
-// kPdlWait: the kernel form; everything that does not come from the MM1 kernel (descale, bias, gamma / beta, cos / sin, the slot)
-// is loaded BEFORE griddepcontrol.wait, i.e. while MM1 is still running, so that only the partial sums are waited for.
+// kPdlWait: the kernel form; the weight-like parameters (descale, bias, gamma / beta), which are complete long before the call, are
+// loaded BEFORE griddepcontrol.wait, i.e. while MM1 is still running, so that only the partial sums are waited for.  The per-call
+// inputs (cos / sin, the slot) join them only under MLAPO_FLAG_INPUT_COMPLETE: this kernel can start as early as the call's first
+// kernel (each kernel releases its dependents at once), so without the caller's word they might still be in the making.
 template <class T, int kMaxSplits, bool kPdlWait = false>
 __device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const int tid) {
   __shared__ double s_sum[9];
@@ -203,7 +214,8 @@ __device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const
   // All global loads are issued before anything is consumed (the kernel is latency-, not bandwidth-bound).
   float x[8];
   uint4 g_vec = make_uint4(0, 0, 0, 0), b_vec = make_uint4(0, 0, 0, 0);  // gamma (+beta) or cos/sin of this thread's 8 columns
-  const int slot = a.slots[t];
+  const bool early_inputs = !kPdlWait || a.input_complete;
+  int slot = early_inputs ? a.slots[t] : 0;
   {
     float d[8];
     int bias[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -221,7 +233,7 @@ __device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const
     }
     if (is_nope) {
       g_vec = reinterpret_cast<const uint4*>(a.gamma2)[tid];
-    } else if (is_pe) {
+    } else if (is_pe && early_inputs) {
       g_vec = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.cos) + (long long)t * 64)[lane & 7];
       b_vec = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.sin) + (long long)t * 64)[lane & 7];
     } else if (is_q) {
@@ -231,6 +243,13 @@ __device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const
     if constexpr (kPdlWait) {
       ptx::griddep_wait();  // partial sums (and the per-token scales of a0) come from the kernels before
       if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 14);
+      if (!early_inputs) {
+        slot = a.slots[t];
+        if (is_pe) {
+          g_vec = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.cos) + (long long)t * 64)[lane & 7];
+          b_vec = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.sin) + (long long)t * 64)[lane & 7];
+        }
+      }
     }
     int4 pu[kMaxSplits], pv[kMaxSplits];
 #pragma unroll

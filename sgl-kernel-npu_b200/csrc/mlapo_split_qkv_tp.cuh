@@ -59,19 +59,25 @@ __host__ __device__ inline int tp_smem_bytes(int row, int rd, int qh, int kvh, i
   return stages * tp_stage_bytes(row, rd) + 2 * (qh + kvh) + 16;
 }
 
+// A record is ONE 64-bit word {value (low), epoch (high)} written and read with single 8-byte accesses at system scope: an
+// aligned 64-bit access is single-copy atomic, so a reader sees the value and the epoch of the same store (a two-word vector
+// access would be two scalar accesses that may tear).
 __device__ __forceinline__ void st_record(unsigned long long addr, float v, unsigned epoch) {
-  asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(addr), "r"(__float_as_uint(v)), "r"(epoch) : "memory");
+  const unsigned long long rec = (unsigned long long)__float_as_uint(v) | ((unsigned long long)epoch << 32);
+  asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(addr), "l"(rec) : "memory");
 }
-// waits (bounded: a peer that never publishes becomes a trap, not a hung GPU) for a record of this call's epoch
+// Waits for a record of this call's epoch.  The wait is bounded so that a peer that never publishes (a rank that failed before its
+// launch) ends as a launch failure instead of a GPU that never answers again; the bound is generous (about half a minute of polling)
+// because ranks legitimately run a call or more apart: a host stall, a first graph instantiation, another kernel queued ahead.
 __device__ __forceinline__ float ld_record(unsigned long long addr, unsigned epoch) {
-  unsigned v, e;
+  unsigned long long rec;
   for (unsigned n = 0;; ++n) {
-    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(addr) : "memory");
-    if (e == epoch) break;
-    if (n > 64) __nanosleep(200);
-    if (n > (1u << 23)) __trap();
+    asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(rec) : "l"(addr) : "memory");
+    if ((unsigned)(rec >> 32) == epoch) break;
+    if (n > 64) __nanosleep(n > 4096 ? 1000 : 200);
+    if (n > (1u << 25)) __trap();
   }
-  return __uint_as_float(v);
+  return __uint_as_float((unsigned)rec);
 }
 
 // Roles run on different tokens at the same time, coupled only by per-stage mbarriers (no CTA-wide barrier in the loop):

@@ -12,7 +12,10 @@
 #include <c10/cuda/CUDAGuard.h>
 #include <torch/library.h>
 
+#include <cuda_runtime.h>
+
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 #include <string>
 #include <unordered_map>
@@ -40,8 +43,13 @@ void check_cabi(int rc, const char* what) { TORCH_CHECK(rc == MLAPO_OK, what, " 
 
 // The op signature has no "prepare" hook, so FRACTAL_NZ weights are repacked on first sight and cached.  The key is the
 // source tensor's StorageImpl (kept addressable by a weak reference, so a recycled device address or a recycled
-// StorageImpl cannot alias a dead entry), its offset, shape and version counter (in-place updates invalidate).
-// Weights are static in serving, so this runs once per layer at warm-up; entries die with their source tensor.
+// StorageImpl cannot alias a dead entry), its offset, shape and version counter (in-place updates invalidate; tensors
+// created under torch.inference_mode() carry no counter and count as version 0, so an in-place update of such a weight
+// needs a new tensor).  Weights are static in serving, so this runs once per layer at warm-up; entries die with their
+// source tensor.  The repack is enqueued on the stream of the first call; an event recorded behind it orders every other
+// stream that later receives the cached tensor.  Nothing is added to the cache while a stream is being captured (the
+// repacked tensor would live in the graph's private pool and the repack would be replayed with the graph): warm up with
+// one eager call, or repack explicitly with mla_preprocess_repack_weight and pass the K-major tensor.
 struct RepackKey {
   const void* storage;
   int64_t offset, k, n;
@@ -58,6 +66,8 @@ struct RepackKeyHash {
 struct RepackEntry {
   c10::weak_intrusive_ptr<c10::StorageImpl> source;
   at::Tensor km;
+  cudaStream_t made_on;
+  cudaEvent_t ready;  // recorded on made_on behind the repack kernel (never destroyed: a handful per process)
 };
 std::mutex g_repack_mutex;
 std::unordered_map<RepackKey, RepackEntry, RepackKeyHash> g_repack_cache;
@@ -81,17 +91,30 @@ at::Tensor kmajor_weight(const at::Tensor& w, int64_t n_out, int64_t k, const ch
   }
   TORCH_CHECK(w.dim() == 4 && w.size(0) == 1 && w.size(1) * 32 == k && w.size(2) == n_out && w.size(3) == 32, name,
               " must be FRACTAL_NZ [1, ", k / 32, ", ", n_out, ", 32], got ", w.sizes());
-  RepackKey key{w.storage().unsafeGetStorageImpl(), w.storage_offset(), k, n_out, (uint32_t)w._version()};
+  const uint32_t version = w.is_inference() ? 0u : (uint32_t)w._version();
+  RepackKey key{w.storage().unsafeGetStorageImpl(), w.storage_offset(), k, n_out, version};
   std::lock_guard<std::mutex> lock(g_repack_mutex);
   auto it = g_repack_cache.find(key);
   if (it != g_repack_cache.end()) {
-    if (!it->second.source.expired()) return it->second.km;
+    if (!it->second.source.expired()) {
+      if (it->second.made_on != stream)
+        TORCH_CHECK(cudaStreamWaitEvent(stream, it->second.ready, 0) == cudaSuccess, "mla_preprocess: cannot order the stream behind the weight repack");
+      return it->second.km;
+    }
     g_repack_cache.erase(it);
   }
+  cudaStreamCaptureStatus capturing = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(stream, &capturing);
+  TORCH_CHECK(capturing == cudaStreamCaptureStatusNone, "mla_preprocess: ", name,
+              " is a FRACTAL_NZ weight seen for the first time inside a CUDA graph capture; run one eager warm-up call first, or "
+              "repack it with torch.ops.npu.mla_preprocess_repack_weight and pass the K-major tensor");
   for (auto e = g_repack_cache.begin(); e != g_repack_cache.end();)  // drop entries whose source weight is gone
     e = e->second.source.expired() ? g_repack_cache.erase(e) : std::next(e);
   at::Tensor km = repack_nz(w, stream);
-  g_repack_cache.emplace(key, RepackEntry{w.storage().getWeakStorageImpl(), km});
+  cudaEvent_t ready = nullptr;
+  TORCH_CHECK(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming) == cudaSuccess && cudaEventRecord(ready, stream) == cudaSuccess,
+              "mla_preprocess: cannot record the weight-repack event");
+  g_repack_cache.emplace(key, RepackEntry{w.storage().getWeakStorageImpl(), km, stream, ready});
   return km;
 }
 
@@ -193,6 +216,10 @@ std::tuple<at::Tensor&, at::Tensor&, at::Tensor&, at::Tensor&> mla_preprocess(
   p.num_cache_blocks = (int32_t)blocks;
   p.cache_block_size = (int32_t)block_size;
   p.descale_is_int64 = dsc_dt == at::kLong;
+  // The operator cannot see what precedes it on the stream, so it only takes the no-wait start (MLAPO_FLAG_INPUT_COMPLETE, see
+  // include/mla_preprocess_b200.h) when the deployment says that no kernel that triggers its dependents early feeds this op.
+  static const bool input_complete = [] { const char* e = std::getenv("SGL_KERNEL_NPU_MLAPO_INPUT_COMPLETE"); return e && e[0] == '1'; }();
+  p.flags = input_complete ? MLAPO_FLAG_INPUT_COMPLETE : 0;
   p.hidden_state = hiddenState.data_ptr();
   p.wdqkv_km = wdqkv_km.data_ptr();
   p.descale0 = descale0.data_ptr();

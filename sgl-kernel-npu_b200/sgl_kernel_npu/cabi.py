@@ -28,7 +28,7 @@ EXPORTS = ["mlapo_version", "mlapo_last_error", "mlapo_get_workspace_size", "mla
 class MlapoParams(ctypes.Structure):
     _fields_ = [(n, ctypes.c_uint32 if n == "struct_bytes" else ctypes.c_int32) for n in (
         "struct_bytes", "num_tokens", "num_heads", "hidden_dim", "act_dtype", "cache_mode", "quant_mode",
-        "num_cache_blocks", "cache_block_size", "descale_is_int64", "reserved0")] + [
+        "num_cache_blocks", "cache_block_size", "descale_is_int64", "flags")] + [
         (n, ctypes.c_void_p) for n in (
             "hidden_state", "wdqkv_km", "descale0", "bias0", "quant_scale0", "quant_offset0", "gamma1", "beta1",
             "quant_scale1", "quant_offset1", "wuq_km", "descale1", "bias1", "gamma2", "cos", "sin", "wuk",
@@ -210,7 +210,7 @@ def _ptr(t):
 
 def build_params(hiddenState, wdqkv_km, descale0, gamma1, beta1, wuq_km, descale1, gamma2, cos, sin, wuk,
                  kv_cache, kv_cache_rope, slotmapping, quant_scale0, quant_offset0, bias0, quant_scale1,
-                 quant_offset1, bias1, ctkv_scale, q_nope_scale, cache_mode, quant_mode, q_out0, q_out1) -> MlapoParams:
+                 quant_offset1, bias1, ctkv_scale, q_nope_scale, cache_mode, quant_mode, q_out0, q_out1, flags=0) -> MlapoParams:
     cache_mode = DEFAULT_CACHE_MODE if cache_mode is None else cache_mode
     quant_mode = DEFAULT_QUANT_MODE if quant_mode is None else quant_mode
     if cache_mode not in CACHE_MODE_MAP:
@@ -286,6 +286,7 @@ def build_params(hiddenState, wdqkv_km, descale0, gamma1, beta1, wuq_km, descale
     p.cache_mode, p.quant_mode = cm, QUANT_MODE_MAP[quant_mode]
     p.num_cache_blocks, p.cache_block_size = blocks, bs
     p.descale_is_int64 = 1 if dsc_dt == torch.int64 else 0
+    p.flags = int(flags)
     p.hidden_state, p.wdqkv_km, p.descale0, p.bias0 = _ptr(hiddenState), _ptr(wdqkv_km), _ptr(descale0), _ptr(bias0)
     p.quant_scale0, p.quant_offset0 = _ptr(quant_scale0), _ptr(quant_offset0)
     p.gamma1, p.beta1 = _ptr(gamma1), _ptr(beta1)
@@ -309,6 +310,7 @@ def launch(p: MlapoParams, workspace: torch.Tensor, stream=None):
            "mla_preprocess_launch")
 
 
+FLAG_INPUT_COMPLETE = 1   # MLAPO_FLAG_INPUT_COMPLETE: nothing the call touches is still pending behind an early-triggering (PDL) producer
 STATIC_MAX_TOKENS, STATIC_MAX_HIDDEN, STATIC_SCRATCH_BYTES = 256, 8192, 20 << 20   # MLAPO_STATIC_* in the header
 
 
@@ -328,7 +330,7 @@ def mla_preprocess(hiddenState, gamma0, beta0, wdqkv_km, descale0, gamma1, beta1
                    cos, sin, wuk, kv_cache, kv_cache_rope, slotmapping,
                    quant_scale0, quant_offset0, bias0, quant_scale1, quant_offset1, bias1, *,
                    ctkv_scale=None, q_nope_scale=None, cache_mode=None, quant_mode=None,
-                   q_out0, kv_cache_out0, q_out1, kv_cache_out1, workspace=None):
+                   q_out0, kv_cache_out0, q_out1, kv_cache_out1, workspace=None, flags=0):
     """Operator-shaped call through the C ABI.  `wdqkv_km` / `wuq_km` are the repacked (K-major) weights.
 
     gamma0/beta0 are accepted and ignored, as in the reference (bf16.hpp:2762, 424-486).
@@ -339,7 +341,7 @@ def mla_preprocess(hiddenState, gamma0, beta0, wdqkv_km, descale0, gamma1, beta1
         raise RuntimeError("kv_cache_out0/1 must be the same storage as kv_cache/kv_cache_rope")
     p = build_params(hiddenState, wdqkv_km, descale0, gamma1, beta1, wuq_km, descale1, gamma2, cos, sin, wuk,
                      kv_cache, kv_cache_rope, slotmapping, quant_scale0, quant_offset0, bias0, quant_scale1,
-                     quant_offset1, bias1, ctkv_scale, q_nope_scale, cache_mode, quant_mode, q_out0, q_out1)
+                     quant_offset1, bias1, ctkv_scale, q_nope_scale, cache_mode, quant_mode, q_out0, q_out1, flags=flags)
     with torch.cuda.device(hiddenState.device):
         if workspace is None:
             workspace = torch.empty(max(workspace_layout(p).total_bytes, 256), dtype=torch.uint8, device=hiddenState.device)

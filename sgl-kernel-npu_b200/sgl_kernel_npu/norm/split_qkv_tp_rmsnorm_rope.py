@@ -1,9 +1,15 @@
 """Mirror of the reference module python/sgl_kernel_npu/sgl_kernel_npu/norm/split_qkv_tp_rmsnorm_rope.py (function
 split_qkv_tp_rmsnorm_rope, :172-288) on the CUDA kernel behind split_qkv_tp_rmsnorm_rope_launch.  Same arguments and return values.
-tp_world == 1: one pass.  tp_world > 1, EXCHANGE == "peer" (default): ONE kernel per rank; the ranks exchange the per-token means inside
-it through a symmetric-memory buffer (torch.distributed._symmetric_memory: every rank's buffer mapped into every process, NVLink peer
-stores).  EXCHANGE == "allreduce", batches beyond the buffer's capacity, or no symmetric memory on this system: local means ->
-dist.all_reduce over tp_group (8 bytes per token, as the reference does between its two kernels, :253-254) -> one-pass apply."""
+tp_world == 1: one pass.  tp_world > 1, EXCHANGE == "allreduce" (default; also batches beyond the buffer's capacity, or no symmetric
+memory on this system): local means -> dist.all_reduce over tp_group (8 bytes per token, as the reference does between its two
+kernels, :253-254) -> one-pass apply.  EXCHANGE == "peer" (opt-in: set the module attribute or SGL_KERNEL_NPU_TP_EXCHANGE=peer): ONE
+kernel per rank; the ranks exchange the per-token means inside it through a symmetric-memory buffer
+(torch.distributed._symmetric_memory: every rank's buffer mapped into every process, plain NVLink peer stores of 8-byte records).
+The one-kernel form halves the latency but asks more of the caller, which is why it is not the default: every rank of the group
+must make the same sequence of calls with the same batch; the kernel's CTAs must all be resident at once (no other kernel may hold
+SMs for good on any rank); one call per group may be in flight; an error return on one rank (so that it skips a launch its peers
+make) leaves the group's epochs apart until the process group is rebuilt; and a rank whose peer never launches traps after its
+bounded wait (about half a minute), which takes that rank's CUDA context down."""
 import ctypes
 import os
 import warnings
@@ -13,7 +19,7 @@ import torch.distributed as dist
 
 from .. import cabi
 
-EXCHANGE = os.environ.get("SGL_KERNEL_NPU_TP_EXCHANGE", "peer")  # "peer" | "allreduce"
+EXCHANGE = os.environ.get("SGL_KERNEL_NPU_TP_EXCHANGE", "allreduce")  # "allreduce" | "peer"
 CAPACITY = 16384  # tokens per call the exchange buffer holds (2 * tp_world * CAPACITY * 16 bytes per rank)
 _state = {}
 

@@ -151,3 +151,23 @@ def test_per_token_mode_runs_and_is_close_to_per_tensor_free_math():
     ref = (x @ case.t["wdqkv_nd"].float().t()) * case.t["descale0"]
     got = taps["y0"].float()
     assert torch.allclose(got, ref, rtol=0.05, atol=0.05 * ref.abs().max().item())
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p) for p in GOLDEN])
+def test_int8_activations_do_not_depend_on_the_reduction_order(path):
+    """north_star: int8 activations bit-exact against the golden.  a0 involves no reduction.  a1 = quant(RMSNorm(q_a)) sees the
+    fp32 row sum, which `var_mode="torch"` takes in the golden's order and `var_mode="exact"` (the CUDA contract) as the
+    exactly accumulated sum: on every fixture the two must give the same int8 a1 (and so the same acc1 / y1 / q_rope), i.e.
+    the CUDA kernels, held bit-exact to "exact", are bit-exact to the golden's a1 as well.  Flips are counted, not hidden."""
+    n, h, d, dt, mode = parse(path)
+    taps_t, taps_e = {}, {}
+    orc.run_case(orc.gen_case(N=n, H=h, D=d, dtype=DT[dt], cache_mode=mode, seed=42), var_mode="torch", taps=taps_t)
+    orc.run_case(orc.gen_case(N=n, H=h, D=d, dtype=DT[dt], cache_mode=mode, seed=42), var_mode="exact", taps=taps_e)
+    flips = {k: int((taps_t[k] != taps_e[k]).sum()) for k in ("a0", "acc0", "y0", "a1", "acc1", "y1", "k_pe")}
+    assert flips == {k: 0 for k in flips}, flips
+    # k_nope is rounded from the normalised fp32 row: a 1-ulp difference of the row sum may move an element across a rounding
+    # boundary; the reference's own tolerance (allclose 1e-3, test_mla:712-744) covers that.  Count what happens here.
+    # Observed: 0 on seven fixtures, 1 element of 15 872 on golden_N31_H64_D7168_fp16_krope_ctkv.
+    kn_flips = int((taps_t["k_nope"] != taps_e["k_nope"]).sum())
+    assert kn_flips <= 1, kn_flips
+    assert torch.allclose(taps_t["k_nope"].float(), taps_e["k_nope"].float(), rtol=1e-3, atol=1e-3)
