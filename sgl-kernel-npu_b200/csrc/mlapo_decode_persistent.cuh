@@ -44,39 +44,38 @@ constexpr int kDecodeSmemBytes = kQSmemBytes;
 constexpr int kDecodeStaticSmem = 256;            // reduction scratch of the quant / norm phases (static __shared__)
 static_assert(kDecodeSmemBytes + kDecodeStaticSmem <= 232448, "persistent decode smem");
 
-// Grid barrier state {arrivals, generation}.  Self-cleaning (arrivals return to 0), so it is valid from module load on;
-// one per device, which is enough because cooperative launches of this kernel on one device are stream-ordered.
-__device__ unsigned g_grid_sync_state[2];
+// Grid barrier: three arrival counters, one per barrier of the kernel, each on its own 128-byte line.  A barrier costs one
+// returning atomic (release) and a poll of the same word (relaxed loads, one acquire fence at the end): two L2 round trips.
+// The counters clean up after themselves — the last CTA to arrive at barrier k zeroes the counter of barrier k-1, which every CTA
+// has left by then — so they are valid from module load on and from launch to launch; one set per device is enough because
+// cooperative launches of this kernel on one device cannot overlap (each needs every SM).
+// (The first version kept {arrivals, generation} on one line and bracketed them with three full membar.gl: 4-5 us per barrier.)
+constexpr int kGridBarriers = 3;
+__device__ unsigned g_grid_ctr[kGridBarriers * 32];
 
-__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
 // All CTAs of the (co-resident) grid.  Global writes made before it by any thread — through the generic proxy or by
 // completed TMA stores — are visible afterwards to generic loads and to TMA loads of every CTA.
-__device__ __forceinline__ void grid_sync(unsigned nblocks) {
+__device__ __forceinline__ void grid_sync(int k, unsigned nblocks) {
   fence_proxy_async_all();
   __syncthreads();
   if (threadIdx.x == 0) {
-    unsigned* st = g_grid_sync_state;
-    const unsigned gen = ld_acquire_gpu(st + 1);
-    __threadfence();
-    if (atomicAdd(st, 1u) == nblocks - 1) {
-      atomicExch(st, 0u);
-      __threadfence();
-      atomicAdd(st + 1, 1u);
+    unsigned* ctr = g_grid_ctr + k * 32;
+    unsigned old;
+    asm volatile("atom.add.release.gpu.global.u32 %0, [%1], 1;" : "=r"(old) : "l"(ctr) : "memory");
+    if (old == nblocks - 1) {
+      unsigned* prev = g_grid_ctr + ((k + kGridBarriers - 1) % kGridBarriers) * 32;
+      asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(prev), "r"(0u) : "memory");
     } else {
-      const long long t0 = clock64();
-      while (ld_acquire_gpu(st + 1) == gen) {
-        __nanosleep(32);
-        const long long dt = clock64() - t0;
-        if (dt > 4000000000LL) ptx::wait_timeout(blockIdx.x, 0xFFFFu, gen, 0);  // a missing participant becomes a launch failure, not a hang
-      }
+      unsigned v;
+      unsigned n = 0;
+      do {
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+        if (++n > (1u << 24)) ptx::wait_timeout(blockIdx.x, 0xFFFFu, (unsigned)k, v);  // a missing participant becomes a launch failure, not a hang
+      } while (v != nblocks);
     }
-    __threadfence();
+    asm volatile("fence.acq_rel.gpu;" ::: "memory");
   }
   __syncthreads();
   fence_proxy_async_all();
@@ -150,7 +149,7 @@ mla_decode_persistent_kernel(const __grid_constant__ CUtensorMap tm_a0, const __
                         (long long)cta * blockDim.x + threadIdx.x, (long long)nblocks * blockDim.x);
   }
   if (threadIdx.x == 0) tl_mark(da.tl_mm1, 10);  // quant done, entering barrier 1
-  grid_sync(nblocks);
+  grid_sync(0, nblocks);
 
   // ---- phase 2: MM1 split-K partial sums
   if (threadIdx.x == 0) tl_mark(da.tl_mm1, 2);
@@ -162,7 +161,7 @@ mla_decode_persistent_kernel(const __grid_constant__ CUtensorMap tm_a0, const __
   if (threadIdx.x == 32) tl_mark(da.tl_mm1, 9);
   // first W_UQ k-blocks of this CTA's head: requested now, they land while the norm phase runs
   if (warp == 0 && lane == 0 && has_q && (da.stop_after == 0 || da.stop_after > 3)) q_issue_weights(qc, &tm_wuq);
-  grid_sync(nblocks);
+  grid_sync(1, nblocks);
   if (threadIdx.x == 0) tl_mark(da.tl_mm1, 11);  // barrier 2 passed
   const bool run3 = da.stop_after == 0 || da.stop_after >= 3;
 
@@ -172,7 +171,7 @@ mla_decode_persistent_kernel(const __grid_constant__ CUtensorMap tm_a0, const __
     __syncthreads();  // the reduction scratch is re-used by the next token
   }
   if (threadIdx.x == 0) tl_mark(da.tl_mm1, 12);  // norm done, entering barrier 3
-  grid_sync(nblocks);
+  grid_sync(2, nblocks);
 
   // ---- phase 4: per-head q path
   if (threadIdx.x == 0) { tl_mark_global(da.tl_q, 0); tl_mark(da.tl_q, 1); tl_mark(da.tl_q, 2); }

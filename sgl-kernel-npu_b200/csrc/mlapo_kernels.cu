@@ -273,6 +273,11 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   if ((rc = make_tmap(&tm_wdqkv, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wdqkv_km, MLAPO_MM1_OUT, d, d, bn, 128))) return rc;
   if ((rc = make_tmap(&tm_part, CU_TENSOR_MAP_DATA_TYPE_INT32, 4, partial0, n, MLAPO_MM1_OUT, MLAPO_MM1_OUT * 4, kBlockM, 32, l.splits0,
                       (uint64_t)n * MLAPO_MM1_OUT * 4))) return rc;
+  // prefill shape: MM1 dequantises in its epilogue and writes act y0 [N, 2112] where the int32 sums would have gone (or, with the
+  // debug tap on, into the tap region, the raw sums then going to their usual place as well)
+  T* const y0_buf = (g_debug_flags & 2) ? reinterpret_cast<T*>(ws + l.y0_tap) : reinterpret_cast<T*>(partial0);
+  CUtensorMap tm_y0;
+  if (wide && (rc = make_tmap(&tm_y0, act_dt, 2, y0_buf, n, MLAPO_MM1_OUT, MLAPO_MM1_OUT * 2, kBlockM, 64))) return rc;
   const int cta_tokens = q_cta_tokens(n, h);
   const int a1_box_rows = cta_tokens > kBlockM ? 2 * kBlockM : kBlockM;  // one box per stage covers every token tile of the CTA
   if ((rc = make_tmap(&tm_a1, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a1, n, MLAPO_Q_LORA, MLAPO_Q_LORA, a1_box_rows, 128))) return rc;
@@ -299,7 +304,8 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   na.slots = reinterpret_cast<const int32_t*>(p->slot_mapping);
   na.ctkv_scale = p->ctkv_scale;
   na.a1 = a1;
-  na.y0_tap = (g_debug_flags & 2) ? ws + l.y0_tap : nullptr;
+  na.y0_tap = ((g_debug_flags & 2) && !wide) ? ws + l.y0_tap : nullptr;
+  na.y0_in = wide ? y0_buf : nullptr;
   na.kv_cache = p->kv_cache; na.kv_cache_rope = p->kv_cache_rope;
   na.cache_mode = p->cache_mode;
   na.cache_slots = (long long)p->num_cache_blocks * p->cache_block_size;
@@ -353,6 +359,7 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     return MLAPO_OK;
   }
   g_kernel_names[0] = "quant_hidden";
+  g_kernel_names[1] = "mm1_splitk";
 
   // ---- k1: quantise hiddenState (bit12 of the debug flags: also ask for the call's weights in L2 — measured slower, see profiles/README.md)
   WeightPrefetch wp{};
@@ -392,9 +399,14 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     const int n_tiles = (MLAPO_MM1_OUT + bn - 1) / bn;
     if (wide) {
       static DoneFlag done[kMaxDevices];
-      if ((rc = set_smem_attr(mm1_splitk_kernel<2, kMm1BlockNWide>, mm1_smem_bytes<2, kMm1BlockNWide>(), &done[dev], "mm1<2,256>"))) return rc;
-      e__ = launch_k(mm1_splitk_kernel<2, kMm1BlockNWide>, dim3(n_tiles, 1, (n + 255) / 256), dim3(kGemmThreads),
-                     mm1_smem_bytes<2, kMm1BlockNWide>(), st, pdl, tm_a0, tm_wdqkv, tm_part, n, d / kBlockKBytes, tl1);
+      constexpr int smem = mm1_smem_bytes<2, kMm1BlockNWide, true>();
+      if ((rc = set_smem_attr(mm1_dequant_kernel<2, kMm1BlockNWide, T>, smem, &done[dev], "mm1_dequant<2,256>"))) return rc;
+      Mm1DequantArgs dq{};
+      dq.bias0 = na.bias0; dq.descale0 = p->descale0; dq.tok_scale0 = na.tok_scale0; dq.descale_is_i64 = p->descale_is_int64;
+      dq.tap_acc = (g_debug_flags & 2) ? 1 : 0;
+      e__ = launch_k(mm1_dequant_kernel<2, kMm1BlockNWide, T>, dim3(n_tiles, 1, (n + 255) / 256), dim3(kGemmThreads), smem, st, pdl,
+                     tm_a0, tm_wdqkv, tm_part, tm_y0, dq, n, d / kBlockKBytes, tl1);
+      g_kernel_names[1] = "mm1_dequant";
     } else if (n > kBlockM) {
       static DoneFlag done[kMaxDevices];
       if ((rc = set_smem_attr(mm1_splitk_kernel<2, kMm1BlockN>, mm1_smem_bytes<2, kMm1BlockN>(), &done[dev], "mm1<2,128>"))) return rc;
@@ -411,7 +423,8 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   record_event(2, st);
 
   // ---- k3: norms, quant, rope, cache scatter
-  if (l.splits0 == 1) e__ = launch_k(norm_rope_cache_kernel<T, 1>, dim3(n), dim3(kNormThreads), 0, st, pdl, na);  // prefill: no split-K
+  if (wide) e__ = launch_k(norm_rope_cache_kernel<T, 0>, dim3(n), dim3(kNormThreads), 0, st, pdl, na);  // prefill: reads the dequantised rows
+  else if (l.splits0 == 1) e__ = launch_k(norm_rope_cache_kernel<T, 1>, dim3(n), dim3(kNormThreads), 0, st, pdl, na);
   else e__ = launch_k(norm_rope_cache_kernel<T, 8>, dim3(n), dim3(kNormThreads), 0, st, pdl, na);
   MLAPO_CHECK_LAUNCH("norm_rope_cache");
   record_event(3, st);

@@ -1,4 +1,4 @@
-// k2 MM1: a0 . Wdqkv^T as tcgen05 kind::i8 with split-K partial sums.
+// k2 MM1: a0 . Wdqkv^T as tcgen05 kind::i8: split-K partial sums (decode) or the dequantised rows y0 straight from the epilogue (prefill).
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -28,10 +28,21 @@ constexpr int kMm1BlockNWide = 256;  // prefill (no split-K): 256 x 256 CTA tile
 
 template <int MT, int BN>
 __host__ __device__ constexpr int mm1_stages() { return (MT * kTile16K + BN * kBlockKBytes) > 49152 ? 3 : 4; }
-template <int MT, int BN>
+template <int MT, int BN, bool kDequant = false>
 constexpr int mm1_smem_bytes() {
-  return mm1_stages<MT, BN>() * (MT * kTile16K + BN * kBlockKBytes) + 256 + 1024;
+  return mm1_stages<MT, BN>() * (MT * kTile16K + BN * kBlockKBytes) + 256 + (kDequant ? BN * 8 : 0) + 1024;
 }
+
+// The dequantising epilogue's inputs (prefill: no split-K, so the accumulators are complete when the MMAs retire):
+// y0 = act_rne(fp32(acc + bias0[n]) * descale0[n]) (per-tensor) or act_rne(fp32(acc) * descale0[n] * tokScale0[m]) (per-token)
+// — PpMatmulW8a8Aiv, mla_preprocess_mix_bf16.hpp:2204-2330, which the reference also runs tile by tile behind the matmul.
+struct Mm1DequantArgs {
+  const int32_t* bias0;     // [2112] or null (per-token mode)
+  const void* descale0;     // f32 | int64 [2112]
+  const float* tok_scale0;  // [N] or null
+  int descale_is_i64;
+  int tap_acc;              // debug: also store the raw int32 accumulators through the partial-sum tensor map
+};
 
 // Where one CTA's MM1 work item lives: its k-range, its tiles, its pipeline in shared memory and its TMEM columns.
 template <int MT, int BN>
@@ -84,9 +95,11 @@ __device__ __forceinline__ void mm1_issue_weights(const Mm1Ctx<MT, BN>& c, const
 // Warp roles of MM1: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer, warps 2..5 = epilogue (TMEM lane quarter = warp%4);
 // other warps fall through.  The caller has already issued mm1_issue_weights().  kStandalone: own kernel under PDL, the
 // producer waits for the upstream kernel before it touches a0; otherwise the caller guarantees a0 is complete.
-template <int MT, int BN, bool kStandalone>
+template <int MT, int BN, bool kStandalone, bool kDequant = false, class T = __nv_bfloat16>
 __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtensorMap* tm_a, const CUtensorMap* tm_b,
-                                          const CUtensorMap* tm_p, int warp, int lane, long long* tl) {
+                                          const CUtensorMap* tm_p, int warp, int lane, long long* tl,
+                                          const CUtensorMap* tm_y = nullptr, const int2* s_cst = nullptr,
+                                          const Mm1DequantArgs* dq = nullptr) {
   using C = Mm1Ctx<MT, BN>;
   constexpr int STAGES = C::STAGES, A_BYTES = C::A_BYTES, B_BYTES = C::B_BYTES, STAGE_BYTES = C::STAGE_BYTES, GRANULES = C::GRANULES;
   uint8_t* const smem = c.smem;
@@ -165,7 +178,9 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
     // each token tile gets its own staging tiles when the drained pipeline is large enough for all of them (decode shape);
     // otherwise the tiles are re-used and the previous token tile's stores must have been read first
     constexpr bool kOwnStaging = MT * GRANULES * kTile16K <= STAGES * STAGE_BYTES;
-    for (int m = 0; m < mt_valid; ++m) {
+    bool raw = true;  // store the int32 accumulators (always in the split-K form; only as a debug tap in the dequantising form)
+    if constexpr (kDequant) raw = dq->tap_acc != 0;
+    for (int m = 0; raw && m < mt_valid; ++m) {
       if (m > 0 && !kOwnStaging) {
         if (issuer) ptx::tma_store_wait_read<0>();
         ptx::named_bar_sync(1, 128);
@@ -190,9 +205,104 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
         ptx::tma_store_commit();
       }
     }
+    if constexpr (kDequant) {
+      // ---- dequantise in the epilogue: TMEM -> (+bias) * descale -> act -> swizzled smem -> TMA store into y0 [N, 2112]
+      constexpr int G64 = BN / 64;  // 64 act columns = one 128-byte row per token
+      static_assert(MT * G64 * kTile16K <= STAGES * STAGE_BYTES, "every token tile has its own staging tiles");
+      if (raw) {  // the tap's stores still read the staging tiles
+        if (issuer) ptx::tma_store_wait_read<0>();
+        ptx::named_bar_sync(1, 128);
+      }
+      for (int m = 0; m < mt_valid; ++m) {
+        const int t = m0 + m * kBlockM + row;
+        const float ts = dq->tok_scale0 ? dq->tok_scale0[t < c.m_total ? t : c.m_total - 1] : 1.f;
+        uint8_t* const stg = smem + m * G64 * kTile16K;
+#pragma unroll 1
+        for (int g = 0; g < G64; ++g) {
+          uint32_t ra[32], rb[32];
+          ptx::tmem_ld_32x32b_x32(t_base + m * BN + g * 64, ra);
+          ptx::tmem_ld_32x32b_x32(t_base + m * BN + g * 64 + 32, rb);
+          ptx::tmem_ld_wait();
+          uint32_t w[32];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            // one expression for both modes: per-tensor carries a token scale of 1 (x * 1.0f is exact), per-token a bias of 0
+            const int4 ca = *reinterpret_cast<const int4*>(s_cst + g * 64 + 2 * j);
+            const int4 cb = *reinterpret_cast<const int4*>(s_cst + g * 64 + 32 + 2 * j);
+            const float a0 = __fmul_rn(__fmul_rn(__int2float_rn((int)ra[2 * j] + ca.x), __int_as_float(ca.y)), ts);
+            const float a1 = __fmul_rn(__fmul_rn(__int2float_rn((int)ra[2 * j + 1] + ca.z), __int_as_float(ca.w)), ts);
+            const float b0 = __fmul_rn(__fmul_rn(__int2float_rn((int)rb[2 * j] + cb.x), __int_as_float(cb.y)), ts);
+            const float b1 = __fmul_rn(__fmul_rn(__int2float_rn((int)rb[2 * j + 1] + cb.z), __int_as_float(cb.w)), ts);
+            w[j] = Act<T>::pack(a0, a1);
+            w[16 + j] = Act<T>::pack(b0, b1);
+          }
+          const uint32_t tile = ptx::smem_u32(stg + g * kTile16K);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) ptx::st_shared_v4(tile + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+        }
+        ptx::fence_proxy_async_smem();
+        ptx::named_bar_sync(1, 128);
+        if (issuer) {
+          for (int g = 0; g < G64; ++g)
+            if (n0 + g * 64 < MLAPO_MM1_OUT) ptx::tma_store_2d(tm_y, ptx::smem_u32(stg + g * kTile16K), n0 + g * 64, m0 + m * kBlockM);
+          ptx::tma_store_commit();
+        }
+      }
+    }
     if (issuer) { tl_mark(tl, 7); ptx::tma_store_wait_read<0>(); tl_mark(tl, 8); }
   }
 
+}
+
+// The same kernel with the dequantising epilogue (no split-K: grid.y == 1): writes y0 act [N, 2112] instead of int32 sums.
+template <int MT, int BN, class T>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+mm1_dequant_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+                   const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_y, Mm1DequantArgs dq,
+                   int m_total, int kb_total, long long* tl) {
+  using C = Mm1Ctx<MT, BN>;
+  if (threadIdx.x == 0) { tl_mark_global(tl, 0); tl_mark(tl, 1); }
+  extern __shared__ uint8_t smem_raw[];
+  C c;
+  c.smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  c.bars = reinterpret_cast<uint64_t*>(c.smem + C::STAGES * C::STAGE_BYTES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(c.bars + C::NUM_BARS + 1);
+  int2* s_cst = reinterpret_cast<int2*>(c.smem + C::STAGES * C::STAGE_BYTES + 256);  // per column {bias, descale bits}
+  c.set_work(blockIdx.x, 0, 1, blockIdx.z, m_total, kb_total);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {  // barriers + the first weight tiles before anything else: they depend on nothing
+    ptx::prefetch_tmap(&tm_b);
+    mm1_init_barriers<MT, BN>(c.bars);
+    ptx::fence_mbar_init();
+    mm1_issue_weights<MT, BN>(c, &tm_b);
+    ptx::prefetch_tmap(&tm_a);
+    ptx::prefetch_tmap(&tm_y);
+    ptx::prefetch_tmap(&tm_p);
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), C::TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  for (int i = threadIdx.x; i < BN; i += kGemmThreads) {  // weight-like parameters: complete long before the call
+    const int col = c.n0 + i;
+    int2 v = make_int2(0, 0);
+    if (col < MLAPO_MM1_OUT) v = make_int2(dq.bias0 ? dq.bias0[col] : 0, __float_as_int(load_descale(dq.descale0, dq.descale_is_i64, col)));
+    s_cst[i] = v;
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  c.tmem_acc = *tmem_slot;
+  ptx::griddep_launch_dependents();
+  if (threadIdx.x == 0) tl_mark(tl, 2);  // prologue done
+
+  mm1_roles<MT, BN, true, true, T>(c, &tm_a, &tm_b, &tm_p, warp, lane, tl, &tm_y, s_cst, &dq);
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(c.tmem_acc, C::TMEM_COLS);
+  if (threadIdx.x == 32) { tl_mark(tl, 9); tl_mark_global(tl, 15); }
 }
 
 template <int MT, int BN>

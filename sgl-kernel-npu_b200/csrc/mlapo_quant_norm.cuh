@@ -163,6 +163,7 @@ __global__ void __launch_bounds__(256) quant_hidden_per_token_kernel(const T* __
 // ============================================================================================ k3: norms, quant, rope, cache
 struct NormArgs {
   const int32_t* partial;  // [splits, N, 2112]
+  const void* y0_in;       // act [N, 2112]: the dequantised rows when MM1's epilogue produced them (kMaxSplits == 0), else unused
   int splits;
   int n_tokens;
   const int32_t* bias0;    // null in per-token mode
@@ -217,9 +218,11 @@ __device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const
   const bool early_inputs = !kPdlWait || a.input_complete;
   int slot = early_inputs ? a.slots[t] : 0;
   {
-    float d[8];
+    float d[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     int bias[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    if (a.descale_is_i64) {
+    if constexpr (kMaxSplits == 0) {
+      // MM1's epilogue already dequantised: nothing to fetch for that
+    } else if (a.descale_is_i64) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) d[j] = load_descale(a.descale0, 1, col + j);
     } else {
@@ -227,7 +230,7 @@ __device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const
       const float4 d1 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(a.descale0) + col + 4);
       d[0] = d0.x; d[1] = d0.y; d[2] = d0.z; d[3] = d0.w; d[4] = d1.x; d[5] = d1.y; d[6] = d1.z; d[7] = d1.w;
     }
-    if (a.bias0) {
+    if (kMaxSplits != 0 && a.bias0) {
       const int4 b0 = *reinterpret_cast<const int4*>(a.bias0 + col), b1 = *reinterpret_cast<const int4*>(a.bias0 + col + 4);
       bias[0] = b0.x; bias[1] = b0.y; bias[2] = b0.z; bias[3] = b0.w; bias[4] = b1.x; bias[5] = b1.y; bias[6] = b1.z; bias[7] = b1.w;
     }
@@ -251,6 +254,11 @@ __device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const
         }
       }
     }
+    if constexpr (kMaxSplits == 0) {
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (active) v = *reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.y0_in) + (long long)t * MLAPO_MM1_OUT + col);
+      unpack8<T>(v, x);
+    } else {
     int4 pu[kMaxSplits], pv[kMaxSplits];
 #pragma unroll
     for (int s = 0; s < kMaxSplits; ++s) {
@@ -279,6 +287,7 @@ __device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const
     if (a.y0_tap && active) {
       T* yo = reinterpret_cast<T*>(a.y0_tap) + (long long)t * MLAPO_MM1_OUT + col;
       ptx::st_global_v4(yo, Act<T>::pack(x[0], x[1]), Act<T>::pack(x[2], x[3]), Act<T>::pack(x[4], x[5]), Act<T>::pack(x[6], x[7]));
+    }
     }
   }
 
@@ -391,7 +400,7 @@ __device__ __forceinline__ void norm_token(const NormArgs& a, const int t, const
 }
 
 template <class T, int kMaxSplits>
-__global__ void __launch_bounds__(kNormThreads, kMaxSplits == 1 ? 4 : 2) norm_rope_cache_kernel(NormArgs a) {
+__global__ void __launch_bounds__(kNormThreads, kMaxSplits <= 1 ? 4 : 2) norm_rope_cache_kernel(NormArgs a) {
   const int tid = threadIdx.x;
   if (tid == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 0);
   ptx::griddep_launch_dependents();
