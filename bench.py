@@ -134,9 +134,7 @@ def kernel_algorithmic_bytes(name, n, h, d, cache_mode):
         "norm_rope_cache": n * 2112 * 4 + n * 1536 + n * (512 * q0 + 128) + n * 260 + 8 * 2112 + 4 * 1536 + 1024,
         "norm_rope_cache_y0": n * 2112 * 2 + n * 1536 + n * (512 * q0 + 128) + n * 260 + 4 * 1536 + 1024,
         "q_fused": qb,
-        "q_stream": qb,
         "q_pair": qb,
-        "decode_persistent": algorithmic_bytes(n, h, d, cache_mode),
     }.get(name, 0)
 
 
@@ -612,7 +610,7 @@ def run_ours(args):
     except Exception:
         pass
     ranks = Ranks("nccl", dev)
-    dbg = (32 if args.persistent else 0) | args.debug_flags
+    dbg = args.debug_flags
     if dbg:
         cabi.set_debug_flags(dbg)
     # The bench enqueues its calls behind torch copy kernels and behind this library's own kernels only, none of which releases its
@@ -736,7 +734,7 @@ def run_ours(args):
                         "kernel_us_in_chain": span,
                         "kernel_us_in_chain_is": "first CTA start to last CTA end of the kernel inside back-to-back chained calls (per-CTA global-timer marks); it starts under its predecessor's tail",
                         "peak_source": peak_src}
-            if wl.n >= 2048 and dom in ("q_fused", "q_stream", "q_pair"):
+            if wl.n >= 2048 and dom in ("q_fused", "q_pair"):
                 ops = 2.0 * wl.n * 1536 * 192 * wl.h + 2.0 * wl.n * 128 * 512 * wl.h
                 tach = ops / (kernels[dom] * 1e-6) / 1e12
                 roofline.update({"bound": "tensor", "achieved": round(tach, 1), "peak": INT8_NOMINAL_TOPS, "unit": "TOP/s",
@@ -867,8 +865,6 @@ def main():
     ap.add_argument("--no-subrecords", action="store_true", help="skip the prefill / c5 / tp sub-records of the default line")
     ap.add_argument("--safe-start", action="store_true", help="do not state MLAPO_FLAG_INPUT_COMPLETE (the library's default start)")
     ap.add_argument("--debug-flags", type=int, default=0, help="A/B: extra mlapo_set_debug_flags bits")
-    ap.add_argument("--persistent", action="store_true",
-                    help="A/B: run eligible calls (<= 256 tokens) as the opt-in single persistent cooperative kernel")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -318,12 +318,12 @@ int mlapo_launches_per_call(const MlapoParams* p);
  * CMakeLists.txt:48-53).  TEST AND PROFILING ONLY: the flags are one process-wide word; set them from one thread while
  * no call is being enqueued by another.  Bits 1 and 3 enlarge the workspace, so mlapo_get_workspace_size() and the launch
  * must see the same flags (a launch takes one snapshot of the word and refuses a workspace that is too small for it).
- * flags: bit0 = synchronise and check after every kernel (errors name the kernel),
- * bit1 = also write the dequantised MM1 rows y0 (act [N,2112]) after the last workspace region,
- * bit2 = record CUDA events around every kernel of the next launches, bit3 = per-CTA clock marks (timeline region),
- * bit6 = keep the one-CTA-per-unit q-path kernel where the streaming form would be used,
- * bit5 = run decode-sized calls (<= 256 tokens) as the single persistent cooperative kernel instead of four chained kernels,
- * bits 8-10 = leave the persistent kernel after that phase, bit11 = log stuck barrier waits to a host-mapped buffer before trapping.
+ * flags: bit0 = synchronise and check after every kernel (errors name the kernel; also serialises the kernels),
+ * bit1 = also write the dequantised MM1 rows y0 (act [N,2112]) after the last workspace region (and, at prefill sizes, the raw
+ * int32 sums where the split-K partial sums normally go), bit2 = record CUDA events around every kernel of the next launches,
+ * bit3 = per-CTA clock marks (timeline region), bit11 = log stuck barrier waits to a host-mapped buffer before trapping,
+ * bit12 = the quantise kernel also asks for the call's weights in L2 (measured slower; kept for A/B), bit13 = use the CTA-pair
+ * q kernel for every call of more than 128 tokens.
  * Returns the previous flags.
  */
 int mlapo_set_debug_flags(int flags);

@@ -1,6 +1,6 @@
 // mla_preprocess for B200 (sm_100a): hand-written CUDA kernels + the C-ABI launcher.
 // This translation unit holds the host side (validation, tensor maps, launches) and the extern "C" entry points; the
-// kernels live in mlapo_quant_norm.cuh (k0 k1 k3), mlapo_mm1.cuh (k2), mlapo_q.cuh (k4 k6), mlapo_decode_persistent.cuh (k5),
+// kernels live in mlapo_quant_norm.cuh (k0 k1 k3), mlapo_mm1.cuh (k2), mlapo_q.cuh (k4), mlapo_q_pair.cuh (k7),
 // on top of mlapo_numerics.cuh and the inline-PTX layer sm100_ptx.cuh.
 //
 // Path (reference phases P1..P6, csrc/mla_preprocess/op_kernel/mla_preprocess_mix_bf16.hpp:2773-2916):
@@ -11,10 +11,10 @@
 //                          latent RMSNorm(512), RoPE(64), paged-cache scatter (RmsNormAndRopeConvergence1, :2499-2686)
 //   k4 q_fused (per head)  a1 . Wuq[h]^T, dequant, RoPE -> q_out1; nope slice stays in smem and is absorbed:
 //                          q_nope . Wuk[h] -> q_out0 (+ int8 re-quant)      (PpMatmulW8a8Aiv, RopeFp16, PpMatmulEinSum, EinSumQuant)
-//   k5 decode_persistent   k1..k4 as phases of ONE cooperative kernel with grid barriers, for calls of <= 256 tokens (opt-in)
-//   k6 q_stream            k4's arithmetic with persistent CTAs and overlapped units, when units outnumber the SMs (prefill)
-// As separate kernels (prefill sizes) k1..k4 are chained with programmatic dependent launch: each requests its weight
-// tiles, then griddepcontrol.wait.
+//   k7 q_pair              k4's arithmetic on CTA pairs (tcgen05 cta_group::2) streaming units, when units outnumber the SMs (prefill)
+// k1..k4 are chained with programmatic dependent launch: each requests its weight tiles, then griddepcontrol.wait.  (A single
+// persistent cooperative kernel holding all four phases existed in rounds 1-2; it was measured slower at every decode size, even
+// with a 1.7 us grid barrier, and was removed: DESIGN.md §5.)
 // The contractions are tcgen05.mma (kind::i8 with int32 accumulators, kind::f16 for the bf16/fp16 absorb) fed by TMA
 // into 128B-swizzled shared memory with accumulators in TMEM.  Arithmetic follows the reference's torch golden
 // (tests/python/sgl_kernel_npu/test_mla_preprocess.py:57-107, 407-484) operation by operation (see oracle/).
@@ -40,7 +40,6 @@
 #include "mlapo_mm1.cuh"
 #include "mlapo_q.cuh"
 #include "mlapo_q_pair.cuh"
-#include "mlapo_decode_persistent.cuh"
 #include "mlapo_format.cuh"
 #include "mlapo_bmt.cuh"
 #include "mlapo_slots.cuh"
@@ -232,18 +231,6 @@ static int set_smem_attr(K kern, int bytes, DoneFlag* done, const char* name) {
 // weights from L2.
 static int q_cta_tokens(int n, int h) { return (n > kBlockM && (long long)h * ((n + 255) / 256) >= 96) ? 256 : 128; }
 
-// Decode-sized calls CAN run as one persistent cooperative kernel (k5) when every phase fits a single wave of CTAs.
-// It is opt-in (flag bit5): measured on B200 at C2 it takes 52.4 us against 38.5 us for the four PDL-chained kernels —
-// each of its three grid barriers costs 2-3 us and the norm phase handles a CTA's tokens one after the other
-// (profiles/README.md, "persistent decode kernel") — so the chain stays the default until those two costs are fixed.
-static bool decode_persistent_eligible(const MlapoParams* p, int splits0) {
-  if (!(g_debug_flags & 32)) return false;  // bit5: use the persistent decode kernel where eligible
-  const int n = p->num_tokens, h = p->num_heads;
-  if (n < 1 || n > 256) return false;
-  const int ct = q_cta_tokens(n, h);
-  return kMm1NTiles * splits0 <= num_sms() && h * ((n + ct - 1) / ct) <= num_sms();
-}
-
 template <class T>
 static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLayout& l, cudaStream_t st) {
   const int n = p->num_tokens, d = p->hidden_dim, h = p->num_heads;
@@ -263,10 +250,9 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   int rc;
   cudaError_t e__ = cudaSuccess;
   const int dev = current_device();
-  const bool persistent = decode_persistent_eligible(p, l.splits0);
 
   // ---- tensor maps and argument blocks shared by both launch shapes
-  const bool wide = !persistent && l.splits0 == 1 && n >= 1024;  // prefill: no split-K, 256-wide weight tiles
+  const bool wide = l.splits0 == 1 && n >= 1024;  // prefill: no split-K, 256-wide weight tiles
   const int bn = wide ? kMm1BlockNWide : kMm1BlockN;
   CUtensorMap tm_a0, tm_wdqkv, tm_part, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1;
   if ((rc = make_tmap(&tm_a0, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a0, n, d, d, kBlockM, 128))) return rc;
@@ -320,44 +306,6 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   qa.num_heads = h; qa.m_total = n; qa.cta_tokens = cta_tokens;
   const int q_tok_tiles = (n + cta_tokens - 1) / cta_tokens;
 
-  if (persistent) {
-    // ---- k5: one cooperative launch, one CTA per SM
-    DecodeArgs da{};
-    da.hidden = p->hidden_state; da.a0 = a0;
-    da.quant_scale0 = p->quant_scale0; da.quant_offset0 = reinterpret_cast<const int8_t*>(p->quant_offset0);
-    da.tok_scale0 = per_token ? tok_scale : nullptr;
-    da.hidden_dim = d; da.n_tokens = n; da.splits0 = l.splits0; da.q_tok_tiles = q_tok_tiles;
-    da.norm = na; da.q = qa; da.tl_mm1 = tl1; da.tl_q = tl4;
-    da.stop_after = (g_debug_flags >> 8) & 7;
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(num_sms());
-    cfg.blockDim = dim3(kQThreads);
-    cfg.dynamicSmemBytes = kDecodeSmemBytes;
-    cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeCooperative;  // the grid barriers need every CTA resident
-    at[0].val.cooperative = 1;
-    cfg.attrs = at;
-    cfg.numAttrs = 1;
-    record_event(0, st);
-#define MLAPO_LAUNCH_DECODE(I8, MT)                                                                                        \
-  do {                                                                                                                     \
-    static DoneFlag done[kMaxDevices];                                                                                             \
-    if ((rc = set_smem_attr(mla_decode_persistent_kernel<T, I8, MT>, kDecodeSmemBytes, &done[dev], "decode_persistent"))) return rc; \
-    e__ = cudaLaunchKernelEx(&cfg, mla_decode_persistent_kernel<T, I8, MT>, tm_a0, tm_wdqkv, tm_part, tm_a1, tm_wuq, tm_wuk, tm_o0,  \
-                             tm_o1, da);                                                                                   \
-  } while (0)
-    if (n > kBlockM) {
-      if (int8_out) MLAPO_LAUNCH_DECODE(true, 2); else MLAPO_LAUNCH_DECODE(false, 2);
-    } else {
-      if (int8_out) MLAPO_LAUNCH_DECODE(true, 1); else MLAPO_LAUNCH_DECODE(false, 1);
-    }
-#undef MLAPO_LAUNCH_DECODE
-    MLAPO_CHECK_LAUNCH("decode_persistent");
-    record_event(1, st);
-    g_kernel_names[0] = "decode_persistent";
-    return MLAPO_OK;
-  }
   g_kernel_names[0] = "quant_hidden";
   g_kernel_names[1] = "mm1_splitk";
 
@@ -374,15 +322,25 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
                    tok_scale, d, wp);
   } else {
     const long long nvec = (long long)n * d / 8;
-    // The whole grid must be resident at once, otherwise its last blocks start late and the programmatic launch of MM1
-    // (which wants to fetch weights meanwhile) waits for them: 4 blocks of 256 threads per SM is always resident.
-    const long long wave = (long long)num_sms() * 4 * 256;
-    if (nvec <= wave) {  // one 16-byte vector per thread
-      e__ = launch_k(quant_hidden_kernel<T, 1>, dim3((unsigned)((nvec + 255) / 256)), dim3(256), 0, st, pdl,
+    // Blocks of 128 threads (4 warps x 40 registers, no shared memory): small enough that one of them fits on an SM next to a
+    // q_fused CTA of the previous call (10 warps x 168 registers and all but 1.25 KB of the SM's shared memory), so that under
+    // MLAPO_FLAG_INPUT_COMPLETE the quantiser runs while that kernel is still busy instead of queueing for its SMs.
+    constexpr int qt = 128;
+    {  // same shared-memory carve-out as the q kernel, or the SM would have to drain before it can take a quantise block
+      static DoneFlag done[kMaxDevices];
+      if (!done[dev].load(std::memory_order_acquire)) {
+        cudaFuncSetAttribute(quant_hidden_kernel<T, 1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(quant_hidden_kernel<T, 2>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        done[dev].store(true, std::memory_order_release);
+      }
+    }
+    const long long wave = (long long)num_sms() * 8 * 256;
+    if (nvec <= wave / 2) {  // one 16-byte vector per thread
+      e__ = launch_k(quant_hidden_kernel<T, 1>, dim3((unsigned)((nvec + qt - 1) / qt)), dim3(qt), 0, st, pdl,
                      reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
                      reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0, input_complete);
-    } else if (nvec <= 2 * wave) {  // two vectors per thread, both loads in flight
-      e__ = launch_k(quant_hidden_kernel<T, 2>, dim3((unsigned)((nvec + 511) / 512)), dim3(256), 0, st, pdl,
+    } else if (nvec <= wave) {  // two vectors per thread, both loads in flight
+      e__ = launch_k(quant_hidden_kernel<T, 2>, dim3((unsigned)((nvec + 2 * qt - 1) / (2 * qt))), dim3(qt), 0, st, pdl,
                      reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
                      reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0, input_complete);
     } else {                 // prefill sizes: grid-stride, 4 independent loads in flight per thread
@@ -429,13 +387,14 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   MLAPO_CHECK_LAUNCH("norm_rope_cache");
   record_event(3, st);
 
-  // ---- k4 / k6: fused MM2 + dequant + RoPE + W_UK absorb.  One CTA per (head, token super-tile) while those fit one wave;
-  //      beyond that, persistent CTAs stream the units so that consecutive units overlap.
+  // ---- k4 / k7: fused MM2 + dequant + RoPE + W_UK absorb.  One CTA per (head, token super-tile) while those fit one wave;
+  //      beyond that, persistent CTA pairs stream the units so that consecutive units overlap.
   const int q_units = h * ((n + 255) / 256);
-  // k7 wins where a pair has many units to stream (C3: 494 vs 558 us for the q path); with one or two units per pair (decode)
-  // its longer dependency chain loses to k4 (C2: 33 vs 27 us), so it takes over k6's range only.  bit13 forces it for n > 128.
+  // k7 wins where a pair has many units to stream (C3: 494 us for the q path against 558 us for the single-CTA streaming kernel
+  // it replaced); with one or two units per pair (decode) its longer dependency chain loses to k4 (C2: 33 vs 27 us), so it runs
+  // only when units outnumber the SMs.  Debug bit13 forces it for n > 128 (parity tests).
   const bool many_units = n > 256 && q_units > num_sms();
-  if (((many_units && !(g_debug_flags & 128)) || ((g_debug_flags & 8192) && n > kBlockM))) {  // bit7: keep k6 for A/B comparisons
+  if (many_units || ((g_debug_flags & 8192) && n > kBlockM)) {
     // ---- k7: CTA pairs.  Each CTA of a pair owns one 128-token tile and half of the head's weight rows.
     int rcx;
     CUtensorMap tm_a1p, tm_wuqp;
@@ -455,22 +414,6 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     }
     MLAPO_CHECK_LAUNCH("q_pair");
     g_kernel_names[3] = "q_pair";
-  } else if (n > 256 && q_units > num_sms() && !(g_debug_flags & 64)) {  // bit6: keep k4 for A/B comparisons
-    int rcx;
-    CUtensorMap tm_a1s;  // the streaming kernel always fetches both token tiles of a unit in one box
-    if ((rcx = make_tmap(&tm_a1s, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a1, n, MLAPO_Q_LORA, MLAPO_Q_LORA, 2 * kBlockM, 128))) return rcx;
-    dim3 grid(num_sms() < q_units ? num_sms() : q_units);
-    if (int8_out) {
-      static DoneFlag done[kMaxDevices];
-      if ((rc = set_smem_attr(q_stream_kernel<T, true>, kSSmemBytes, &done[dev], "q_stream<int8>"))) return rc;
-      e__ = launch_k(q_stream_kernel<T, true>, grid, dim3(kSThreads), kSSmemBytes, st, pdl, tm_a1s, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, q_units, tl4);
-    } else {
-      static DoneFlag done[kMaxDevices];
-      if ((rc = set_smem_attr(q_stream_kernel<T, false>, kSSmemBytes, &done[dev], "q_stream"))) return rc;
-      e__ = launch_k(q_stream_kernel<T, false>, grid, dim3(kSThreads), kSSmemBytes, st, pdl, tm_a1s, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, q_units, tl4);
-    }
-    MLAPO_CHECK_LAUNCH("q_stream");
-    g_kernel_names[3] = "q_stream";
   } else {
     g_kernel_names[3] = "q_fused";
     dim3 grid(h, q_tok_tiles);
@@ -622,7 +565,7 @@ int mlapo_get_workspace_size(const MlapoParams* p, size_t* bytes) {
 int mlapo_launches_per_call(const MlapoParams* p) {
   snapshot_debug_flags();
   if (check_params(p)) return 0;
-  return decode_persistent_eligible(p, choose_splits0(p->num_tokens, p->hidden_dim)) ? 1 : 4;
+  return 4;
 }
 
 int batch_matmul_transpose_launch(const void* a, const void* b, void* c, int64_t m, int64_t batch, int64_t k, int64_t n,

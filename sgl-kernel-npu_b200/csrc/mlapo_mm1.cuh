@@ -16,9 +16,9 @@ namespace mlapo {
 // ============================================================================================ k2: MM1 (W_DQKV), split-K
 // acc[MT*128 tokens x 128] (int32, TMEM) = a0[tokens x Kslice] (int8, K-major) . Wdqkv[128 rows x Kslice]^T (int8, K-major).
 // grid = (n_tiles=17, splits, token super-tiles of MT*128).  One CTA streams its weight tile once for all MT token tiles.
-// 6 warps: w0 = TMA producer, w1 = tcgen05.mma issuer (+TMEM alloc), w2..w5 = epilogue (TMEM lane quarter = warp%4).
+// 10 warps: w0 = TMA producer, w1 = tcgen05.mma issuer (+TMEM alloc), w2..w9 = two epilogue groups (TMEM lane quarter = warp%4).
 // Weight (B) tiles do not depend on the upstream kernel, so they are requested before griddepcontrol.wait (PDL).
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;
 constexpr int kBlockM = 128;
 constexpr int kBlockKBytes = 128;  // one 128B swizzle atom along K
 constexpr int kUmmaKBytes = 32;    // K per tcgen05.mma for 8-bit (32 elems) and 16-bit (16 elems) operands
@@ -92,10 +92,10 @@ __device__ __forceinline__ void mm1_issue_weights(const Mm1Ctx<MT, BN>& c, const
   }
 }
 
-// Warp roles of MM1: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer, warps 2..5 = epilogue (TMEM lane quarter = warp%4);
-// other warps fall through.  The caller has already issued mm1_issue_weights().  kStandalone: own kernel under PDL, the
-// producer waits for the upstream kernel before it touches a0; otherwise the caller guarantees a0 is complete.
-template <int MT, int BN, bool kStandalone, bool kDequant = false, class T = __nv_bfloat16>
+// Warp roles of MM1: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer, warps 2..9 = epilogue (TMEM lane quarter = warp%4);
+// other warps fall through.  The caller has already issued mm1_issue_weights(); under programmatic dependent launch the producer
+// waits for the upstream kernel before it touches a0.
+template <int MT, int BN, bool kDequant = false, class T = __nv_bfloat16>
 __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtensorMap* tm_a, const CUtensorMap* tm_b,
                                           const CUtensorMap* tm_p, int warp, int lane, long long* tl,
                                           const CUtensorMap* tm_y = nullptr, const int2* s_cst = nullptr,
@@ -114,10 +114,8 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
     if (lane == 0) {
       const uint32_t stage_tx = (uint32_t)(mt_valid * kTile16K + B_BYTES);
       const int pre = nkb < STAGES ? nkb : STAGES;
-      if (kStandalone) {
-        ptx::griddep_wait();  // a0 is produced by the quantise kernel (the weight tiles were requested at kernel start)
-        tl_mark(tl, 3);       // upstream complete
-      }
+      ptx::griddep_wait();  // a0 is produced by the quantise kernel (the weight tiles were requested at kernel start)
+      tl_mark(tl, 3);       // upstream complete
       for (int i = 0; i < pre; ++i) {
         const uint32_t fb = ptx::smem_u32(full_bar + i);
         for (int m = 0; m < mt_valid; ++m)
@@ -164,64 +162,72 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
     }
     if (lane == 0) ptx::umma_commit(ptx::smem_u32(done_bar));
     __syncwarp();
-  } else if (warp < 6) {
+  } else if (warp < 10) {
     // ------------------------------------------------------------------ epilogue: TMEM -> swizzled smem -> TMA store
-    const int quarter = warp & 3;
+    // Two groups of four warps (a warp reads the TMEM lane quarter warp % 4).  With two valid token tiles each group drains one;
+    // with one, each drains half of its column granules.  Every granule tile is handed to the TMA store engine as soon as its 128
+    // rows are written, so the stores of one granule run under the TMEM reads of the next.
+    const int quarter = warp & 3, group = (warp - 2) >> 2;
     const int row = quarter * 32 + lane;
     const uint32_t t_base = tmem_acc + ((uint32_t)(quarter * 32) << 16);
-    const bool issuer = threadIdx.x == 64;
+    const bool issuer = threadIdx.x == 64 + group * 128;
+    const int bar_id = 1 + group;
+    constexpr int kGroupBytes = STAGES * STAGE_BYTES / 2 / kTile16K * kTile16K;  // each group stages in its half of the drained pipeline
+    constexpr int TPG = kGroupBytes / kTile16K;                                    // staging tiles per group
+    uint8_t* const stg = smem + group * kGroupBytes;
     ptx::mbar_wait(ptx::smem_u32(done_bar), 0);   // all MMAs retired => every pipeline stage has been consumed
     __syncwarp();
     ptx::tc_fence_after();
-    if (issuer) tl_mark(tl, 6);  // MMAs retired
+    if (issuer && group == 0) tl_mark(tl, 6);  // MMAs retired
     __syncwarp();                                 // tcgen05.ld below is warp-aligned: reconverge after the one-lane branch
-    // each token tile gets its own staging tiles when the drained pipeline is large enough for all of them (decode shape);
-    // otherwise the tiles are re-used and the previous token tile's stores must have been read first
-    constexpr bool kOwnStaging = MT * GRANULES * kTile16K <= STAGES * STAGE_BYTES;
+    const bool two = mt_valid > 1;
+    const int m_lo = two ? group : 0, m_hi = two ? group + 1 : 1;
+    int used = 0;  // staging tiles this group has handed to the store engine so far
+    auto tile_acquire = [&]() -> uint8_t* {   // the tile's previous store (TPG tiles ago) has been read out of shared memory
+      if (used >= TPG) {
+        if (issuer) ptx::tma_store_wait_read<TPG - 1>();
+        ptx::named_bar_sync(bar_id, 128);
+      }
+      return stg + (used % TPG) * kTile16K;
+    };
     bool raw = true;  // store the int32 accumulators (always in the split-K form; only as a debug tap in the dequantising form)
     if constexpr (kDequant) raw = dq->tap_acc != 0;
-    for (int m = 0; raw && m < mt_valid; ++m) {
-      if (m > 0 && !kOwnStaging) {
-        if (issuer) ptx::tma_store_wait_read<0>();
-        ptx::named_bar_sync(1, 128);
-      }
-      uint8_t* const stg = smem + (kOwnStaging ? m * GRANULES * kTile16K : 0);
+    if (raw) {
+      const int g_lo = two ? 0 : group * (GRANULES / 2), g_hi = two ? GRANULES : (group + 1) * (GRANULES / 2);
+      for (int m = m_lo; m < m_hi; ++m) {
 #pragma unroll 1
-      for (int g = 0; g < GRANULES; ++g) {
-        uint32_t r[32];
-        ptx::tmem_ld_32x32b_x32(t_base + m * BN + g * 32, r);
-        ptx::tmem_ld_wait();
-        const uint32_t tile = ptx::smem_u32(stg + g * kTile16K);
+        for (int g = g_lo; g < g_hi; ++g) {
+          uint32_t r[32];
+          ptx::tmem_ld_32x32b_x32(t_base + m * BN + g * 32, r);
+          uint8_t* const tile_p = tile_acquire();
+          ptx::tmem_ld_wait();
+          const uint32_t tile = ptx::smem_u32(tile_p);
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          ptx::st_shared_v4(tile + ptx::sw128_offset(row, j), r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
-      }
-      ptx::fence_proxy_async_smem();
-      ptx::named_bar_sync(1, 128);
-      if (issuer) {
-        for (int g = 0; g < GRANULES; ++g)
-          if (n0 + g * 32 < MLAPO_MM1_OUT)
-            ptx::tma_store_3d(tm_p, ptx::smem_u32(stg + g * kTile16K), n0 + g * 32, m0 + m * kBlockM, split);
-        ptx::tma_store_commit();
+          for (int j = 0; j < 8; ++j)
+            ptx::st_shared_v4(tile + ptx::sw128_offset(row, j), r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+          ptx::fence_proxy_async_smem();
+          ptx::named_bar_sync(bar_id, 128);
+          if (issuer) {
+            if (n0 + g * 32 < MLAPO_MM1_OUT) ptx::tma_store_3d(tm_p, tile, n0 + g * 32, m0 + m * kBlockM, split);
+            ptx::tma_store_commit();
+          }
+          ++used;
+        }
       }
     }
     if constexpr (kDequant) {
       // ---- dequantise in the epilogue: TMEM -> (+bias) * descale -> act -> swizzled smem -> TMA store into y0 [N, 2112]
       constexpr int G64 = BN / 64;  // 64 act columns = one 128-byte row per token
-      static_assert(MT * G64 * kTile16K <= STAGES * STAGE_BYTES, "every token tile has its own staging tiles");
-      if (raw) {  // the tap's stores still read the staging tiles
-        if (issuer) ptx::tma_store_wait_read<0>();
-        ptx::named_bar_sync(1, 128);
-      }
-      for (int m = 0; m < mt_valid; ++m) {
+      const int g_lo = two ? 0 : group * (G64 / 2), g_hi = two ? G64 : (group + 1) * (G64 / 2);
+      for (int m = m_lo; m < m_hi; ++m) {
         const int t = m0 + m * kBlockM + row;
         const float ts = dq->tok_scale0 ? dq->tok_scale0[t < c.m_total ? t : c.m_total - 1] : 1.f;
-        uint8_t* const stg = smem + m * G64 * kTile16K;
 #pragma unroll 1
-        for (int g = 0; g < G64; ++g) {
+        for (int g = g_lo; g < g_hi; ++g) {
           uint32_t ra[32], rb[32];
           ptx::tmem_ld_32x32b_x32(t_base + m * BN + g * 64, ra);
           ptx::tmem_ld_32x32b_x32(t_base + m * BN + g * 64 + 32, rb);
+          uint8_t* const tile_p = tile_acquire();
           ptx::tmem_ld_wait();
           uint32_t w[32];
 #pragma unroll
@@ -236,20 +242,24 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
             w[j] = Act<T>::pack(a0, a1);
             w[16 + j] = Act<T>::pack(b0, b1);
           }
-          const uint32_t tile = ptx::smem_u32(stg + g * kTile16K);
+          const uint32_t tile = ptx::smem_u32(tile_p);
 #pragma unroll
           for (int j = 0; j < 8; ++j) ptx::st_shared_v4(tile + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
-        }
-        ptx::fence_proxy_async_smem();
-        ptx::named_bar_sync(1, 128);
-        if (issuer) {
-          for (int g = 0; g < G64; ++g)
-            if (n0 + g * 64 < MLAPO_MM1_OUT) ptx::tma_store_2d(tm_y, ptx::smem_u32(stg + g * kTile16K), n0 + g * 64, m0 + m * kBlockM);
-          ptx::tma_store_commit();
+          ptx::fence_proxy_async_smem();
+          ptx::named_bar_sync(bar_id, 128);
+          if (issuer) {
+            if (n0 + g * 64 < MLAPO_MM1_OUT) ptx::tma_store_2d(tm_y, tile, n0 + g * 64, m0 + m * kBlockM);
+            ptx::tma_store_commit();
+          }
+          ++used;
         }
       }
     }
-    if (issuer) { tl_mark(tl, 7); ptx::tma_store_wait_read<0>(); tl_mark(tl, 8); }
+    if (issuer) {
+      if (group == 0) tl_mark(tl, 7);
+      ptx::tma_store_wait_read<0>();
+      if (group == 0) tl_mark(tl, 8);
+    }
   }
 
 }
@@ -297,7 +307,7 @@ mm1_dequant_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
   ptx::griddep_launch_dependents();
   if (threadIdx.x == 0) tl_mark(tl, 2);  // prologue done
 
-  mm1_roles<MT, BN, true, true, T>(c, &tm_a, &tm_b, &tm_p, warp, lane, tl, &tm_y, s_cst, &dq);
+  mm1_roles<MT, BN, true, T>(c, &tm_a, &tm_b, &tm_p, warp, lane, tl, &tm_y, s_cst, &dq);
 
   ptx::tc_fence_before();
   __syncthreads();
@@ -338,7 +348,7 @@ mm1_splitk_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constan
   ptx::griddep_launch_dependents();
   if (threadIdx.x == 0) tl_mark(tl, 2);  // prologue done
 
-  mm1_roles<MT, BN, true>(c, &tm_a, &tm_b, &tm_p, warp, lane, tl);
+  mm1_roles<MT, BN>(c, &tm_a, &tm_b, &tm_p, warp, lane, tl);
 
   ptx::tc_fence_before();
   __syncthreads();

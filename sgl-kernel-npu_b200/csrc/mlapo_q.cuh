@@ -1,4 +1,4 @@
-// k4 / k6 the q path: MM2 (int8) -> dequant -> RoPE -> W_UK absorb (bf16/fp16), one CTA per unit (k4) or streaming (k6).
+// k4 the q path: MM2 (int8) -> dequant -> RoPE -> W_UK absorb (bf16/fp16), one CTA per (head, up to 256 tokens).
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -33,8 +33,12 @@ constexpr int kQNopeOff = 4 * 32768;                        // 4 x 16 KB: (m, kb
 constexpr int kQStageOff = kQNopeOff + 4 * kTile16K;        // 2 x 16 KB output staging (one per epilogue group)
 constexpr int kQBarOff = kQStages * kQStageBytes;           // 229376
 static_assert(kQStageOff + 2 * kTile16K == kQBarOff, "smem regions must tile the pipeline exactly");
-constexpr int kQSmemBytes = kQBarOff + 256 + MLAPO_Q_HEAD * 8 + 1024;
-static_assert(kQSmemBytes <= 232448, "q_fused smem");
+// No slack for aligning the base: the kernel has no static shared memory, its dynamic region is declared 1024-byte aligned and
+// starts right behind the 1 KB the system reserves per CTA (checked at run time).  That leaves 1.25 KB of the SM's 228 KB free,
+// exactly what lets ONE block of the next call's quantise kernel (no shared memory of its own, 1 KB reserved) share the SM with
+// a q CTA — so the quantiser runs while the q kernel is still busy instead of queueing for its SMs.
+constexpr int kQSmemBytes = kQBarOff + 256 + MLAPO_Q_HEAD * 8;
+static_assert(kQSmemBytes + 1024 + 1024 <= 233472, "q_fused CTA + one quantise block per SM");
 constexpr int kQKBlocks = MLAPO_Q_LORA / kBlockKBytes;      // 12
 
 struct QArgs {
@@ -91,9 +95,9 @@ __device__ __forceinline__ void q_issue_weights(const QCtx& c, const CUtensorMap
 }
 
 // Warp roles of the q path: warp 0 = TMA producer, warp 1 = MMA issuer, warps 2..5 / 6..9 = epilogue groups of token tile 0 / 1.
-// The caller has already issued q_issue_weights().  kStandalone: own kernel under PDL (waits for the upstream kernel
-// before touching a1 / the per-token scales); otherwise the caller guarantees they are complete.
-template <class T, bool kInt8Out, bool kStandalone>
+// The caller has already issued q_issue_weights().  Under programmatic dependent launch the roles wait for the upstream kernel
+// before touching a1 / the per-token scales.
+template <class T, bool kInt8Out>
 __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1, const CUtensorMap* tm_wuq, const CUtensorMap* tm_wuk,
                                         const CUtensorMap* tm_out0, const CUtensorMap* tm_out1, const QArgs& qa, int warp, int lane,
                                         long long* tl) {
@@ -123,10 +127,8 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
         ptx::tma_load_2d(ptx::smem_u32(smem + s * kQStageBytes), tm_a1, ptx::smem_u32(full_bar + s), kb * kBlockKBytes, tok0,
                          ptx::kEvictLast);
       };
-      if (kStandalone) {
-        ptx::griddep_wait();  // a1 is produced by the norm kernel (the first W_UQ k-blocks were requested at kernel start)
-        tl_mark(tl, 3);
-      }
+      ptx::griddep_wait();  // a1 is produced by the norm kernel (the first W_UQ k-blocks were requested at kernel start)
+      tl_mark(tl, 3);
       for (int kb = 0; kb < kQStages; ++kb) load_a(kb);
       for (int kb = kQStages; kb < kQKBlocks; ++kb) {
         const int s = kb & 3;
@@ -233,12 +235,10 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
         s_cst[c] = make_int2(qa.bias1 ? qa.bias1[head * MLAPO_Q_HEAD + c] : 0, __float_as_int(dsc));
       }
     }
-    if (kStandalone) {
-      ptx::griddep_wait();  // tok_scale1 comes from the norm kernel (and keeps the PDL completion chain transitive)
-      // dependents (the next call's quantise kernel, which stores to a0 without waiting) are signalled only now: the norm kernel, and
-      // with it this call's MM1, the last reader of a0, are complete
-      ptx::griddep_launch_dependents();
-    }
+    ptx::griddep_wait();  // tok_scale1 comes from the norm kernel (and keeps the PDL completion chain transitive)
+    // dependents (the next call's quantise kernel, which may store to a0 without waiting) are signalled only now: the norm kernel,
+    // and with it this call's MM1, the last reader of a0, are complete
+    ptx::griddep_launch_dependents();
     ptx::named_bar_sync(3, 256);
 
     if (g < num_mt) {
@@ -442,9 +442,10 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
                const __grid_constant__ CUtensorMap tm_wuk, const __grid_constant__ CUtensorMap tm_out0,
                const __grid_constant__ CUtensorMap tm_out1, QArgs qa, long long* tl) {
   if (threadIdx.x == 0) { tl_mark_global(tl, 0); tl_mark(tl, 1); }
-  extern __shared__ uint8_t smem_raw[];
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
   QCtx c;
-  c.smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  c.smem = smem_raw;
+  if ((ptx::smem_u32(smem_raw) & 1023u) != 0) __trap();  // the 128-byte swizzle needs 1024-byte aligned tiles
   c.bars = reinterpret_cast<uint64_t*>(c.smem + kQBarOff);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(c.bars + 26);
   c.s_cst = reinterpret_cast<int2*>(c.smem + kQBarOff + 256);
@@ -476,397 +477,12 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
     tl[(blockIdx.x + gridDim.x * blockIdx.y) * 16 + 13] = smid;
   }
 
-  q_roles<T, kInt8Out, true>(c, &tm_a1, &tm_wuq, &tm_wuk, &tm_out0, &tm_out1, qa, warp, lane, tl);
+  q_roles<T, kInt8Out>(c, &tm_a1, &tm_wuq, &tm_wuk, &tm_out0, &tm_out1, qa, warp, lane, tl);
 
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 1) ptx::tmem_dealloc(c.tmem, 512);
   if (threadIdx.x == 32) { tl_mark(tl, 12); tl_mark_global(tl, 15); }
-}
-
-// ============================================================================================ k6: q path, streaming form (prefill)
-// Same arithmetic as k4, re-shaped for calls with many more (head, 256-token) units than SMs: persistent CTAs walk a list
-// of units and the phases of consecutive units overlap —  MM2 of unit i+1 (TMA + int8 MMAs) runs while unit i is being
-// absorbed, drained and stored.  That needs the MM2 pipeline, the q_nope tile, the W_UK chunks and the output staging to
-// live in DISJOINT shared memory, and separate issuing threads for the two MMA streams and the two TMA streams:
-//   w0  TMA: a1 + W_UQ k-blocks (2 stages x 56 KB)          w10 TMA: W_UK 64-column chunks (3 slots x 16 KB)
-//   w1  MMA: MM2 (kind::i8, acc2[m] = TMEM [256m, 256m+192)) w11 MMA: absorb (kind::f16, N=64, buffers TMEM [192,256), [448,512))
-//   w2..w5 / w6..w9: epilogue group of token tile 0 / 1 (dequant, RoPE -> q_out1, q_nope -> smem, drains -> q_out0)
-// The q_nope smem tile is single (32 KB): token tile 0 is absorbed first, then tile 1 re-uses the bytes, so every W_UK
-// chunk is fetched twice per unit (L2 hits).  Units are ordered head-major: a CTA's next unit is the same or the next head.
-constexpr int kSThreads = 384;
-constexpr int kSStages = 2;
-constexpr int kSWukSlots = 3;
-constexpr int kSNopeOff = kSStages * kQStageBytes;              // 114688: 2 x 16 KB (k-block 0 / 1 of one token tile)
-constexpr int kSWukOff = kSNopeOff + 2 * kTile16K;              // 147456: 3 x 16 KB
-constexpr int kSStageOff = kSWukOff + kSWukSlots * kTile16K;    // 196608: 2 x 16 KB, one per epilogue group
-constexpr int kSBarOff = kSStageOff + 2 * kTile16K;             // 229376
-constexpr int kSSmemBytes = kSBarOff + 256 + MLAPO_Q_HEAD * 8 + 1024;
-static_assert(kSSmemBytes <= 232448, "q_stream smem");
-
-template <class T, bool kInt8Out>
-__global__ void __launch_bounds__(kSThreads, 1)
-q_stream_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__ CUtensorMap tm_wuq,
-                const __grid_constant__ CUtensorMap tm_wuk, const __grid_constant__ CUtensorMap tm_out0,
-                const __grid_constant__ CUtensorMap tm_out1, QArgs qa, int total_units, long long* tl) {
-  if (threadIdx.x == 0) { tl_mark_global(tl, 0); tl_mark(tl, 1); }
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSBarOff);
-  uint64_t* full_bar = bars;           // [2]  TMA -> MM2
-  uint64_t* empty_bar = bars + 2;      // [2]  MM2 -> TMA
-  uint64_t* mm2_done = bars + 4;       // [1]  MM2 -> epilogue groups
-  uint64_t* acc2_free = bars + 5;      // [1]  both epilogue groups (256 threads) -> MM2: acc2 of the previous unit drained
-  uint64_t* qn_ready = bars + 6;       // [2]  epilogue group m -> absorb: q_nope tile of token tile m is in smem
-  uint64_t* qn_free = bars + 8;        // [1]  absorb -> epilogue: the q_nope tile has been consumed (twice per unit)
-  uint64_t* wuk_full = bars + 9;       // [3]  TMA -> absorb
-  uint64_t* wuk_empty = bars + 12;     // [3]  absorb -> TMA
-  uint64_t* unit_full = bars + 15;     // [2]  absorb -> draining epilogue group
-  uint64_t* abuf_empty = bars + 17;    // [2]  draining epilogue group (128 threads) -> absorb
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
-  int2* s_cst = reinterpret_cast<int2*>(smem + kSBarOff + 256);  // per column {bias, descale bits} of the current head
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // units are walked head-major: the CTAs running at any moment share ~5 heads' weights (always L2-hot) and a1 (12.6 MB)
-  const int n_st = (qa.m_total + 255) / 256;
-
-  if (warp == 0 && lane == 0) {
-    ptx::prefetch_tmap(&tm_a1);
-    ptx::prefetch_tmap(&tm_wuq);
-    ptx::prefetch_tmap(&tm_wuk);
-    ptx::prefetch_tmap(&tm_out0);
-    ptx::prefetch_tmap(&tm_out1);
-    for (int i = 0; i < 19; ++i) {
-      const uint32_t cnt = i == 5 ? 256u : (i == 6 || i == 7 || i == 17 || i == 18) ? 128u : 1u;
-      ptx::mbar_init(ptx::smem_u32(bars + i), cnt);
-    }
-    ptx::fence_mbar_init();
-  }
-  if (warp == 1) {
-    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
-    ptx::tmem_relinquish();
-  }
-  ptx::tc_fence_before();
-  __syncthreads();
-  ptx::tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-
-  if (warp == 0) {
-    // ------------------------------------------------------------------ TMA: a1 + W_UQ k-blocks
-    if (lane == 0) {
-      ptx::griddep_wait();  // a1 is produced by the norm kernel
-      constexpr uint32_t stage_tx = 2 * kTile16K + MLAPO_Q_HEAD * kBlockKBytes;
-      uint32_t gk = 0;
-      for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-        const int head = u / n_st, tok0 = (u % n_st) * 256;
-        for (int kb = 0; kb < kQKBlocks; ++kb, ++gk) {
-          const uint32_t s = gk & 1;
-          if (gk >= kSStages) ptx::mbar_wait(ptx::smem_u32(empty_bar + s), ((gk >> 1) & 1) ^ 1);
-          const uint32_t fb = ptx::smem_u32(full_bar + s);
-          ptx::mbar_arrive_expect_tx(fb, stage_tx);
-          ptx::tma_load_2d(ptx::smem_u32(smem + s * kQStageBytes + 2 * kTile16K), &tm_wuq, fb, kb * kBlockKBytes, head * MLAPO_Q_HEAD,
-                           ptx::kEvictLast);
-          ptx::tma_load_2d(ptx::smem_u32(smem + s * kQStageBytes), &tm_a1, fb, kb * kBlockKBytes, tok0, ptx::kEvictLast);
-        }
-      }
-    }
-  } else if (warp == 10) {
-    // ------------------------------------------------------------------ TMA: W_UK chunks (each twice per unit: tile 0, then tile 1)
-    if (lane == 0) {
-      uint32_t gc = 0;
-      for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-        const int head = u / n_st;
-        for (int j = 0; j < 16; ++j, ++gc) {
-          const uint32_t w = gc % kSWukSlots, use = gc / kSWukSlots;
-          if (use >= 1) ptx::mbar_wait(ptx::smem_u32(wuk_empty + w), (use & 1) ^ 1);
-          const uint32_t fb = ptx::smem_u32(wuk_full + w);
-          ptx::mbar_arrive_expect_tx(fb, kTile16K);
-          ptx::tma_load_2d(ptx::smem_u32(smem + kSWukOff + w * kTile16K), &tm_wuk, fb, (j & 7) * 64, head * MLAPO_Q_NOPE, ptx::kEvictLast);
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA: MM2
-    constexpr uint32_t idesc2 = ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, kBlockM, MLAPO_Q_HEAD);
-    uint32_t gk = 0, it = 0;
-    for (int u = blockIdx.x; u < total_units; u += gridDim.x, ++it) {
-      if (it > 0) ptx::mbar_wait(ptx::smem_u32(acc2_free), (it - 1) & 1);  // the previous unit's accumulators have been read
-      for (int kb = 0; kb < kQKBlocks; ++kb, ++gk) {
-        const uint32_t s = gk & 1;
-        ptx::mbar_wait(ptx::smem_u32(full_bar + s), (gk >> 1) & 1);
-        __syncwarp();
-        ptx::tc_fence_after();
-        if (lane == 0) {
-          const uint32_t a_base = ptx::smem_u32(smem + s * kQStageBytes);
-          const uint32_t b_base = a_base + 2 * kTile16K;
-#pragma unroll
-          for (int m = 0; m < 2; ++m) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const uint64_t da = ptx::make_smem_desc(a_base + m * kTile16K + k * kUmmaKBytes, 1024, 0);
-              const uint64_t db = ptx::make_smem_desc(b_base + k * kUmmaKBytes, 1024, 0);
-              ptx::umma_i8(tmem + m * 256, da, db, idesc2, (kb > 0 || k > 0) ? 1u : 0u);
-            }
-          }
-          ptx::umma_commit(ptx::smem_u32(empty_bar + s));
-        }
-        __syncwarp();
-      }
-      if (lane == 0) ptx::umma_commit(ptx::smem_u32(mm2_done));
-      __syncwarp();
-    }
-  } else if (warp == 11) {
-    // ------------------------------------------------------------------ MMA: absorb, 64 output columns per unit of work
-    constexpr uint32_t kAFmt = std::is_same<T, __nv_bfloat16>::value ? ptx::kFmtBF16 : ptx::kFmtF16;
-    constexpr uint32_t idesc3 = ptx::make_idesc(ptx::kCFmtF32, kAFmt, kAFmt, 0, 1, kBlockM, 64);
-    uint32_t gc = 0, it = 0;
-    for (int u = blockIdx.x; u < total_units; u += gridDim.x, ++it) {
-      for (int m = 0; m < 2; ++m) {
-        ptx::mbar_wait(ptx::smem_u32(qn_ready + m), it & 1);
-        for (int c = 0; c < 8; ++c, ++gc) {
-          const uint32_t w = gc % kSWukSlots, b = gc & 1;
-          ptx::mbar_wait(ptx::smem_u32(wuk_full + w), (gc / kSWukSlots) & 1);
-          if (gc >= 2) ptx::mbar_wait(ptx::smem_u32(abuf_empty + b), ((gc >> 1) - 1) & 1);
-          __syncwarp();
-          ptx::tc_fence_after();
-          if (lane == 0) {
-            const uint32_t b_base = ptx::smem_u32(smem + kSWukOff + w * kTile16K);
-            const uint32_t d_col = tmem + (b ? 448u : 192u);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {  // 8 x UMMA_K(16) = 128
-              const uint32_t a_addr = ptx::smem_u32(smem + kSNopeOff + (k >> 2) * kTile16K) + (k & 3) * kUmmaKBytes;
-              const uint64_t da = ptx::make_smem_desc(a_addr, 1024, 0);
-              const uint64_t db = ptx::make_smem_desc(b_base + k * 2048, 1024, 0);  // MN-major, one 64-column atom
-              ptx::umma_f16(d_col, da, db, idesc3, k > 0 ? 1u : 0u);
-            }
-            ptx::umma_commit(ptx::smem_u32(wuk_empty + w));
-            ptx::umma_commit(ptx::smem_u32(unit_full + b));
-          }
-          __syncwarp();
-        }
-        if (lane == 0) ptx::umma_commit(ptx::smem_u32(qn_free));  // every MMA that reads this q_nope tile has retired
-        __syncwarp();
-      }
-    }
-  } else {
-    // ------------------------------------------------------------------ epilogue groups (thread = token row of tile g)
-    const int g = (warp - 2) >> 2;
-    const int quarter = warp & 3;
-    const int row = quarter * 32 + lane;
-    const int et = threadIdx.x - 64 - g * 128;
-    const bool issuer = et == 0;
-    const int bar_id = 1 + g;
-    const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
-    const uint32_t st_tile = ptx::smem_u32(smem + kSStageOff + g * kTile16K);
-    const bool per_token = qa.tok_scale1 != nullptr;
-    auto stage_acquire = [&]() {
-      if (issuer) ptx::tma_store_wait_read<0>();
-      ptx::named_bar_sync(bar_id, 128);
-    };
-    auto stage_publish = [&]() {
-      ptx::fence_proxy_async_smem();
-      ptx::named_bar_sync(bar_id, 128);
-    };
-    ptx::griddep_wait();  // per-token scales come from the norm kernel
-    ptx::griddep_launch_dependents();  // only after the wait: see q_fused
-
-    uint32_t it = 0;
-    for (int u = blockIdx.x; u < total_units; u += gridDim.x, ++it) {
-      const int head = u / n_st, tok0 = (u % n_st) * 256;
-      const int t = tok0 + g * kBlockM + row;
-      const int tc = t < qa.m_total ? t : qa.m_total - 1;  // clamped row for loads; TMA stores clip rows >= N
-      // per-column constants of this head.  Both groups meet here first: nobody may still be dequantising the previous
-      // unit with the old constants (free in steady state: the next MM2 needs far longer than the other group's drains).
-      ptx::named_bar_sync(3, 256);
-      if (g == 0) {
-        for (int c = et; c < MLAPO_Q_HEAD; c += 128) {
-          const float dsc = load_descale(qa.descale1, qa.descale_is_i64, head * MLAPO_Q_HEAD + c);
-          s_cst[c] = make_int2(qa.bias1 ? qa.bias1[head * MLAPO_Q_HEAD + c] : 0, __float_as_int(dsc));
-        }
-      }
-      const float ts = per_token ? qa.tok_scale1[tc] : 1.f;
-      uint4 cs[8], sn[8];
-      {
-        const uint4* cp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(qa.cos) + (long long)tc * 64);
-        const uint4* sp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(qa.sin) + (long long)tc * 64);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { cs[j] = ptx::ld_global_nc_v4(cp + j); sn[j] = ptx::ld_global_nc_v4(sp + j); }
-      }
-      ptx::named_bar_sync(3, 256);  // constants visible to both groups
-      // y = fp32(acc + bias) * descale * token scale for columns c, c+1 (c even): the per-tensor mode carries a token scale of 1
-      // (x * 1.0f is exact), the per-token mode a bias of 0, so one expression serves both; one 16-byte load brings both columns'
-      // constants
-      auto deq2 = [&](uint32_t acc0, uint32_t acc1, int c, float& f0, float& f1) {
-        const int4 cst = *reinterpret_cast<const int4*>(s_cst + c);
-        f0 = __fmul_rn(__fmul_rn(__int2float_rn((int)acc0 + cst.x), __int_as_float(cst.y)), ts);
-        f1 = __fmul_rn(__fmul_rn(__int2float_rn((int)acc1 + cst.z), __int_as_float(cst.w)), ts);
-      };
-
-      ptx::mbar_wait(ptx::smem_u32(mm2_done), it & 1);
-      __syncwarp();
-      ptx::tc_fence_after();
-      if (issuer && g == 0 && it < 4) tl_mark(tl, 2 + 3 * it);   // debug timeline: MM2 of unit `it` retired
-      const uint32_t acc2 = lane_base + g * 256;
-
-      // rope slice first (columns 128..191): it needs no shared q_nope bytes, so tile 1 does it while tile 0 is absorbed
-      float x[64];
-      {
-        uint32_t ra[32], rb[32];
-        ptx::tmem_ld_32x32b_x32(acc2 + 128, ra);
-        ptx::tmem_ld_32x32b_x32(acc2 + 160, rb);
-        ptx::tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; j += 2) {
-          deq2(ra[j], ra[j + 1], 128 + j, x[j], x[j + 1]);
-          x[j] = Act<T>::round(x[j]);
-          x[j + 1] = Act<T>::round(x[j + 1]);
-        }
-#pragma unroll
-        for (int j = 0; j < 32; j += 2) {
-          deq2(rb[j], rb[j + 1], 160 + j, x[32 + j], x[33 + j]);
-          x[32 + j] = Act<T>::round(x[32 + j]);
-          x[33 + j] = Act<T>::round(x[33 + j]);
-        }
-      }
-      stage_acquire();
-#pragma unroll
-      for (int gg = 0; gg < 4; ++gg) {
-        float c_lo[8], s_lo[8], c_hi[8], s_hi[8];
-        unpack8<T>(cs[gg], c_lo);
-        unpack8<T>(sn[gg], s_lo);
-        unpack8<T>(cs[gg + 4], c_hi);
-        unpack8<T>(sn[gg + 4], s_hi);
-        uint32_t wl[4], wh[4];
-#pragma unroll
-        for (int v = 0; v < 4; ++v) {
-          const int i0 = gg * 8 + 2 * v, i1 = i0 + 1;
-          // out[i] = x[i]*cos[i] + (-x[i+32])*sin[i];  out[i+32] = x[i+32]*cos[i+32] + x[i]*sin[i+32]   (test_mla:57-67)
-          const float a0 = __fadd_rn(__fmul_rn(x[i0], c_lo[2 * v]), __fmul_rn(-x[i0 + 32], s_lo[2 * v]));
-          const float a1 = __fadd_rn(__fmul_rn(x[i1], c_lo[2 * v + 1]), __fmul_rn(-x[i1 + 32], s_lo[2 * v + 1]));
-          const float b0 = __fadd_rn(__fmul_rn(x[i0 + 32], c_hi[2 * v]), __fmul_rn(x[i0], s_hi[2 * v]));
-          const float b1 = __fadd_rn(__fmul_rn(x[i1 + 32], c_hi[2 * v + 1]), __fmul_rn(x[i1], s_hi[2 * v + 1]));
-          wl[v] = Act<T>::pack(a0, a1);
-          wh[v] = Act<T>::pack(b0, b1);
-        }
-        ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, gg), wl[0], wl[1], wl[2], wl[3]);
-        ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, gg + 4), wh[0], wh[1], wh[2], wh[3]);
-      }
-      stage_publish();
-      if (issuer) {
-        ptx::tma_store_2d(&tm_out1, st_tile, head * MLAPO_ROPE, tok0 + g * kBlockM);
-        ptx::tma_store_commit();
-      }
-
-      // nope slice: dequantised and packed in registers first, so that acc2[g] is released to the next unit's MM2 without
-      // waiting for the shared q_nope tile
-      uint32_t wn[64];
-      {
-        auto nope_chunk = [&](const uint32_t (&r)[32], int c0) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            float f0, f1;
-            deq2(r[2 * j], r[2 * j + 1], c0 + 2 * j, f0, f1);
-            wn[(c0 >> 1) + j] = Act<T>::pack(f0, f1);
-          }
-        };
-        uint32_t ra[32], rb[32];
-        ptx::tmem_ld_32x32b_x32(acc2 + 0, ra);
-        ptx::tmem_ld_wait();
-        ptx::tmem_ld_32x32b_x32(acc2 + 32, rb);
-        nope_chunk(ra, 0);
-        ptx::tmem_ld_wait();
-        ptx::tmem_ld_32x32b_x32(acc2 + 64, ra);
-        nope_chunk(rb, 32);
-        ptx::tmem_ld_wait();
-        ptx::tmem_ld_32x32b_x32(acc2 + 96, rb);
-        nope_chunk(ra, 64);
-        ptx::tmem_ld_wait();
-        nope_chunk(rb, 96);
-      }
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(ptx::smem_u32(acc2_free));      // acc2[g] fully read (both groups arrive: 256)
-      if (issuer && g == 1 && it < 4) tl_mark(tl, 3 + 3 * it);   // debug timeline: accumulators of unit `it` released
-      // the shared q_nope tile is free once the absorb of the previous token tile has retired
-      // (qn_free completes twice per unit: after tile 0 and after tile 1; tile 0 waits for the previous unit's second one)
-      if (g == 1) ptx::mbar_wait(ptx::smem_u32(qn_free), 0);
-      else if (it > 0) ptx::mbar_wait(ptx::smem_u32(qn_free), 1);
-      __syncwarp();
-#pragma unroll
-      for (int j = 0; j < 16; ++j)  // 16-byte chunk j of the 256-byte row: k-block j/8, chunk j%8
-        ptx::st_shared_v4(ptx::smem_u32(smem + kSNopeOff + (j >> 3) * kTile16K) + ptx::sw128_offset(row, j & 7), wn[4 * j], wn[4 * j + 1],
-                          wn[4 * j + 2], wn[4 * j + 3]);
-      ptx::fence_proxy_async_smem();
-      ptx::mbar_arrive(ptx::smem_u32(qn_ready + g));   // q_nope rows of tile g written
-
-      // drains: this group's 8 absorb units, in the global order the absorb warp issues them
-      float qs = 1.f;
-      if (kInt8Out) qs = Act<T>::to_f(reinterpret_cast<const T*>(qa.q_nope_scale)[head]);
-#pragma unroll 1
-      for (int cp = 0; cp < 4; ++cp) {
-        uint32_t w8[32];  // int8 output: two 64-column units fill one 128-byte row per token
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          const int c = cp * 2 + half;
-          const uint32_t gd = (it * 2 + g) * 8 + c, b = gd & 1;
-          ptx::mbar_wait(ptx::smem_u32(unit_full + b), (gd >> 1) & 1);
-          __syncwarp();
-          ptx::tc_fence_after();
-          uint32_t ra[32], rb[32];
-          const uint32_t acc3 = lane_base + (b ? 448u : 192u);
-          ptx::tmem_ld_32x32b_x32(acc3, ra);
-          ptx::tmem_ld_32x32b_x32(acc3 + 32, rb);
-          ptx::tmem_ld_wait();
-          ptx::tc_fence_before();
-          ptx::mbar_arrive(ptx::smem_u32(abuf_empty + b));
-          if (kInt8Out) {
-            // S9: int8( fp16( act(acc) * q_nope_scale[h] ) )   (golden test_mla:86-92, 466-470)
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              int qa4[4], qb4[4];
-#pragma unroll
-              for (int v = 0; v < 4; ++v) {
-                qa4[v] = sat_i8(__fmul_rn(Act<T>::round(__uint_as_float(ra[4 * j + v])), qs));
-                qb4[v] = sat_i8(__fmul_rn(Act<T>::round(__uint_as_float(rb[4 * j + v])), qs));
-              }
-              w8[half * 16 + j] = pack4_i8(qa4[0], qa4[1], qa4[2], qa4[3]);
-              w8[half * 16 + 8 + j] = pack4_i8(qb4[0], qb4[1], qb4[2], qb4[3]);
-            }
-          } else {
-            uint32_t w[32];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              w[j] = Act<T>::pack(__uint_as_float(ra[2 * j]), __uint_as_float(ra[2 * j + 1]));
-              w[16 + j] = Act<T>::pack(__uint_as_float(rb[2 * j]), __uint_as_float(rb[2 * j + 1]));
-            }
-            stage_acquire();
-#pragma unroll
-            for (int j = 0; j < 8; ++j) ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
-            stage_publish();
-            if (issuer) {
-              ptx::tma_store_2d(&tm_out0, st_tile, head * MLAPO_KV_LORA + c * 64, tok0 + g * kBlockM);
-              ptx::tma_store_commit();
-            }
-          }
-        }
-        if (kInt8Out) {
-          stage_acquire();
-#pragma unroll
-          for (int j = 0; j < 8; ++j) ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, j), w8[4 * j], w8[4 * j + 1], w8[4 * j + 2], w8[4 * j + 3]);
-          stage_publish();
-          if (issuer) {
-            ptx::tma_store_2d(&tm_out0, st_tile, head * MLAPO_KV_LORA + cp * 128, tok0 + g * kBlockM);
-            ptx::tma_store_commit();
-          }
-        }
-      }
-      if (issuer && g == 1 && it < 4) tl_mark(tl, 4 + 3 * it);   // debug timeline: unit `it` fully drained
-    }
-    if (issuer) ptx::tma_store_wait_read<0>();
-  }
-
-  ptx::tc_fence_before();
-  __syncthreads();
-  if (warp == 1) ptx::tmem_dealloc(tmem, 512);
 }
 
 

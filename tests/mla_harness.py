@@ -13,10 +13,9 @@ def to_device(case, device):
     return {k: case.t[k].to(device) for k in TO_DEVICE_KEYS}
 
 
-def run_cuda(case, device, quant_mode="per_tensor_quant_asymm", debug=True, cache_fill=None, persistent=False, extra_flags=0):
-    """Returns (gpu tensors dict, taps dict on CPU).  persistent=True asks for the single persistent cooperative decode
-    kernel (debug flag bit5) where the call is eligible (<= 256 tokens); the default is four PDL-chained kernels.
-    extra_flags: further mlapo_set_debug_flags bits (128 = pre-pair q kernels, 8192 = CTA-pair q kernel wherever n > 128).
+def run_cuda(case, device, quant_mode="per_tensor_quant_asymm", debug=True, cache_fill=None, extra_flags=0, flags=0):
+    """Returns (gpu tensors dict, taps dict on CPU).
+    extra_flags: further mlapo_set_debug_flags bits (8192 = CTA-pair q kernel wherever n > 128); flags: MlapoParams.flags.
     debug=True: synchronise + check after every kernel (which also serialises them) and write the y0 tap; debug="tap": only the
     y0 tap, the kernels stay chained by programmatic dependent launch exactly as in production; debug=False: nothing."""
     from sgl_kernel_npu import cabi
@@ -26,13 +25,13 @@ def run_cuda(case, device, quant_mode="per_tensor_quant_asymm", debug=True, cach
         g["kv_cache_rope"].fill_(cache_fill)
     g["wdqkv_km"] = cabi.repack_nz_weight(g["wdqkv"])
     g["wuq_km"] = cabi.repack_nz_weight(g["wuq"])
-    old = cabi.set_debug_flags((2 if debug == "tap" else 3 if debug else 0) | (32 if persistent else 0) | extra_flags)
+    old = cabi.set_debug_flags((2 if debug == "tap" else 3 if debug else 0) | extra_flags)
     try:
         p = cabi.build_params(g["hiddenState"], g["wdqkv_km"], g["descale0"], g["gamma1"], g["beta1"], g["wuq_km"],
                               g["descale1"], g["gamma2"], g["cos"], g["sin"], g["wuk"], g["kv_cache"], g["kv_cache_rope"],
                               g["slotmapping"], g["quant_scale0"], g["quant_offset0"], g["bias0"], g["quant_scale1"],
                               g["quant_offset1"], g["bias1"], g["ctkv_scale"], g["q_nope_scale"], case.cache_mode,
-                              quant_mode, g["q_out0"], g["q_out1"])
+                              quant_mode, g["q_out0"], g["q_out1"], flags=flags)
         lay = cabi.workspace_layout(p)
         ws = torch.zeros(lay.total_bytes, dtype=torch.uint8, device=device)
         cabi.launch(p, ws)

@@ -38,7 +38,7 @@ CASES = [
     (200, 128, 7168, "bf16", "nzcache", PT, 0.0),
     # prefill-sized: no split-K, 256-wide MM1 tiles, many token super-tiles (the reference stops at 1024 tokens)
     (2400, 2, 7168, "bf16", "krope_ctkv", PT, 0.05),
-    # more (head, 256-token) units than SMs: the q path runs in its streaming form (persistent CTAs, overlapped units)
+    # more (head, 256-token) units than SMs: the q path runs on CTA pairs that stream the units
     (2400, 16, 7168, "bf16", "nzcache", PT, 0.05),
     (1300, 32, 6144, "bf16", "int8_nzcache", PT, 0.0),
     (1100, 40, 7168, "fp16", "krope_ctkv", TOK, 0.0),
@@ -62,29 +62,24 @@ def check(res, case, quant_mode, q0_close):
         assert res["q_out0"][0] <= 2e-3 * res["q_out0"][1], res["q_out0"]  # and almost always bit-identical
 
 
-VARIANTS = {"chained": (False, 0), "persistent": (True, 0), "single_cta_q": (False, 128), "pair_q": (False, 8192)}
+VARIANTS = {"chained": 0, "pair_q": 8192}
 
 
 @pytest.mark.parametrize("variant", list(VARIANTS))
 @pytest.mark.parametrize("cfg", CASES, ids=[f"N{c[0]}-H{c[1]}-D{c[2]}-{c[3]}-{c[4]}-{c[5][:9]}" for c in CASES])
 def test_parity_vs_oracle(cfg, variant, cuda_device):
-    """`chained` = the default launch shape (four PDL-chained kernels; the q path is the per-head kernel, or the CTA-pair
-    kernel when there are more (head, 256-token) units than SMs); `persistent` = the opt-in single cooperative kernel for
-    calls of <= 256 tokens; `single_cta_q` = the streaming q kernel the pair kernel replaced; `pair_q` = the pair kernel
-    forced on every call of more than 128 tokens.  All meet the same bars."""
+    """`chained` = the default launch shape (four kernels chained by programmatic dependent launch; the q path is the per-head
+    kernel, or the CTA-pair kernel when there are more (head, 256-token) units than SMs); `pair_q` = the pair kernel forced on
+    every call of more than 128 tokens.  Both meet the same bars."""
     n, h, d, dt, mode, qm, neg = cfg
-    persistent, extra = VARIANTS[variant]
-    if persistent and n > 256:
-        pytest.skip("the persistent decode kernel covers <= 256 tokens")
+    extra = VARIANTS[variant]
     many_units = n > 256 and h * ((n + 255) // 256) > torch.cuda.get_device_properties(cuda_device).multi_processor_count
-    if variant == "single_cta_q" and not many_units:
-        pytest.skip("same kernels as `chained` for this shape")
     if variant == "pair_q" and (n <= 128 or many_units):
         pytest.skip("same kernels as `chained` for this shape")
     case = orc.gen_case(N=n, H=h, D=d, dtype=DT[dt], cache_mode=mode, seed=42, num_blocks=max(12, n // 64), neg_slot_frac=neg)
     case.t["kv_cache"].fill_(5)
     case.t["kv_cache_rope"].fill_(5)
-    g, taps = hz.run_cuda(case, cuda_device, quant_mode=qm, persistent=persistent, extra_flags=extra)
+    g, taps = hz.run_cuda(case, cuda_device, quant_mode=qm, extra_flags=extra)
     res, ocase, _ = hz.compare(case, qm, g, taps)
     q0_close = mode == "int8_nzcache" or torch.allclose(g["q_out0"].cpu().float(), ocase.t["q_out0"].float(), rtol=1e-2, atol=1e-3)
     check(res, case, qm, q0_close)
@@ -305,16 +300,15 @@ def test_c4_tp_slices(heads, cuda_device):
     check(res, case, PT, q0_close)
 
 
-@pytest.mark.parametrize("variant", ["chained", "persistent"])
 @pytest.mark.parametrize("mode", ["krope_ctkv", "nzcache", "int8_nzcache"])
-def test_c5_kimi_k2_ragged_slots(mode, variant, cuda_device):
+def test_c5_kimi_k2_ragged_slots(mode, cuda_device):
     """BASELINE configs[4]: one DP-attention rank of Kimi-K2 — 128 tokens x 64 heads, every cache mode, slot_mapping made of
     per-request contiguous runs at random block offsets with 10 % of the rows at -1."""
     case = orc.gen_case(N=128, H=64, D=7168, dtype=torch.bfloat16, cache_mode=mode, seed=42, num_blocks=64, neg_slot_frac=0.1,
                         slot_runs=True)
     case.t["kv_cache"].fill_(5)
     case.t["kv_cache_rope"].fill_(5)
-    g, taps = hz.run_cuda(case, cuda_device, quant_mode=PT, debug="tap", persistent=variant == "persistent")
+    g, taps = hz.run_cuda(case, cuda_device, quant_mode=PT, debug="tap")
     res, ocase, _ = hz.compare(case, PT, g, taps)
     q0_close = mode == "int8_nzcache" or torch.allclose(g["q_out0"].cpu().float(), ocase.t["q_out0"].float(), rtol=1e-2, atol=1e-3)
     check(res, case, PT, q0_close)

@@ -4,6 +4,9 @@
 //   mlapo_mb_i8_peak      dense int8 tensor-core peak of this GPU: every SM issues tcgen05.mma.kind::i8 (M128 N256 K32, int32
 //                         accumulators in TMEM) on operand tiles that stay resident in shared memory, so nothing but the tensor
 //                         pipe is exercised.  SURVEY.md §8(d) asks for this figure as the denominator of the prefill roofline.
+//   mlapo_mb_late_copy    a stand-in for a producer kernel that uses programmatic dependent launch the aggressive way: it releases
+//                         its dependents first and only then, after a delay, writes its output (tests/test_back_to_back_gpu.py
+//                         puts it in front of mla_preprocess to check that the operator waits for its inputs by default).
 //   mlapo_mb_dsmem        how fast a CTA can move a split-K partial tile into a peer CTA's shared memory inside a cluster of 8:
 //                         (0) st.shared::cluster 16-byte stores, (1) cp.async.bulk shared::cta -> shared::cluster,
 //                         (2) cp.reduce.async.bulk ... .add.s32 (the reduction done by the copy engine).  Decides whether MM1's
@@ -120,7 +123,10 @@ __global__ void __cluster_dims__(8, 1, 1) __launch_bounds__(kDsThreads, 1) dsmem
         }
       }
       ptx::mbar_wait(ptx::smem_u32(&bar), r & 1);
-      __syncthreads();
+      // nobody starts the next round (whose bytes would be counted on a barrier still in this round's phase) before every CTA
+      // of the cluster has seen this round complete
+      ptx::cluster_arrive();
+      ptx::cluster_wait();
     }
   }
   const long long t1 = clock64();
@@ -129,9 +135,22 @@ __global__ void __cluster_dims__(8, 1, 1) __launch_bounds__(kDsThreads, 1) dsmem
   if (threadIdx.x == 0 && rank == 0) out[blockIdx.x / 8] = t1 - t0;
 }
 
+__global__ void late_copy_kernel(uint4* dst, const uint4* src, long long n16, long long delay_cycles) {
+  ptx::griddep_launch_dependents();   // dependents may start NOW, long before the stores below
+  const long long t0 = clock64();
+  while (clock64() - t0 < delay_cycles) {}
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16; i += (long long)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
 }  // namespace
 
 extern "C" {
+
+// dst[0 .. n16) <- src (16-byte units) by a kernel that triggers its dependents at once and stores after `delay_cycles`.
+int mlapo_mb_late_copy(void* dst, const void* src, long long n16, long long delay_cycles, void* stream) {
+  late_copy_kernel<<<64, 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<uint4*>(dst), static_cast<const uint4*>(src), n16, delay_cycles);
+  return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
 
 // Runs the resident-tile MMA loop for about `target_ms` on every SM and returns the achieved dense int8 rate in TOP/s
 // (2 * M * N * K per MMA); *ms_out = the measured duration.  Negative on CUDA errors.

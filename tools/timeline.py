@@ -10,13 +10,12 @@ import torch
 import bench
 from sgl_kernel_npu import cabi
 
-MM1 = ["gtimer", "start", "prologue/phase2", "upstream", "first_full", "last_full", "mma_done", "epi_issued", "stores_read", "end/mm1-phase-done",
-       "P:quant_done", "P:barrier2_passed", "P:norm_done"]
+MM1 = ["gtimer", "start", "prologue", "upstream", "first_full", "last_full", "mma_done", "epi_issued", "stores_read", "end"]
 QF = ["gtimer", "start", "prologue", "upstream", "first_full", "last_full", "mm2_done", "epi2_done", "unit0", "unit4", "drain_issued",
       "stores_read", "end"]
 
 
-def main(workload="c2", pdl=False, persistent=False, legacy=False):
+def main(workload="c2", pdl=False):
     n, h, d, cache_mode, _ = bench.WORKLOADS[workload]
     dev = torch.device("cuda:0")
     gen = torch.Generator(device=dev).manual_seed(1)
@@ -26,13 +25,13 @@ def main(workload="c2", pdl=False, persistent=False, legacy=False):
     kv, kvr = bench.cache_tensors(torch, cache_mode, 64, dev)
     q0 = torch.zeros((n, h, 512), dtype=torch.int8 if cache_mode == "int8_nzcache" else torch.bfloat16, device=dev)
     q1 = torch.zeros((n, h, 64), dtype=torch.bfloat16, device=dev)
-    cabi.set_debug_flags(8 | (0 if pdl else 1) | (32 if persistent else 0) | (128 if legacy else 0) | int(os.environ.get("MLAPO_EXTRA_FLAGS", "0")))
+    cabi.set_debug_flags(8 | (0 if pdl else 1) | int(os.environ.get("MLAPO_EXTRA_FLAGS", "0")))
     ps = []
     for w in sets:
         ps.append(cabi.build_params(hid, w["wdqkv_km"], w["descale0"], w["gamma1"], w["beta1"], w["wuq_km"], w["descale1"], w["gamma2"],
                                     cos, sin, w["wuk"], kv, kvr, sl, w["quant_scale0"], w["quant_offset0"], w["bias0"], w["quant_scale1"],
                                     w["quant_offset1"], w["bias1"], w["ctkv_scale"], w["q_nope_scale"], cache_mode,
-                                    "per_tensor_quant_asymm", q0, q1))
+                                    "per_tensor_quant_asymm", q0, q1, flags=int(os.environ.get("MLAPO_TL_FLAGS", "1"))))
     lay = cabi.workspace_layout(ps[0])
     ws = torch.zeros(lay.total_bytes, dtype=torch.uint8, device=dev)
     for i in range(6):
@@ -73,12 +72,9 @@ def main(workload="c2", pdl=False, persistent=False, legacy=False):
         t0_ = qs_.min()
         print("quant CTA starts (us), percentiles 0/10/25/50/75/90/100: " + " ".join(f"{(np.percentile(qs_, p) - t0_) / 1e3:.2f}" for p in (0, 10, 25, 50, 75, 90, 100)), "of", qs_.size)
         print("q CTA ends of the SAME call (us, same origin), percentiles 0/50/100: " + " ".join(f"{(np.percentile(qe_, p) - t0_) / 1e3:.2f}" for p in (0, 50, 100)))
-    QS = ["gtimer", "start"] + [f"u{i}:{w}" for i in range(4) for w in ("mm2_done", "acc2_released", "drained")]
     QP = ["gtimer", "start", "prologue", "upstream", "first_full"] + [f"u{i}:{w}" for i in range(3) for w in ("mm2_done", "acc_read", "drained")] + ["end"]
     stream = n > 256 and h * ((n + 255) // 256) > 148
-    qname, qlabels = ("q_stream", QS) if stream else ("q_fused", QF)
-    if stream and not legacy:
-        qname, qlabels = "q_pair", QP
+    qname, qlabels = ("q_pair", QP) if stream else ("q_fused", QF)
     for k, (name, labels) in enumerate([("mm1_splitk", MM1), (qname, qlabels)]):
         a = tl[k]
         used = a[:, 1] != 0
@@ -116,6 +112,5 @@ def main(workload="c2", pdl=False, persistent=False, legacy=False):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1] if len(sys.argv) > 1 else "c2", pdl=len(sys.argv) > 2 and ("pdl" in sys.argv[2:] or "persistent" in sys.argv[2:]),
-         persistent=len(sys.argv) > 2 and sys.argv[2] == "persistent", legacy="legacy" in sys.argv[2:])
+    main(sys.argv[1] if len(sys.argv) > 1 else "c2", pdl="pdl" in sys.argv[2:])
 
