@@ -416,16 +416,32 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     g_kernel_names[3] = "q_pair";
   } else {
     g_kernel_names[3] = "q_fused";
-    dim3 grid(h, q_tok_tiles);
-    if (int8_out) {
-      static DoneFlag done[kMaxDevices];
-      if ((rc = set_smem_attr(q_fused_kernel<T, true>, kQSmemBytes, &done[dev], "q_fused<int8>"))) return rc;
-      e__ = launch_k(q_fused_kernel<T, true>, grid, dim3(kQThreads), kQSmemBytes, st, pdl, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, tl4);
-    } else {
-      static DoneFlag done[kMaxDevices];
-      if ((rc = set_smem_attr(q_fused_kernel<T, false>, kQSmemBytes, &done[dev], "q_fused"))) return rc;
-      e__ = launch_k(q_fused_kernel<T, false>, grid, dim3(kQThreads), kQSmemBytes, st, pdl, tm_a1, tm_wuq, tm_wuk, tm_o0, tm_o1, qa, tl4);
+    // Few (head, token tile) units: 2 or 4 CTAs share a unit (each recomputes the nope slice of MM2 and takes its share of the
+    // RoPE pairs and of the absorb chunks) as long as the grid still fits one wave.  Debug bit14 keeps one CTA per unit (A/B).
+    const int units = h * q_tok_tiles;
+    const int split = (g_debug_flags & 16384) ? 1 : (units * 4 <= num_sms() ? 4 : units * 2 <= num_sms() ? 2 : 1);
+    CUtensorMap tm_wuq_n = tm_wuq, tm_wuq_r = tm_wuq;
+    if (split > 1) {
+      if ((rc = make_tmap(&tm_wuq_n, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wuq_km, (uint64_t)h * MLAPO_Q_HEAD, MLAPO_Q_LORA, MLAPO_Q_LORA,
+                          MLAPO_Q_NOPE, 128))) return rc;
+      if ((rc = make_tmap(&tm_wuq_r, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wuq_km, (uint64_t)h * MLAPO_Q_HEAD, MLAPO_Q_LORA, MLAPO_Q_LORA,
+                          32 / split, 128))) return rc;
     }
+    qa.q_out1 = p->q_out1;
+    dim3 grid(h, q_tok_tiles, split);
+#define MLAPO_LAUNCH_QF(I8, SP)                                                                                                   \
+  do {                                                                                                                            \
+    static DoneFlag done[kMaxDevices];                                                                                            \
+    if ((rc = set_smem_attr(q_fused_kernel<T, I8, SP>, kQSmemBytes, &done[dev], "q_fused"))) return rc;                           \
+    e__ = launch_k(q_fused_kernel<T, I8, SP>, grid, dim3(kQThreads), kQSmemBytes, st, pdl, tm_a1, tm_wuq, tm_wuq_n, tm_wuq_r,     \
+                   tm_wuk, tm_o0, tm_o1, qa, tl4);                                                                                \
+  } while (0)
+    if (int8_out) {
+      if (split == 4) MLAPO_LAUNCH_QF(true, 4); else if (split == 2) MLAPO_LAUNCH_QF(true, 2); else MLAPO_LAUNCH_QF(true, 1);
+    } else {
+      if (split == 4) MLAPO_LAUNCH_QF(false, 4); else if (split == 2) MLAPO_LAUNCH_QF(false, 2); else MLAPO_LAUNCH_QF(false, 1);
+    }
+#undef MLAPO_LAUNCH_QF
     MLAPO_CHECK_LAUNCH("q_fused");
   }
   record_event(4, st);

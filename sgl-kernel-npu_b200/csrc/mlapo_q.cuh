@@ -52,6 +52,18 @@ struct QArgs {
   int m_total;
   int descale_is_i64;
   int cta_tokens;             // 256 (two token tiles per CTA, weights streamed once per 256 tokens) or 128 (more CTAs when heads are few)
+  void* q_out1;               // act [N, H, 64]: written with plain stores by the split forms (kSplit > 1)
+};
+
+// Few heads (a TP slice, a small batch) leave most SMs without a (head, token tile) unit.  kSplit = 2 or 4 CTAs then share a unit:
+// each recomputes the nope slice of MM2 (all 128 columns: it is the A operand of every absorb chunk), takes 32 / kSplit of the 32
+// RoPE pairs (columns i and i + 32 of the rope slice) and 4 / kSplit of the four 128-column absorb chunks.  Per CTA that is
+// 196 KB + (98 + 131) KB / kSplit of weights instead of 426 KB, and 1 / kSplit of the outputs.
+template <int kSplit> struct QSplit {
+  static_assert(kSplit == 1 || kSplit == 2 || kSplit == 4, "kSplit");
+  static constexpr int G = 32 / kSplit;        // RoPE pairs of this CTA
+  static constexpr int NB = 128 + 2 * G;       // MM2 columns of this CTA (MMA N): 192, 160, 144
+  static constexpr int CH = 4 / kSplit;        // absorb chunks of this CTA
 };
 
 // Where one CTA's q-path work item lives.
@@ -60,11 +72,12 @@ struct QCtx {
   uint64_t* bars;    // full[4] empty[4] mm2_done wuk_full[4] qn_ready[2] unit_full[4] buf_empty[4] rope_done[2]
   int2* s_cst;       // per column {bias, descale bits}
   uint32_t tmem;     // base of a 512-column TMEM allocation
-  int head, tok0, num_mt, load_mt;
+  int head, tok0, num_mt, load_mt, z;
   static constexpr int NUM_BARS = 25;
 
-  __device__ void set_work(int head_, int tok_tile, const QArgs& qa) {
+  __device__ void set_work(int head_, int tok_tile, int z_, const QArgs& qa) {
     head = head_;
+    z = z_;
     tok0 = tok_tile * qa.cta_tokens;
     num_mt = (qa.cta_tokens > kBlockM && (qa.m_total - tok0) > kBlockM) ? 2 : 1;  // token tiles with valid rows in this CTA
     load_mt = (qa.cta_tokens > kBlockM && qa.m_total > kBlockM) ? 2 : 1;          // token tiles fetched per stage (uniform over the grid)
@@ -83,24 +96,43 @@ __device__ __forceinline__ void q_init_barriers(uint64_t* bars) {  // one thread
   ptx::mbar_init(ptx::smem_u32(bars + 24), 128);
 }
 
+// W_UQ rows of k-block kb for this CTA -> the B area of stage `dst_stage`: the whole head (kSplit == 1), or its nope rows plus
+// this CTA's RoPE pairs (rows 128 + z G .. and 160 + z G ..), which land behind one another so that the MMA sees NB contiguous rows.
+template <int kSplit>
+__device__ __forceinline__ void q_load_wuq(const QCtx& c, const CUtensorMap* tm_wuq, const CUtensorMap* tm_wuq_n, const CUtensorMap* tm_wuq_r,
+                                           int kb, uint32_t dst, uint32_t bar) {
+  using S = QSplit<kSplit>;
+  const int row0 = c.head * MLAPO_Q_HEAD;
+  if constexpr (kSplit == 1) {
+    ptx::tma_load_2d(dst, tm_wuq, bar, kb * kBlockKBytes, row0, ptx::kEvictFirst);
+  } else {
+    // the nope rows are fetched by every CTA of the unit: keep them in L2 for the siblings
+    ptx::tma_load_2d(dst, tm_wuq_n, bar, kb * kBlockKBytes, row0, ptx::kEvictLast);
+    ptx::tma_load_2d(dst + 128 * kBlockKBytes, tm_wuq_r, bar, kb * kBlockKBytes, row0 + 128 + c.z * S::G, ptx::kEvictFirst);
+    ptx::tma_load_2d(dst + (128 + S::G) * kBlockKBytes, tm_wuq_r, bar, kb * kBlockKBytes, row0 + 160 + c.z * S::G, ptx::kEvictFirst);
+  }
+}
+
 // One thread: arm the four MM2 stages and request their W_UQ k-blocks (which depend on nothing upstream).
-__device__ __forceinline__ void q_issue_weights(const QCtx& c, const CUtensorMap* tm_wuq) {
-  const uint32_t stage_tx = (uint32_t)(c.load_mt * kTile16K + MLAPO_Q_HEAD * kBlockKBytes);
+template <int kSplit>
+__device__ __forceinline__ void q_issue_weights(const QCtx& c, const CUtensorMap* tm_wuq, const CUtensorMap* tm_wuq_n, const CUtensorMap* tm_wuq_r) {
+  const uint32_t stage_tx = (uint32_t)(c.load_mt * kTile16K + QSplit<kSplit>::NB * kBlockKBytes);
   for (int kb = 0; kb < kQStages; ++kb) {
     const uint32_t fb = ptx::smem_u32(c.bars + kb);
     ptx::mbar_arrive_expect_tx(fb, stage_tx);
-    ptx::tma_load_2d(ptx::smem_u32(c.smem + kb * kQStageBytes + 2 * kTile16K), tm_wuq, fb, kb * kBlockKBytes, c.head * MLAPO_Q_HEAD,
-                     ptx::kEvictFirst);
+    q_load_wuq<kSplit>(c, tm_wuq, tm_wuq_n, tm_wuq_r, kb, ptx::smem_u32(c.smem + kb * kQStageBytes + 2 * kTile16K), fb);
   }
 }
 
 // Warp roles of the q path: warp 0 = TMA producer, warp 1 = MMA issuer, warps 2..5 / 6..9 = epilogue groups of token tile 0 / 1.
 // The caller has already issued q_issue_weights().  Under programmatic dependent launch the roles wait for the upstream kernel
 // before touching a1 / the per-token scales.
-template <class T, bool kInt8Out>
-__device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1, const CUtensorMap* tm_wuq, const CUtensorMap* tm_wuk,
-                                        const CUtensorMap* tm_out0, const CUtensorMap* tm_out1, const QArgs& qa, int warp, int lane,
-                                        long long* tl) {
+template <class T, bool kInt8Out, int kSplit>
+__device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1, const CUtensorMap* tm_wuq, const CUtensorMap* tm_wuq_n,
+                                        const CUtensorMap* tm_wuq_r, const CUtensorMap* tm_wuk, const CUtensorMap* tm_out0,
+                                        const CUtensorMap* tm_out1, const QArgs& qa, int warp, int lane, long long* tl) {
+  using S = QSplit<kSplit>;
+  constexpr int G = S::G, NB = S::NB, CH = S::CH;
   uint8_t* const smem = c.smem;
   uint64_t* const full_bar = c.bars;        // [4]  TMA -> MMA
   uint64_t* const empty_bar = c.bars + 4;   // [4]  MMA -> TMA
@@ -112,15 +144,14 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
   uint64_t* const rope_done = c.bars + 23;  // [2]  epilogue group m -> MMA: acc2[m] columns 128..191 drained as well
   int2* const s_cst = c.s_cst;
   const uint32_t tmem = c.tmem;
-  const int head = c.head, tok0 = c.tok0, num_mt = c.num_mt, load_mt = c.load_mt;
+  const int head = c.head, tok0 = c.tok0, num_mt = c.num_mt, load_mt = c.load_mt, z = c.z;
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      const uint32_t stage_tx = (uint32_t)(load_mt * kTile16K + MLAPO_Q_HEAD * kBlockKBytes);
+      const uint32_t stage_tx = (uint32_t)(load_mt * kTile16K + NB * kBlockKBytes);
       auto load_b = [&](int kb) {
         const int s = kb & 3;
-        ptx::tma_load_2d(ptx::smem_u32(smem + s * kQStageBytes + 2 * kTile16K), tm_wuq, ptx::smem_u32(full_bar + s),
-                         kb * kBlockKBytes, head * MLAPO_Q_HEAD, ptx::kEvictFirst);
+        q_load_wuq<kSplit>(c, tm_wuq, tm_wuq_n, tm_wuq_r, kb, ptx::smem_u32(smem + s * kQStageBytes + 2 * kTile16K), ptx::smem_u32(full_bar + s));
       };
       auto load_a = [&](int kb) {  // one box = all token tiles of the stage (box rows = 128 * load_mt)
         const int s = kb & 3;
@@ -137,25 +168,30 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
         load_b(kb);
         load_a(kb);
       }
-      // Wuk chunk c -> bytes [32K*c, 32K*c+32K): needs the last use (3rd release, parity 0) of the stages it overlaps
-      auto load_wuk = [&](int c) {
-        const uint32_t fb = ptx::smem_u32(wuk_full + c);
+      // This CTA's Wuk chunk cl (columns 128 (z CH + cl) ..) -> bytes [32K*cl, 32K*cl+32K): needs the last use (3rd release,
+      // parity 0) of the stages it overlaps
+      auto load_wuk = [&](int cl) {
+        const uint32_t fb = ptx::smem_u32(wuk_full + cl);
         ptx::mbar_arrive_expect_tx(fb, 2 * kTile16K);
         for (int at = 0; at < 2; ++at)
-          ptx::tma_load_2d(ptx::smem_u32(smem + kQWukOff + c * 32768 + at * kTile16K), tm_wuk, fb, c * 128 + at * 64,
+          ptx::tma_load_2d(ptx::smem_u32(smem + kQWukOff + cl * 32768 + at * kTile16K), tm_wuk, fb, (z * CH + cl) * 128 + at * 64,
                            head * MLAPO_Q_NOPE, ptx::kEvictFirst);
       };
       ptx::mbar_wait(ptx::smem_u32(empty_bar + 0), 0);
       load_wuk(0);                                   // [0, 32K)    in stage 0
-      ptx::mbar_wait(ptx::smem_u32(empty_bar + 1), 0);
-      load_wuk(1);                                   // [32K, 64K)  in stages 0, 1
-      load_wuk(2);                                   // [64K, 96K)  in stage 1
-      ptx::mbar_wait(ptx::smem_u32(empty_bar + 2), 0);
-      load_wuk(3);                                   // [96K, 128K) in stages 1, 2
+      if constexpr (CH > 1) {
+        ptx::mbar_wait(ptx::smem_u32(empty_bar + 1), 0);
+        load_wuk(1);                                 // [32K, 64K)  in stages 0, 1
+      }
+      if constexpr (CH > 2) {
+        load_wuk(2);                                 // [64K, 96K)  in stage 1
+        ptx::mbar_wait(ptx::smem_u32(empty_bar + 2), 0);
+        load_wuk(3);                                 // [96K, 128K) in stages 1, 2
+      }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    constexpr uint32_t idesc2 = ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, kBlockM, MLAPO_Q_HEAD);
+    constexpr uint32_t idesc2 = ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, kBlockM, NB);
     constexpr uint32_t kAFmt = std::is_same<T, __nv_bfloat16>::value ? ptx::kFmtBF16 : ptx::kFmtF16;
     constexpr uint32_t idesc3 = ptx::make_idesc(ptx::kCFmtF32, kAFmt, kAFmt, 0, 1, kBlockM, 128);
     for (int kb = 0; kb < kQKBlocks; ++kb) {
@@ -182,12 +218,12 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
     }
     if (lane == 0) ptx::umma_commit(ptx::smem_u32(mm2_done));
     __syncwarp();
-    // absorb units (c, m): token tile m ping-pongs its own two TMEM buffers over the four Wuk chunks
-    for (int c = 0; c < 4; ++c) {
+    // absorb units (c, m): token tile m ping-pongs its own two TMEM buffers over this CTA's Wuk chunks
+    for (int c = 0; c < CH; ++c) {
       for (int m = 0; m < num_mt; ++m) {
         const int ub = m * 2 + (c & 1);
         if (c == 0) ptx::mbar_wait(ptx::smem_u32(qn_ready + m), 0);   // buffer 0 = acc2[m] columns 0..127 (nope, drained)
-        if (c == 1) ptx::mbar_wait(ptx::smem_u32(rope_done + m), 0);  // buffer 1 overlaps acc2[m] columns 128..191 (rope)
+        if (c == 1) ptx::mbar_wait(ptx::smem_u32(rope_done + m), 0);  // buffer 1 overlaps acc2[m] columns 128.. (rope)
         if (c >= 2) ptx::mbar_wait(ptx::smem_u32(buf_empty + ub), 0);
         if (m == 0) ptx::mbar_wait(ptx::smem_u32(wuk_full + c), 0);
         __syncwarp();
@@ -230,9 +266,10 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
     };
 
     if (g == 0) {
-      for (int c = et; c < MLAPO_Q_HEAD; c += 128) {
-        const float dsc = load_descale(qa.descale1, qa.descale_is_i64, head * MLAPO_Q_HEAD + c);
-        s_cst[c] = make_int2(qa.bias1 ? qa.bias1[head * MLAPO_Q_HEAD + c] : 0, __float_as_int(dsc));
+      for (int cc = et; cc < NB; cc += 128) {  // local MM2 column -> column of the head: nope | this CTA's pairs, low halves | high halves
+        const int col = head * MLAPO_Q_HEAD + (cc < 128 ? cc : cc < 128 + G ? 128 + z * G + (cc - 128) : 160 + z * G + (cc - 128 - G));
+        const float dsc = load_descale(qa.descale1, qa.descale_is_i64, col);
+        s_cst[cc] = make_int2(qa.bias1 ? qa.bias1[col] : 0, __float_as_int(dsc));
       }
     }
     ptx::griddep_wait();  // tok_scale1 comes from the norm kernel (and keeps the PDL completion chain transitive)
@@ -255,13 +292,28 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
         f0 = __fmul_rn(__fmul_rn(__int2float_rn((int)acc0 + cst.x), __int_as_float(cst.y)), ts);
         f1 = __fmul_rn(__fmul_rn(__int2float_rn((int)acc1 + cst.z), __int_as_float(cst.w)), ts);
       };
-      // cos/sin rows of this token (issued before the MM2 wait; consumed after the nope slice)
-      uint4 cs[8], sn[8];
+      // cos/sin of this token (issued before the MM2 wait; consumed after the nope slice): the whole rows, or — split forms — the
+      // G values of this CTA's pairs and the G of their partners 32 columns on
+      constexpr int CSV = kSplit == 1 ? 8 : 2 * G / 8;   // 16-byte vectors per table
+      uint4 cs[CSV], sn[CSV];
       {
-        const uint4* cp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(qa.cos) + (long long)tc * 64);
-        const uint4* sp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(qa.sin) + (long long)tc * 64);
+        const T* cp = reinterpret_cast<const T*>(qa.cos) + (long long)tc * 64;
+        const T* sp = reinterpret_cast<const T*>(qa.sin) + (long long)tc * 64;
+        if constexpr (kSplit == 1) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { cs[j] = ptx::ld_global_nc_v4(cp + j); sn[j] = ptx::ld_global_nc_v4(sp + j); }
+          for (int j = 0; j < 8; ++j) {
+            cs[j] = ptx::ld_global_nc_v4(reinterpret_cast<const uint4*>(cp) + j);
+            sn[j] = ptx::ld_global_nc_v4(reinterpret_cast<const uint4*>(sp) + j);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < G / 8; ++j) {
+            cs[j] = ptx::ld_global_nc_v4(reinterpret_cast<const uint4*>(cp + z * G) + j);
+            sn[j] = ptx::ld_global_nc_v4(reinterpret_cast<const uint4*>(sp + z * G) + j);
+            cs[G / 8 + j] = ptx::ld_global_nc_v4(reinterpret_cast<const uint4*>(cp + 32 + z * G) + j);
+            sn[G / 8 + j] = ptx::ld_global_nc_v4(reinterpret_cast<const uint4*>(sp + 32 + z * G) + j);
+          }
+        }
       }
 
       ptx::mbar_wait(ptx::smem_u32(mm2_done), 0);
@@ -286,6 +338,7 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
           ptx::st_shared_v4(tile + ptx::sw128_offset(row, ((c0 & 63) >> 3) + j), w[0], w[1], w[2], w[3]);
         }
       };
+      if constexpr (kSplit == 1) {
       float x[64];
       {
         uint32_t ra[32], rb[32];
@@ -354,19 +407,83 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
         ptx::tma_store_2d(tm_out1, st_tile, head * MLAPO_ROPE, tok0 + m * kBlockM);
         ptx::tma_store_commit();
       }
+      } else {
+        // split forms: the rope slice of this CTA is columns [128, 128 + G) (pairs' low halves) and [128 + G, 128 + 2 G) (their
+        // partners); its 2 x G results go to q_out1 with plain 16-byte stores (two short runs per row: no staging tile needed)
+        float xl[G], xh[G];
+        {
+          uint32_t ra[32], rb[32];
+          ptx::tmem_ld_32x32b_x32(acc2 + 0, ra);
+          ptx::tmem_ld_wait();
+          ptx::tmem_ld_32x32b_x32(acc2 + 32, rb);
+          nope_chunk(ra, 0);
+          ptx::tmem_ld_wait();
+          ptx::tmem_ld_32x32b_x32(acc2 + 64, ra);
+          nope_chunk(rb, 32);
+          ptx::tmem_ld_wait();
+          ptx::tmem_ld_32x32b_x32(acc2 + 96, rb);
+          nope_chunk(ra, 64);
+          ptx::tmem_ld_wait();
+          uint32_t rr[2 * G];
+          if constexpr (G == 16) ptx::tmem_ld_32x32b_x32(acc2 + 128, rr);
+          else ptx::tmem_ld_32x32b_x16(acc2 + 128, rr);
+          nope_chunk(rb, 96);
+          ptx::fence_proxy_async_smem();
+          ptx::tmem_ld_wait();
+          // q_nope rows written and acc2[m] read completely: both absorb buffers of this token tile are free
+          ptx::tc_fence_before();
+          ptx::mbar_arrive(ptx::smem_u32(qn_ready + m));
+          ptx::mbar_arrive(ptx::smem_u32(rope_done + m));
+#pragma unroll
+          for (int j = 0; j < G; j += 2) {
+            deq2(rr[j], rr[j + 1], 128 + j, xl[j], xl[j + 1]);
+            deq2(rr[G + j], rr[G + j + 1], 128 + G + j, xh[j], xh[j + 1]);
+            xl[j] = Act<T>::round(xl[j]);
+            xl[j + 1] = Act<T>::round(xl[j + 1]);
+            xh[j] = Act<T>::round(xh[j]);
+            xh[j + 1] = Act<T>::round(xh[j + 1]);
+          }
+        }
+        if (t < qa.m_total) {
+          T* const o_lo = reinterpret_cast<T*>(qa.q_out1) + ((long long)t * qa.num_heads + head) * MLAPO_ROPE + z * G;
+#pragma unroll
+          for (int v = 0; v < G / 8; ++v) {
+            float c_lo[8], s_lo[8], c_hi[8], s_hi[8];
+            unpack8<T>(cs[v], c_lo);
+            unpack8<T>(sn[v], s_lo);
+            unpack8<T>(cs[G / 8 + v], c_hi);
+            unpack8<T>(sn[G / 8 + v], s_hi);
+            uint32_t wl[4], wh[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int i0 = v * 8 + 2 * u, i1 = i0 + 1;
+              // out[i] = x[i]*cos[i] + (-x[i+32])*sin[i];  out[i+32] = x[i+32]*cos[i+32] + x[i]*sin[i+32]   (test_mla:57-67)
+              const float a0 = __fadd_rn(__fmul_rn(xl[i0], c_lo[2 * u]), __fmul_rn(-xh[i0], s_lo[2 * u]));
+              const float a1 = __fadd_rn(__fmul_rn(xl[i1], c_lo[2 * u + 1]), __fmul_rn(-xh[i1], s_lo[2 * u + 1]));
+              const float b0 = __fadd_rn(__fmul_rn(xh[i0], c_hi[2 * u]), __fmul_rn(xl[i0], s_hi[2 * u]));
+              const float b1 = __fadd_rn(__fmul_rn(xh[i1], c_hi[2 * u + 1]), __fmul_rn(xl[i1], s_hi[2 * u + 1]));
+              wl[u] = Act<T>::pack(a0, a1);
+              wh[u] = Act<T>::pack(b0, b1);
+            }
+            ptx::st_global_v4(o_lo + v * 8, wl[0], wl[1], wl[2], wl[3]);
+            ptx::st_global_v4(o_lo + 32 + v * 8, wh[0], wh[1], wh[2], wh[3]);
+          }
+        }
+      }
       if (issuer && g == 0) tl_mark(tl, 7);  // epi2 done
 
       // absorb drains
       float qs = 1.f;
       if (kInt8Out) qs = Act<T>::to_f(reinterpret_cast<const T*>(qa.q_nope_scale)[head]);
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < CH; ++c) {   // local chunk index; its output columns start at 128 * cg
+        const int cg = z * CH + c;
         const int ub = m * 2 + (c & 1);
         ptx::mbar_wait(ptx::smem_u32(unit_full + ub), (c >> 1) & 1);
         __syncwarp();
         ptx::tc_fence_after();
         if (issuer && g == 0 && c == 0) tl_mark(tl, 8);  // first absorb unit ready
-        if (issuer && g == 0 && c == 3) tl_mark(tl, 9);
+        if (issuer && g == 0 && c == CH - 1) tl_mark(tl, 9);
         const uint32_t acc3 = lane_base + m * 256 + (c & 1) * 128;
         if (kInt8Out) {
           // S9: int8( fp16( act(acc) * q_nope_scale[h] ) )   (golden test_mla:86-92, 466-470); 128 cols = one 128-byte row
@@ -385,13 +502,13 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
             }
           }
           ptx::tc_fence_before();
-          if (c < 2) ptx::mbar_arrive(ptx::smem_u32(buf_empty + ub));
+          if (c + 2 < CH) ptx::mbar_arrive(ptx::smem_u32(buf_empty + ub));
           stage_acquire();
 #pragma unroll
           for (int j = 0; j < 8; ++j) ptx::st_shared_v4(st_tile + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
           stage_publish();
           if (issuer) {
-            ptx::tma_store_2d(tm_out0, st_tile, head * MLAPO_KV_LORA + c * 128, tok0 + m * kBlockM);
+            ptx::tma_store_2d(tm_out0, st_tile, head * MLAPO_KV_LORA + cg * 128, tok0 + m * kBlockM);
             ptx::tma_store_commit();
           }
         } else {
@@ -408,7 +525,7 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
             }
             if (half == 1) {
               ptx::tc_fence_before();
-              if (c < 2) ptx::mbar_arrive(ptx::smem_u32(buf_empty + ub));
+              if (c + 2 < CH) ptx::mbar_arrive(ptx::smem_u32(buf_empty + ub));
             }
             // unit_full(c) implies every MMA of chunk c-1 has retired, so Wuk slot c-1 is dead: its g-th 16 KB tile
             // becomes this group's second staging buffer (first half -> own tile, second half -> dead slot).
@@ -420,7 +537,7 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
             for (int j = 0; j < 8; ++j) ptx::st_shared_v4(dst + ptx::sw128_offset(row, j), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
             stage_publish();
             if (issuer) {
-              ptx::tma_store_2d(tm_out0, dst, head * MLAPO_KV_LORA + c * 128 + half * 64, tok0 + m * kBlockM);
+              ptx::tma_store_2d(tm_out0, dst, head * MLAPO_KV_LORA + cg * 128 + half * 64, tok0 + m * kBlockM);
               ptx::tma_store_commit();
             }
           }
@@ -436,9 +553,10 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
 
 }
 
-template <class T, bool kInt8Out>
+template <class T, bool kInt8Out, int kSplit>
 __global__ void __launch_bounds__(kQThreads, 1)
 q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__ CUtensorMap tm_wuq,
+               const __grid_constant__ CUtensorMap tm_wuq_n, const __grid_constant__ CUtensorMap tm_wuq_r,
                const __grid_constant__ CUtensorMap tm_wuk, const __grid_constant__ CUtensorMap tm_out0,
                const __grid_constant__ CUtensorMap tm_out1, QArgs qa, long long* tl) {
   if (threadIdx.x == 0) { tl_mark_global(tl, 0); tl_mark(tl, 1); }
@@ -449,14 +567,14 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
   c.bars = reinterpret_cast<uint64_t*>(c.smem + kQBarOff);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(c.bars + 26);
   c.s_cst = reinterpret_cast<int2*>(c.smem + kQBarOff + 256);
-  c.set_work(blockIdx.x, blockIdx.y, qa);
+  c.set_work(blockIdx.x, blockIdx.y, blockIdx.z, qa);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {  // barriers + the first W_UQ k-blocks before anything else: they depend on nothing
-    ptx::prefetch_tmap(&tm_wuq);
+    ptx::prefetch_tmap(kSplit == 1 ? &tm_wuq : &tm_wuq_n);
     q_init_barriers(c.bars);
     ptx::fence_mbar_init();
-    q_issue_weights(c, &tm_wuq);
+    q_issue_weights<kSplit>(c, &tm_wuq, &tm_wuq_n, &tm_wuq_r);
     ptx::prefetch_tmap(&tm_a1);
     ptx::prefetch_tmap(&tm_wuk);
     ptx::prefetch_tmap(&tm_out0);
@@ -474,10 +592,10 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
   if (threadIdx.x == 0 && tl) {  // which SM ran this CTA (timeline analysis only)
     unsigned smid;
     asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-    tl[(blockIdx.x + gridDim.x * blockIdx.y) * 16 + 13] = smid;
+    tl[(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) * 16 + 13] = smid;
   }
 
-  q_roles<T, kInt8Out>(c, &tm_a1, &tm_wuq, &tm_wuk, &tm_out0, &tm_out1, qa, warp, lane, tl);
+  q_roles<T, kInt8Out, kSplit>(c, &tm_a1, &tm_wuq, &tm_wuq_n, &tm_wuq_r, &tm_wuk, &tm_out0, &tm_out1, qa, warp, lane, tl);
 
   ptx::tc_fence_before();
   __syncthreads();
