@@ -130,6 +130,7 @@ def kernel_algorithmic_bytes(name, n, h, d, cache_mode):
     return {
         "quant_hidden": n * d * 2 + n * d,
         "mm1_splitk": 2112 * d + n * d + n * 2112 * 4,
+        "mm1_pair": 2112 * d + n * d + n * 2112 * 4,
         "mm1_dequant": 2112 * d + n * d + n * 2112 * 2,
         "norm_rope_cache": n * 2112 * 4 + n * 1536 + n * (512 * q0 + 128) + n * 260 + 8 * 2112 + 4 * 1536 + 1024,
         "norm_rope_cache_y0": n * 2112 * 2 + n * 1536 + n * (512 * q0 + 128) + n * 260 + 4 * 1536 + 1024,

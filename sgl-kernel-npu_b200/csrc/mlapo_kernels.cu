@@ -38,6 +38,7 @@
 #include "mlapo_numerics.cuh"
 #include "mlapo_quant_norm.cuh"
 #include "mlapo_mm1.cuh"
+#include "mlapo_mm1_pair.cuh"
 #include "mlapo_q.cuh"
 #include "mlapo_q_pair.cuh"
 #include "mlapo_format.cuh"
@@ -163,11 +164,15 @@ static cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_
   return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
 }
 
+// Calls of more than 128 tokens run MM1 on CTA pairs (mlapo_mm1_pair.cuh): a work item then occupies two SMs.  Debug bit16
+// keeps the single-CTA form (A/B).
+static bool mm1_on_pairs(int n_tokens) { return n_tokens > kBlockM && !(g_debug_flags & 65536); }
+
 static int choose_splits0(int n_tokens, int hidden_dim) {
-  const int m_super = n_tokens > 0 ? (n_tokens + 2 * kBlockM - 1) / (2 * kBlockM) : 1;  // CTAs cover up to 256 tokens
+  const int m_super = n_tokens > 0 ? (n_tokens + 2 * kBlockM - 1) / (2 * kBlockM) : 1;  // work items cover up to 256 tokens
   const int n_tiles = (MLAPO_MM1_OUT + kMm1BlockN - 1) / kMm1BlockN;                     // 17
   const int kb_total = hidden_dim / kBlockKBytes;
-  int s = num_sms() / (n_tiles * m_super);  // one wave of CTAs
+  int s = (mm1_on_pairs(n_tokens) ? num_sms() / 2 : num_sms()) / (n_tiles * m_super);  // one wave of CTAs (or CTA pairs)
   if (s < 1) s = 1;
   if (s > 8) s = 8;
   if (s > kb_total) s = kb_total;
@@ -365,6 +370,14 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
       e__ = launch_k(mm1_dequant_kernel<2, kMm1BlockNWide, T>, dim3(n_tiles, 1, (n + 255) / 256), dim3(kGemmThreads), smem, st, pdl,
                      tm_a0, tm_wdqkv, tm_part, tm_y0, dq, n, d / kBlockKBytes, tl1);
       g_kernel_names[1] = "mm1_dequant";
+    } else if (mm1_on_pairs(n)) {
+      static DoneFlag done[kMaxDevices];
+      if ((rc = set_smem_attr(mm1_pair_kernel, kM1PSmemBytes, &done[dev], "mm1_pair"))) return rc;
+      CUtensorMap tm_wh;  // this form fetches the weight tile in two halves of 64 rows, one per CTA of the pair
+      if ((rc = make_tmap(&tm_wh, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wdqkv_km, MLAPO_MM1_OUT, d, d, kM1PHalfB, 128))) return rc;
+      e__ = launch_k(mm1_pair_kernel, dim3(2 * n_tiles, l.splits0, (n + 255) / 256), dim3(kGemmThreads), kM1PSmemBytes, st, pdl,
+                     tm_a0, tm_wh, tm_part, n, d / kBlockKBytes, tl1);
+      g_kernel_names[1] = "mm1_pair";
     } else if (n > kBlockM) {
       static DoneFlag done[kMaxDevices];
       if ((rc = set_smem_attr(mm1_splitk_kernel<2, kMm1BlockN>, mm1_smem_bytes<2, kMm1BlockN>(), &done[dev], "mm1<2,128>"))) return rc;
