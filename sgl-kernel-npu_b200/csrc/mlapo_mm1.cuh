@@ -26,6 +26,8 @@ constexpr int kTile16K = 16384;    // [128 rows x 128 B] swizzled tile
 constexpr int kMm1BlockN = 128;   // decode: 17 weight tiles x up to 8 K-splits fill one wave
 constexpr int kMm1BlockNWide = 256;  // prefill (no split-K): 256 x 256 CTA tiles halve the activation re-reads per weight byte
 
+// (Seven stages for the one-token-tile form — its whole weight slice requested before the wait — were tried: C1 17.75 -> 17.45 us,
+// but C5 24.2 -> 26.0 us: at 230 KB the CTA leaves no room for the norm kernel's CTAs to start under it.)
 template <int MT, int BN>
 __host__ __device__ constexpr int mm1_stages() { return (MT * kTile16K + BN * kBlockKBytes) > 49152 ? 3 : 4; }
 template <int MT, int BN, bool kDequant = false>
