@@ -394,7 +394,11 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   record_event(2, st);
 
   // ---- k3: norms, quant, rope, cache scatter
-  if (wide) e__ = launch_k(norm_rope_cache_kernel<T, 0>, dim3(n), dim3(kNormThreads), 0, st, pdl, na);  // prefill: reads the dequantised rows
+  if (wide && !(g_debug_flags & 131072)) {  // prefill: one warp per row of the dequantised y0 (debug bit17 keeps the CTA-per-row form)
+    const int rows_per_block = kNormWarpThreads / 32;
+    const int want = (n + rows_per_block - 1) / rows_per_block, cap = num_sms() * 4;
+    e__ = launch_k(norm_rows_warp_kernel<T>, dim3(want < cap ? want : cap), dim3(kNormWarpThreads), 0, st, pdl, na);
+  } else if (wide) e__ = launch_k(norm_rope_cache_kernel<T, 0>, dim3(n), dim3(kNormThreads), 0, st, pdl, na);
   else if (l.splits0 == 1) e__ = launch_k(norm_rope_cache_kernel<T, 1>, dim3(n), dim3(kNormThreads), 0, st, pdl, na);
   else e__ = launch_k(norm_rope_cache_kernel<T, 8>, dim3(n), dim3(kNormThreads), 0, st, pdl, na);
   MLAPO_CHECK_LAUNCH("norm_rope_cache");

@@ -409,4 +409,153 @@ __global__ void __launch_bounds__(kNormThreads, kMaxSplits <= 1 ? 4 : 2) norm_ro
 }
 
 
+// ---- prefill form of k3: one WARP per token row, behind the dequantising MM1 (the row is read as act y0 [N, 2112]).
+// The CTA-per-token kernel above keeps four rows in flight per SM, which is right for decode (every SM has a row at once) and
+// latency-bound for thousands of rows; here a warp owns a row end to end (no shared memory, no CTA barrier), 16+ rows are in
+// flight per SM and the norm parameters are fetched once per warp.  Same arithmetic, operation by operation, as norm_token().
+// Lane l holds k_nope vectors l, l+32 (8 columns each), k_pe vector l (l < 8) and q_a vectors l + 32 j, j < 6.
+constexpr int kNormWarpThreads = 256;
+template <class T>
+__global__ void __launch_bounds__(kNormWarpThreads, 2) norm_rows_warp_kernel(NormArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int gw = blockIdx.x * (kNormWarpThreads / 32) + (threadIdx.x >> 5), warps_total = gridDim.x * (kNormWarpThreads / 32);
+  if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 0);
+  ptx::griddep_launch_dependents();
+  uint4 g2[2];   // gamma2 stays in registers; gamma1 / beta1 (12 vectors per lane) are re-read per row from L1 (volatile asm loads,
+                 // so that the compiler does not hoist them into 48 registers and spill)
+#pragma unroll
+  for (int j = 0; j < 2; ++j) g2[j] = reinterpret_cast<const uint4*>(a.gamma2)[lane + 32 * j];
+  const uint4* const g1p = reinterpret_cast<const uint4*>(a.gamma1) + lane;
+  const uint4* const b1p = reinterpret_cast<const uint4*>(a.beta1) + lane;
+  const bool per_token = a.tok_scale1 != nullptr;
+  const float qs1 = per_token ? 1.f : Act<T>::to_f(reinterpret_cast<const T*>(a.quant_scale1)[0]);
+  const float zp1 = per_token ? 0.f : (float)a.quant_offset1[0];
+  const float cs_kv = a.cache_mode == MLAPO_CACHE_INT8_NZ ? Act<T>::to_f(reinterpret_cast<const T*>(a.ctkv_scale)[0]) : 1.f;
+  ptx::griddep_wait();  // y0 (and, per token, nothing else) comes from the MM1 kernel
+  if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 14);
+  for (int t = gw; t < a.n_tokens; t += warps_total) {
+    const T* row = reinterpret_cast<const T*>(a.y0_in) + (long long)t * MLAPO_MM1_OUT;
+    uint4 xn[2], xq[6], xpe = make_uint4(0, 0, 0, 0), cs_v = xpe, sn_v = xpe;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) xn[j] = *reinterpret_cast<const uint4*>(row + 8 * (lane + 32 * j));
+#pragma unroll
+    for (int j = 0; j < 6; ++j) xq[j] = *reinterpret_cast<const uint4*>(row + 576 + 8 * (lane + 32 * j));
+    if (lane < 8) {
+      xpe = *reinterpret_cast<const uint4*>(row + 512 + 8 * lane);
+      cs_v = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.cos) + (long long)t * 64)[lane];
+      sn_v = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.sin) + (long long)t * 64)[lane];
+    }
+    const int slot = a.slots[t];
+    // ---- row sums of squares, accumulated in fp64 (order-free), rounded once to fp32
+    double ssn = 0.0, ssq = 0.0;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      float f[8];
+      unpack8<T>(xn[j], f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) ssn += (double)f[e] * (double)f[e];
+    }
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      float f[8];
+      unpack8<T>(xq[j], f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) ssq += (double)f[e] * (double)f[e];
+    }
+    ssn = warp_sum_f64(ssn);
+    ssq = warp_sum_f64(ssq);
+    const bool slot_ok = slot >= 0 && (long long)slot < a.cache_slots;
+    const int blk = slot >> 7, r128 = slot & 127;  // NZ modes: block size 128
+    // ---- S8: k_nope = act(x * rsqrt(mean+eps) * gamma2)
+    {
+      const float var = __fdiv_rn(__double2float_rn(ssn), 512.f);
+      const float rs = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var, 1e-6f)));
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int col = 8 * (lane + 32 * j);
+        float x[8], g[8], y[8];
+        unpack8<T>(xn[j], x);
+        unpack8<T>(g2[j], g);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) y[e] = __fmul_rn(__fmul_rn(x[e], rs), g[e]);
+        if (slot_ok) {
+          if (a.cache_mode == MLAPO_CACHE_INT8_NZ) {
+            int q[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) q[e] = sat_i8(__fdiv_rn(y[e], cs_kv));
+            int8_t* dst = reinterpret_cast<int8_t*>(a.kv_cache) + (long long)blk * (128 * 512) + (col >> 5) * (128 * 32) + r128 * 32 + (col & 31);
+            ptx::st_global_v2(dst, pack4_i8(q[0], q[1], q[2], q[3]), pack4_i8(q[4], q[5], q[6], q[7]));
+          } else {
+            T* base = reinterpret_cast<T*>(a.kv_cache);
+            T* dst = a.cache_mode == MLAPO_CACHE_NZ ? base + (long long)blk * (128 * 512) + (col >> 4) * (128 * 16) + r128 * 16 + (col & 15)
+                                                    : base + (long long)slot * 512 + col;
+            ptx::st_global_v4(dst, Act<T>::pack(y[0], y[1]), Act<T>::pack(y[2], y[3]), Act<T>::pack(y[4], y[5]), Act<T>::pack(y[6], y[7]));
+          }
+        }
+      }
+    }
+    // ---- S7: k_pe = rope(x[512:576]); lanes l and l^4 (l < 8) hold partner halves
+    {
+      float x[8], xp[8];
+      unpack8<T>(xpe, x);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) xp[e] = __shfl_xor_sync(0xffffffffu, x[e], 4);
+      if (lane < 8 && slot_ok) {
+        const int c = lane * 8;
+        float cs[8], sn[8], y[8];
+        unpack8<T>(cs_v, cs);
+        unpack8<T>(sn_v, sn);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float rot = lane < 4 ? -xp[e] : xp[e];
+          y[e] = __fadd_rn(__fmul_rn(x[e], cs[e]), __fmul_rn(rot, sn[e]));
+        }
+        T* base = reinterpret_cast<T*>(a.kv_cache_rope);
+        T* dst = a.cache_mode == MLAPO_CACHE_KROPE_CTKV ? base + (long long)slot * 64 + c
+                                                        : base + (long long)blk * (128 * 64) + (c >> 4) * (128 * 16) + r128 * 16 + (c & 15);
+        ptx::st_global_v4(dst, Act<T>::pack(y[0], y[1]), Act<T>::pack(y[2], y[3]), Act<T>::pack(y[4], y[5]), Act<T>::pack(y[6], y[7]));
+      }
+    }
+    // ---- S4: q_a RMSNorm(+beta) + quant -> a1
+    {
+      const float var = __fdiv_rn(__double2float_rn(ssq), 1536.f);
+      const float rs = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var, 1e-6f)));
+      float inv = 0.f;
+      if (per_token) {  // UNPINNED mode: s1 = max|y| / 127 over the row
+        float amax = 0.f;
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+          float x[8], g[8], b[8];
+          unpack8<T>(xq[j], x);
+          unpack8<T>(ptx::ld_global_nc_v4(g1p + 32 * j), g);
+          unpack8<T>(ptx::ld_global_nc_v4(b1p + 32 * j), b);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) amax = fmaxf(amax, fabsf(__fadd_rn(__fmul_rn(__fmul_rn(x[e], rs), g[e]), b[e])));
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        const float s1 = __fdiv_rn(amax, 127.f);
+        inv = __fdiv_rn(1.f, s1);
+        if (lane == 0) a.tok_scale1[t] = s1;
+      }
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        float x[8], g[8], b[8];
+        unpack8<T>(xq[j], x);
+        unpack8<T>(ptx::ld_global_nc_v4(g1p + 32 * j), g);
+        unpack8<T>(ptx::ld_global_nc_v4(b1p + 32 * j), b);
+        int q[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float yq = __fadd_rn(__fmul_rn(__fmul_rn(x[e], rs), g[e]), b[e]);
+          q[e] = per_token ? sat_i8(__fmul_rn(yq, inv)) : sat_i8(__fadd_rn(__fdiv_rn(yq, qs1), zp1));
+        }
+        ptx::st_global_v2(a.a1 + (long long)t * MLAPO_Q_LORA + 8 * (lane + 32 * j), pack4_i8(q[0], q[1], q[2], q[3]), pack4_i8(q[4], q[5], q[6], q[7]));
+      }
+    }
+  }
+  if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(a.tl, 15);
+}
+
+
 }  // namespace mlapo
