@@ -312,3 +312,31 @@ def test_c5_kimi_k2_ragged_slots(mode, cuda_device):
     res, ocase, _ = hz.compare(case, PT, g, taps)
     q0_close = mode == "int8_nzcache" or torch.allclose(g["q_out0"].cpu().float(), ocase.t["q_out0"].float(), rtol=1e-2, atol=1e-3)
     check(res, case, PT, q0_close)
+
+
+@pytest.mark.parametrize("shape", [(130, 100, 0), (64, 64, 0), (40, 4, 0), (130, 4, 8192)], ids=["one_cta_per_unit", "split2", "split4", "pair_q"])
+def test_large_accumulators_take_the_exact_conversion(shape, cuda_device):
+    """The CTA-pair q kernel turns int32 accumulators into fp32 with an integer add and a float subtract, exact while
+    |acc + bias| < 2^22, and redoes a batch with the converting instruction when a value is larger (the other q kernels always
+    convert; the same trick made them slower).  Random data never gets there (|acc| of MM2 is a few 10^5), so this case forces it: the q_a norm is made to produce the constant 100 (gamma1 = 0, beta1 = 100), which
+    quantises to +127 in every column, and half of W_UQ's rows are all +127 / all -128: |acc1| = 1536 * 127 * 127 = 24.8 M in
+    those columns, small in the others — both paths inside one warp."""
+    n, h, dbg = shape
+    case = orc.gen_case(N=n, H=h, D=2048, dtype=torch.bfloat16, cache_mode="krope_ctkv", seed=17, num_blocks=4, full_range_weights=True)
+    t = case.t
+    t["gamma1"].zero_()
+    t["beta1"].fill_(100.0)
+    t["quant_scale1"].fill_(0.5)
+    t["quant_offset1"].zero_()
+    w = t["wuq_nd"]
+    rows = torch.arange(w.shape[0])
+    w[rows % 4 == 0] = 127
+    w[rows % 4 == 1] = -128
+    t["wuq"] = orc.nz_pack(w)
+    t["descale1"] = torch.full_like(t["descale1"], 3e-8)      # keeps y1 = acc * descale within a few units
+    g, taps = hz.run_cuda(case, cuda_device, quant_mode=PT, debug="tap", extra_flags=dbg)
+    res, ocase, otaps = hz.compare(case, PT, g, taps)
+    assert int(otaps["acc1"].abs().max()) > (1 << 24) and int((otaps["acc1"].abs() < (1 << 20)).sum()) > 0
+    assert int(otaps["a1"].min()) == 127
+    q0_close = torch.allclose(g["q_out0"].cpu().float(), ocase.t["q_out0"].float(), rtol=1e-2, atol=1e-3)
+    check(res, case, PT, q0_close)
