@@ -18,7 +18,8 @@ def _params(cabi, g, case, flags=0):
 
 
 @pytest.mark.parametrize("flags", [0, 1], ids=["default_start", "input_complete"])
-@pytest.mark.parametrize("shape", [(256, 128, 7168, "krope_ctkv"), (64, 16, 7168, "int8_nzcache"), (1100, 40, 7168, "nzcache")],
+@pytest.mark.parametrize("shape", [(256, 128, 7168, "krope_ctkv"), (64, 16, 7168, "int8_nzcache"), (1100, 40, 7168, "nzcache"),
+                                   (8, 16, 7168, "krope_ctkv")],
                          ids=lambda s: "n%d_h%d_d%d_%s" % s)
 def test_alternating_inputs_back_to_back(shape, flags, cuda_device):
     """flags = MLAPO_FLAG_INPUT_COMPLETE: the quantise kernel starts under the previous call's tail (what bench.py times); 0: every
@@ -53,7 +54,8 @@ def test_alternating_inputs_back_to_back(shape, flags, cuda_device):
             assert torch.equal(g[k], want), (r, k, int((g[k] != want).sum()))
 
 
-def test_waits_for_a_producer_that_releases_its_dependents_early(cuda_device):
+@pytest.mark.parametrize("n_tokens", [64, 8], ids=["n64", "n8"])
+def test_waits_for_a_producer_that_releases_its_dependents_early(n_tokens, cuda_device):
     """hiddenState (and cos / sin / slot_mapping) are written by a kernel that triggers programmatic launch completion FIRST and
     stores ~100 us LATER — what a PDL-enabled norm kernel in front of this operator may do.  With the default flags the operator's
     first kernel waits for that producer to complete before it reads anything, so the results equal those of a call on finished
@@ -66,7 +68,7 @@ def test_waits_for_a_producer_that_releases_its_dependents_early(cuda_device):
         pytest.skip("tools/microbench/libmlapo_microbench.so not built")
     mb = ctypes.CDLL(path)
     mb.mlapo_mb_late_copy.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_longlong, ctypes.c_void_p]
-    case = orc.gen_case(N=64, H=16, D=7168, dtype=torch.bfloat16, cache_mode="krope_ctkv", seed=21, num_blocks=8, neg_slot_frac=0.1)
+    case = orc.gen_case(N=n_tokens, H=16, D=7168, dtype=torch.bfloat16, cache_mode="krope_ctkv", seed=21, num_blocks=8, neg_slot_frac=0.1)
     g_ref, _ = hz.run_cuda(case, cuda_device, debug=False, cache_fill=0)
     want = {k: g_ref[k].clone() for k in ("q_out0", "q_out1", "kv_cache", "kv_cache_rope")}
     g = hz.to_device(case, cuda_device)

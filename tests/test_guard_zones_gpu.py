@@ -28,6 +28,7 @@ def intact(buf, nbytes):
 
 SHAPES = [  # N, H, D, cache_mode, quant_mode, debug flags
     (8, 16, 7168, "krope_ctkv", PT, 0),            # 4 CTAs per (head, tile) unit
+    (16, 2, 2048, "int8_nzcache", PT, 0),
     (1, 32, 7168, "nzcache", PT, 0),
     (127, 64, 7168, "int8_nzcache", PT, 0),        # 2 CTAs per unit, ragged last rows
     (129, 16, 7168, "nzcache", TOK, 0),            # one row in the second token tile
