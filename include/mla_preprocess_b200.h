@@ -324,7 +324,8 @@ int mlapo_launches_per_call(const MlapoParams* p);
  * bit3 = per-CTA clock marks (timeline region), bit11 = log stuck barrier waits to a host-mapped buffer before trapping,
  * bit12 = the quantise kernel also asks for the call's weights in L2 (measured slower; kept for A/B), bit13 = use the CTA-pair
  * q kernel for every call of more than 128 tokens, bit14 = one CTA per (head, token tile) unit even when there are few units,
- * bit16 = MM1 on single CTAs (8 K-splits) where CTA pairs (4 K-splits) would run, bit17 = the CTA-per-row norm kernel at prefill sizes.
+ * bit16 = MM1 on single CTAs (8 K-splits) where CTA pairs (4 K-splits) would run, bit17 = the CTA-per-row norm kernel at prefill sizes,
+ * bit19 = 128-column weight tiles for MM1 on CTA pairs where 256-column tiles would be used (more than 256 tokens).
  * Returns the previous flags.
  */
 int mlapo_set_debug_flags(int flags);

@@ -167,10 +167,13 @@ static cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_
 // Calls of more than 128 tokens run MM1 on CTA pairs (mlapo_mm1_pair.cuh): a work item then occupies two SMs.  Debug bit16
 // keeps the single-CTA form (A/B).
 static bool mm1_on_pairs(int n_tokens) { return n_tokens > kBlockM && !(g_debug_flags & 65536); }
+// ... with 128-column weight tiles for one block of 256 tokens, 256-column tiles for more (debug bit19 keeps 128)
+static int mm1_pair_bn(int n_tokens) { return (n_tokens > 2 * kBlockM && !(g_debug_flags & 524288)) ? kMm1BlockNWide : kMm1BlockN; }
 
 static int choose_splits0(int n_tokens, int hidden_dim) {
   const int m_super = n_tokens > 0 ? (n_tokens + 2 * kBlockM - 1) / (2 * kBlockM) : 1;  // work items cover up to 256 tokens
-  const int n_tiles = (MLAPO_MM1_OUT + kMm1BlockN - 1) / kMm1BlockN;                     // 17
+  const int bn = mm1_on_pairs(n_tokens) ? mm1_pair_bn(n_tokens) : kMm1BlockN;
+  const int n_tiles = (MLAPO_MM1_OUT + bn - 1) / bn;                                     // 17 (or 9)
   const int kb_total = hidden_dim / kBlockKBytes;
   int s = (mm1_on_pairs(n_tokens) ? num_sms() / 2 : num_sms()) / (n_tiles * m_super);  // one wave of CTAs (or CTA pairs)
   if (s < 1) s = 1;
@@ -336,6 +339,7 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
       if (!done[dev].load(std::memory_order_acquire)) {
         cudaFuncSetAttribute(quant_hidden_kernel<T, 1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         cudaFuncSetAttribute(quant_hidden_kernel<T, 2>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(quant_hidden_kernel<T, 4>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         done[dev].store(true, std::memory_order_release);
       }
     }
@@ -346,6 +350,10 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
                      reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0, input_complete);
     } else if (nvec <= wave) {  // two vectors per thread, both loads in flight
       e__ = launch_k(quant_hidden_kernel<T, 2>, dim3((unsigned)((nvec + 2 * qt - 1) / (2 * qt))), dim3(qt), 0, st, pdl,
+                     reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
+                     reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0, input_complete);
+    } else if (nvec <= 2 * wave) {  // four vectors per thread, still in the small blocks (up to ~670 tokens at D = 7168)
+      e__ = launch_k(quant_hidden_kernel<T, 4>, dim3((unsigned)((nvec + 4 * qt - 1) / (4 * qt))), dim3(qt), 0, st, pdl,
                      reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
                      reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0, input_complete);
     } else {                 // prefill sizes: grid-stride, 4 independent loads in flight per thread
@@ -371,12 +379,21 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
                      tm_a0, tm_wdqkv, tm_part, tm_y0, dq, n, d / kBlockKBytes, tl1);
       g_kernel_names[1] = "mm1_dequant";
     } else if (mm1_on_pairs(n)) {
-      static DoneFlag done[kMaxDevices];
-      if ((rc = set_smem_attr(mm1_pair_kernel, kM1PSmemBytes, &done[dev], "mm1_pair"))) return rc;
-      CUtensorMap tm_wh;  // this form fetches the weight tile in two halves of 64 rows, one per CTA of the pair
-      if ((rc = make_tmap(&tm_wh, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wdqkv_km, MLAPO_MM1_OUT, d, d, kM1PHalfB, 128))) return rc;
-      e__ = launch_k(mm1_pair_kernel, dim3(2 * n_tiles, l.splits0, (n + 255) / 256), dim3(kGemmThreads), kM1PSmemBytes, st, pdl,
-                     tm_a0, tm_wh, tm_part, n, d / kBlockKBytes, tl1);
+      const int pbn = mm1_pair_bn(n), p_tiles = (MLAPO_MM1_OUT + pbn - 1) / pbn;
+      CUtensorMap tm_wh;  // this form fetches the weight tile in two halves, one per CTA of the pair
+      if ((rc = make_tmap(&tm_wh, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wdqkv_km, MLAPO_MM1_OUT, d, d, pbn / 2, 128))) return rc;
+      const dim3 pgrid(2 * p_tiles, l.splits0, (n + 255) / 256);
+      if (pbn == kMm1BlockN) {
+        static DoneFlag done[kMaxDevices];
+        if ((rc = set_smem_attr(mm1_pair_kernel<kMm1BlockN>, Mm1Pair<kMm1BlockN>::SMEM_BYTES, &done[dev], "mm1_pair<128>"))) return rc;
+        e__ = launch_k(mm1_pair_kernel<kMm1BlockN>, pgrid, dim3(kGemmThreads), Mm1Pair<kMm1BlockN>::SMEM_BYTES, st, pdl, tm_a0, tm_wh, tm_part, n,
+                       d / kBlockKBytes, tl1);
+      } else {
+        static DoneFlag done[kMaxDevices];
+        if ((rc = set_smem_attr(mm1_pair_kernel<kMm1BlockNWide>, Mm1Pair<kMm1BlockNWide>::SMEM_BYTES, &done[dev], "mm1_pair<256>"))) return rc;
+        e__ = launch_k(mm1_pair_kernel<kMm1BlockNWide>, pgrid, dim3(kGemmThreads), Mm1Pair<kMm1BlockNWide>::SMEM_BYTES, st, pdl, tm_a0, tm_wh,
+                       tm_part, n, d / kBlockKBytes, tl1);
+      }
       g_kernel_names[1] = "mm1_pair";
     } else if (n > kBlockM) {
       static DoneFlag done[kMaxDevices];

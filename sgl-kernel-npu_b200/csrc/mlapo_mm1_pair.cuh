@@ -12,21 +12,30 @@
 
 namespace mlapo {
 
-constexpr int kM1PStages = 8;
-constexpr int kM1PHalfB = kMm1BlockN / 2;                               // 64 weight rows per CTA
-constexpr int kM1PStageBytes = kTile16K + kM1PHalfB * kBlockKBytes;      // 24576
-constexpr int kM1PBarOff = kM1PStages * kM1PStageBytes;                  // 196608
-constexpr int kM1PSmemBytes = kM1PBarOff + 256;
-static_assert(kM1PStageBytes % 1024 == 0, "swizzled tiles need 1024-byte alignment");
-static_assert(4 * kTile16K <= kM1PBarOff, "the epilogue stages its four granule tiles in the drained pipeline");
+// BN = 128 (one block of 256 tokens: 17 tiles x 4 K-splits = 68 pairs) or 256 (several token blocks, where the K range of a
+// pair is long and the a0 bytes per weight byte matter more than the partial sums: 9 tiles x 2 blocks x 4 K-splits at 512 tokens).
+template <int BN>
+struct Mm1Pair {
+  static constexpr int HALF_B = BN / 2;                                  // weight rows per CTA
+  static constexpr int STAGE_BYTES = kTile16K + HALF_B * kBlockKBytes;   // 24576 / 32768
+  static constexpr int STAGES = BN == 128 ? 8 : 6;
+  static constexpr int BAR_OFF = STAGES * STAGE_BYTES;                   // 196608 for both
+  static constexpr int SMEM_BYTES = BAR_OFF + 256;
+  static constexpr int GRANULES = BN / 32;                               // 32 int32 columns = one 128-byte row per token
+  static_assert(STAGE_BYTES % 1024 == 0, "swizzled tiles need 1024-byte alignment");
+  static_assert(GRANULES * kTile16K <= BAR_OFF, "the epilogue stages its granule tiles in the drained pipeline");
+};
 
+template <int BN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 mm1_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                 const __grid_constant__ CUtensorMap tm_p, int m_total, int kb_total, long long* tl) {
   if (threadIdx.x == 0) { tl_mark_global(tl, 0); tl_mark(tl, 1); }
+  using P = Mm1Pair<BN>;
+  constexpr int kM1PStages = P::STAGES, kM1PStageBytes = P::STAGE_BYTES, kM1PHalfB = P::HALF_B;
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
-  uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + kM1PBarOff);
+  uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + P::BAR_OFF);
   uint64_t* const full_bar = bars;                    // [8] leader's copy used: TMA of both CTAs -> MMA
   uint64_t* const empty_bar = bars + kM1PStages;      // [8] MMA commit (both CTAs) -> TMA
   uint64_t* const done_bar = bars + 2 * kM1PStages;   // [1] MMA commit (both CTAs) -> epilogue
@@ -34,7 +43,7 @@ mm1_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = ptx::cluster_ctarank();
   const bool leader = rank == 0;
-  const int n0 = (int)(blockIdx.x >> 1) * kMm1BlockN;
+  const int n0 = (int)(blockIdx.x >> 1) * BN;
   const int split = blockIdx.y, splits = gridDim.y;
   const int m0 = blockIdx.z * (2 * kBlockM) + (int)rank * kBlockM;      // this CTA's token tile
   const int kb0 = (int)(((long long)split * kb_total) / splits);
@@ -48,7 +57,7 @@ mm1_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
     ptx::fence_mbar_init();
   }
   if (warp == 1) {
-    ptx::tmem_alloc_pair(ptx::smem_u32(tmem_slot), kMm1BlockN);
+    ptx::tmem_alloc_pair(ptx::smem_u32(tmem_slot), BN);
     ptx::tmem_relinquish_pair();
   }
   ptx::tc_fence_before();
@@ -92,7 +101,7 @@ mm1_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (leader CTA, one thread, for both SMs)
     if (leader) {
-      constexpr uint32_t idesc = ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, 2 * kBlockM, kMm1BlockN);
+      constexpr uint32_t idesc = ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, 2 * kBlockM, BN);
       uint32_t stage = 0, phase = 0;
       for (int i = 0; i < nkb; ++i) {
         ptx::mbar_wait(ptx::smem_u32(full_bar + stage), phase);
@@ -118,8 +127,8 @@ mm1_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
       __syncwarp();
     }
   } else if (warp < 10) {
-    // ------------------------------------------------------------------ epilogue: this CTA's 128 rows x 128 int32 columns
-    // Two groups of four warps, two 32-column granules each: TMEM -> swizzled smem tile -> its own TMA store.
+    // ------------------------------------------------------------------ epilogue: this CTA's 128 rows x BN int32 columns
+    // Two groups of four warps, half of the 32-column granules each: TMEM -> swizzled smem tile -> its own TMA store.
     const int quarter = warp & 3, group = (warp - 2) >> 2;
     const int row = quarter * 32 + lane;
     const uint32_t t_base = tmem_acc + ((uint32_t)(quarter * 32) << 16);
@@ -130,8 +139,8 @@ mm1_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
     if (issuer && group == 0) tl_mark(tl, 6);
     __syncwarp();
 #pragma unroll 1
-    for (int j = 0; j < 2; ++j) {
-      const int g = group * 2 + j;
+    for (int j = 0; j < P::GRANULES / 2; ++j) {
+      const int g = group * (P::GRANULES / 2) + j;
       uint32_t r[32];
       ptx::tmem_ld_32x32b_x32(t_base + g * 32, r);
       ptx::tmem_ld_wait();
@@ -158,7 +167,7 @@ mm1_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
   __syncthreads();
   ptx::cluster_arrive();
   ptx::cluster_wait();
-  if (warp == 1) ptx::tmem_dealloc_pair(tmem_acc, kMm1BlockN);
+  if (warp == 1) ptx::tmem_dealloc_pair(tmem_acc, BN);
   if (threadIdx.x == 32) { tl_mark(tl, 9); tl_mark_global(tl, 15); }
 }
 

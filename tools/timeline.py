@@ -17,6 +17,7 @@ QF = ["gtimer", "start", "prologue", "upstream", "first_full", "last_full", "mm2
 
 def main(workload="c2", pdl=False):
     n, h, d, cache_mode, _ = bench.WORKLOADS[workload]
+    h = int(os.environ.get("MLAPO_TL_HEADS", h))   # e.g. 16 with c4: one rank of the TP8 split
     dev = torch.device("cuda:0")
     gen = torch.Generator(device=dev).manual_seed(1)
     sets = [bench.make_weight_set(torch, h, d, dev, gen) for _ in range(3)]
