@@ -325,11 +325,12 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
         {
           const uint4* cp = reinterpret_cast<const uint4*>(cos_row);
           const uint4* sp = reinterpret_cast<const uint4*>(sin_row);
-#pragma unroll
-          for (int j = 0; j < 2; ++j) {
-            cs4[j] = ptx::ld_global_nc_v4(cp + j); sn4[j] = ptx::ld_global_nc_v4(sp + j);
-            cs4[2 + j] = ptx::ld_global_nc_v4(cp + 4 + j); sn4[2 + j] = ptx::ld_global_nc_v4(sp + 4 + j);
-          }
+          // 32 bytes per request: a warp's rows are 32 different lines either way, so half the requests is half the time the
+          // load/store unit spends on them (it also carries the drain set's staging stores)
+          ptx::ld_global_nc_v8(cp, cs4[0], cs4[1]);
+          ptx::ld_global_nc_v8(sp, sn4[0], sn4[1]);
+          ptx::ld_global_nc_v8(cp + 4, cs4[2], cs4[3]);
+          ptx::ld_global_nc_v8(sp + 4, sn4[2], sn4[3]);
         }
         ptx::fence_proxy_async_smem();
         ptx::tc_fence_before();
@@ -343,6 +344,7 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
         // RoPE of dims [16g,16g+16) and their partners, 32-byte sectors straight to q_out1 (test_mla:57-67)
         if (valid) {
           T* dst = reinterpret_cast<T*>(q_out1) + ((long long)t * qa.num_heads + head) * MLAPO_ROPE + 16 * g;
+          uint32_t wl[8], wh[8];
 #pragma unroll
           for (int j = 0; j < 2; ++j) {
             float c_lo[8], s_lo[8], c_hi[8], s_hi[8];
@@ -350,7 +352,6 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
             unpack8<T>(sn4[j], s_lo);
             unpack8<T>(cs4[2 + j], c_hi);
             unpack8<T>(sn4[2 + j], s_hi);
-            uint32_t wl[4], wh[4];
 #pragma unroll
             for (int v = 0; v < 4; ++v) {
               const int i0 = 8 * j + 2 * v, i1 = i0 + 1;
@@ -358,12 +359,12 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
               const float a1 = __fadd_rn(__fmul_rn(xl[i1], c_lo[2 * v + 1]), __fmul_rn(-xh[i1], s_lo[2 * v + 1]));
               const float b0 = __fadd_rn(__fmul_rn(xh[i0], c_hi[2 * v]), __fmul_rn(xl[i0], s_hi[2 * v]));
               const float b1 = __fadd_rn(__fmul_rn(xh[i1], c_hi[2 * v + 1]), __fmul_rn(xl[i1], s_hi[2 * v + 1]));
-              wl[v] = Act<T>::pack(a0, a1);
-              wh[v] = Act<T>::pack(b0, b1);
+              wl[4 * j + v] = Act<T>::pack(a0, a1);
+              wh[4 * j + v] = Act<T>::pack(b0, b1);
             }
-            ptx::st_global_v4(dst + 8 * j, wl[0], wl[1], wl[2], wl[3]);
-            ptx::st_global_v4(dst + 32 + 8 * j, wh[0], wh[1], wh[2], wh[3]);
           }
+          ptx::st_global_v8(dst, wl[0], wl[1], wl[2], wl[3], wl[4], wl[5], wl[6], wl[7]);
+          ptx::st_global_v8(dst + 32, wh[0], wh[1], wh[2], wh[3], wh[4], wh[5], wh[6], wh[7]);
         }
         tl_trace(tl, tr, tb + 14);
       }
