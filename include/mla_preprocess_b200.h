@@ -326,7 +326,6 @@ int mlapo_launches_per_call(const MlapoParams* p);
  * q kernel for every call of more than 128 tokens, bit14 = one CTA per (head, token tile) unit even when there are few units,
  * bit16 = MM1 on single CTAs (8 K-splits) where CTA pairs (4 K-splits) would run, bit17 = the CTA-per-row norm kernel at prefill sizes,
  * bit19 = 128-column weight tiles for MM1 on CTA pairs where 256-column tiles would be used (more than 256 tokens).
- * bit20 = 256-token work units for the q path on CTA pairs where 512-token units would be used (more than 256 tokens).
  * Returns the previous flags.
  */
 int mlapo_set_debug_flags(int flags);

@@ -41,7 +41,6 @@
 #include "mlapo_mm1_pair.cuh"
 #include "mlapo_q.cuh"
 #include "mlapo_q_pair.cuh"
-#include "mlapo_q_pair_wide.cuh"
 #include "mlapo_format.cuh"
 #include "mlapo_bmt.cuh"
 #include "mlapo_slots.cuh"
@@ -437,28 +436,6 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
     if ((rcx = make_tmap(&tm_wuqp, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p->wuq_km, (uint64_t)h * MLAPO_Q_HEAD, MLAPO_Q_LORA, MLAPO_Q_LORA,
                          kPHalfB, 128))) return rcx;
     const int max_pairs = num_sms() / 2;
-    if (n > 256 && !(g_debug_flags & 1048576)) {
-      // k7w: 512 tokens per unit, every weight byte used by two token sets (debug bit20 keeps the 256-token units for A/B runs)
-      CUtensorMap tm_a1w, tm_cos, tm_sin;
-      if ((rcx = make_tmap(&tm_a1w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, a1, n, MLAPO_Q_LORA, MLAPO_Q_LORA, 2 * kBlockM, 128))) return rcx;
-      if ((rcx = make_tmap(&tm_cos, act_dt, 2, p->cos, n, MLAPO_ROPE, MLAPO_ROPE * 2, kBlockM, 64))) return rcx;
-      if ((rcx = make_tmap(&tm_sin, act_dt, 2, p->sin, n, MLAPO_ROPE, MLAPO_ROPE * 2, kBlockM, 64))) return rcx;
-      const int w_units = h * ((n + 511) / 512);
-      dim3 wgrid(2 * (w_units < max_pairs ? w_units : max_pairs));
-      if (int8_out) {
-        static DoneFlag done[kMaxDevices];
-        if ((rc = set_smem_attr(q_pair_wide_kernel<T, true>, kPWSmemBytes, &done[dev], "q_pair_wide<int8>"))) return rc;
-        e__ = launch_k(q_pair_wide_kernel<T, true>, wgrid, dim3(kPThreads), kPWSmemBytes, st, pdl, tm_a1w, tm_wuqp, tm_wuk, tm_o0, tm_cos, tm_sin, tm_o1, qa, w_units, tl4);
-      } else {
-        static DoneFlag done[kMaxDevices];
-        if ((rc = set_smem_attr(q_pair_wide_kernel<T, false>, kPWSmemBytes, &done[dev], "q_pair_wide"))) return rc;
-        e__ = launch_k(q_pair_wide_kernel<T, false>, wgrid, dim3(kPThreads), kPWSmemBytes, st, pdl, tm_a1w, tm_wuqp, tm_wuk, tm_o0, tm_cos, tm_sin, tm_o1, qa, w_units, tl4);
-      }
-      MLAPO_CHECK_LAUNCH("q_pair_wide");
-      g_kernel_names[3] = "q_pair";
-      record_event(4, st);
-      return MLAPO_OK;
-    }
     dim3 grid(2 * (q_units < max_pairs ? q_units : max_pairs));
     if (int8_out) {
       static DoneFlag done[kMaxDevices];

@@ -299,12 +299,19 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
       {
         const T* cp = reinterpret_cast<const T*>(qa.cos) + (long long)tc * 64;
         const T* sp = reinterpret_cast<const T*>(qa.sin) + (long long)tc * 64;
+        // (32 bytes per request where the run allows: every row of a warp is a different line, so the number of requests is
+        // what the load/store unit pays for — and the TMA issue and the staging stores queue behind it)
         if constexpr (kSplit == 1) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            cs[j] = ptx::ld_global_nc_v4(reinterpret_cast<const uint4*>(cp) + j);
-            sn[j] = ptx::ld_global_nc_v4(reinterpret_cast<const uint4*>(sp) + j);
+          for (int j = 0; j < 8; j += 2) {
+            ptx::ld_global_nc_v8(reinterpret_cast<const uint4*>(cp) + j, cs[j], cs[j + 1]);
+            ptx::ld_global_nc_v8(reinterpret_cast<const uint4*>(sp) + j, sn[j], sn[j + 1]);
           }
+        } else if constexpr (G == 16) {
+          ptx::ld_global_nc_v8(cp + z * G, cs[0], cs[1]);
+          ptx::ld_global_nc_v8(sp + z * G, sn[0], sn[1]);
+          ptx::ld_global_nc_v8(cp + 32 + z * G, cs[2], cs[3]);
+          ptx::ld_global_nc_v8(sp + 32 + z * G, sn[2], sn[3]);
         } else {
 #pragma unroll
           for (int j = 0; j < G / 8; ++j) {
@@ -446,6 +453,7 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
         }
         if (t < qa.m_total) {
           T* const o_lo = reinterpret_cast<T*>(qa.q_out1) + ((long long)t * qa.num_heads + head) * MLAPO_ROPE + z * G;
+          uint32_t wlo[G / 2], whi[G / 2];
 #pragma unroll
           for (int v = 0; v < G / 8; ++v) {
             float c_lo[8], s_lo[8], c_hi[8], s_hi[8];
@@ -453,7 +461,8 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
             unpack8<T>(sn[v], s_lo);
             unpack8<T>(cs[G / 8 + v], c_hi);
             unpack8<T>(sn[G / 8 + v], s_hi);
-            uint32_t wl[4], wh[4];
+            uint32_t* const wl = wlo + 4 * v;
+            uint32_t* const wh = whi + 4 * v;
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
               const int i0 = v * 8 + 2 * u, i1 = i0 + 1;
@@ -465,8 +474,13 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
               wl[u] = Act<T>::pack(a0, a1);
               wh[u] = Act<T>::pack(b0, b1);
             }
-            ptx::st_global_v4(o_lo + v * 8, wl[0], wl[1], wl[2], wl[3]);
-            ptx::st_global_v4(o_lo + 32 + v * 8, wh[0], wh[1], wh[2], wh[3]);
+          }
+          if constexpr (G == 16) {
+            ptx::st_global_v8(o_lo, wlo[0], wlo[1], wlo[2], wlo[3], wlo[4], wlo[5], wlo[6], wlo[7]);
+            ptx::st_global_v8(o_lo + 32, whi[0], whi[1], whi[2], whi[3], whi[4], whi[5], whi[6], whi[7]);
+          } else {
+            ptx::st_global_v4(o_lo, wlo[0], wlo[1], wlo[2], wlo[3]);
+            ptx::st_global_v4(o_lo + 32, whi[0], whi[1], whi[2], whi[3]);
           }
         }
       }

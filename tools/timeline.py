@@ -103,15 +103,7 @@ def main(workload="c2", pdl=False):
                   f" CTA end p10/p50/p90/max {np.percentile(e, 10):.2f} {np.median(e):.2f} {np.percentile(e, 90):.2f} {e.max():.2f}")
         g = a[:, 0]
         print(f"   CTA start skew (globaltimer ns): p50-min {np.median(g) - g.min():.0f}  max-min {g.max() - g.min():.0f}")
-    if qname == "q_pair" and n > 256 and not (int(os.environ.get("MLAPO_EXTRA_FLAGS", "0")) & 1048576):
-        tr = tl[1][1024:1024 + 4].reshape(-1)
-        names = ["unit", "mm2_done", "nope_deq", "rope_deq", "st_wait", "g_bar", "rope_st"] + [f"c{c}:{w}" for c in range(4) for w in ("full", "ld", "wait_read", "bar", "staged", "stored")]
-        tr = tl[1][1024:1024 + 8].reshape(-1)
-        for base in (0, 32):
-            print(f"wide-unit trace, unit 2, group {base // 16} (cycles since group 0's unit start): " + " ".join(f"{names[j]}={tr[base + j] - tr[0]}" for j in range(len(names))))
-        print("absorb issuer, unit 2: waits passed for (chunk, set) " + " ".join(f"c{c}={tr[64 + 2 * c] - tr[0]}" for c in range(4)))
-        print(f"MM2 issuer: unit 2 regions free at {tr[72] - tr[0]}, unit 3 at {tr[73] - tr[0]}")
-    elif qname == "q_pair":
+    if qname == "q_pair":
         tr = tl[1][1024:1024 + 8].reshape(-1)
         names = ["mm2_done", "qn_free", "ld0", "deq0", "ld1", "deq1", "ld2", "deq2", "ld3", "deq3", "rope_deq", "fence", "g_bar", "arrive", "rope_st", "fetch"]
         for it in range(2):
