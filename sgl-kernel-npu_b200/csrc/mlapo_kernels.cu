@@ -222,6 +222,19 @@ static int compute_layout(const MlapoParams* p, MlapoWorkspaceLayout* l) {
     if (e__ != cudaSuccess) return fail(MLAPO_ERR_CUDA, "%s: %s", name, cudaGetErrorString(e__));   \
   } while (0)
 
+// Resident blocks per SM of a kernel without dynamic shared memory, cached per device at the call site (`slot` = a static
+// std::atomic<int>[kMaxDevices]).  Grid-stride kernels are launched with exactly one wave: a second, partial wave of blocks that
+// each take the same share of the rows would run at a fraction of the occupancy for as long as the first.
+template <class K>
+static int resident_blocks(K kern, int threads, std::atomic<int>* slot, int fallback) {
+  int v = slot->load(std::memory_order_relaxed);
+  if (!v) {
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, kern, threads, 0) != cudaSuccess || v <= 0) { cudaGetLastError(); v = fallback; }
+    slot->store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
+
 // Shared-memory opt-in of one kernel instantiation, once per device.  `done` is a per-call-site latch indexed by device ordinal;
 // two threads racing on the first call both set the (idempotent) attribute and both store `true`.
 using DoneFlag = std::atomic<bool>;
@@ -356,8 +369,9 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
       e__ = launch_k(quant_hidden_kernel<T, 4>, dim3((unsigned)((nvec + 4 * qt - 1) / (4 * qt))), dim3(qt), 0, st, pdl,
                      reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
                      reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0, input_complete);
-    } else {                 // prefill sizes: grid-stride, 4 independent loads in flight per thread
-      e__ = launch_k(quant_hidden_kernel<T, 4>, dim3(num_sms() * 8), dim3(256), 0, st, pdl,
+    } else {                 // prefill sizes: grid-stride over one resident wave, 4 independent loads in flight per thread
+      static std::atomic<int> occ[kMaxDevices];
+      e__ = launch_k(quant_hidden_kernel<T, 4>, dim3(num_sms() * resident_blocks(quant_hidden_kernel<T, 4>, 256, &occ[dev], 4)), dim3(256), 0, st, pdl,
                      reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
                      reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0, input_complete);
     }
@@ -413,7 +427,9 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   // ---- k3: norms, quant, rope, cache scatter
   if (wide && !(g_debug_flags & 131072)) {  // prefill: one warp per row of the dequantised y0 (debug bit17 keeps the CTA-per-row form)
     const int rows_per_block = kNormWarpThreads / 32;
-    const int want = (n + rows_per_block - 1) / rows_per_block, cap = num_sms() * 4;
+    static std::atomic<int> occ[kMaxDevices];
+    const int want = (n + rows_per_block - 1) / rows_per_block;
+    const int cap = num_sms() * resident_blocks(norm_rows_warp_kernel<T>, kNormWarpThreads, &occ[dev], 2);
     e__ = launch_k(norm_rows_warp_kernel<T>, dim3(want < cap ? want : cap), dim3(kNormWarpThreads), 0, st, pdl, na);
   } else if (wide) e__ = launch_k(norm_rope_cache_kernel<T, 0>, dim3(n), dim3(kNormThreads), 0, st, pdl, na);
   else if (l.splits0 == 1) e__ = launch_k(norm_rope_cache_kernel<T, 1>, dim3(n), dim3(kNormThreads), 0, st, pdl, na);
