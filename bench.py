@@ -870,7 +870,24 @@ def main():
     if args.impl == "reference":
         run_reference(args)
     else:
-        run_ours(args)
+        try:
+            run_ours(args)
+        except Exception:
+            if args.debug_flags & 2048:   # a kernel died with the stuck-wait log on: say which barrier it was waiting on
+                try:
+                    from sgl_kernel_npu import cabi
+                    buf = (ctypes.c_uint * 1024)()
+                    n = cabi.lib.mlapo_debug_read_wait_log(buf, 1024)
+                    print(f"[bench] stuck barrier waits logged: {n}", file=sys.stderr)
+                    seen = {}
+                    for i in range(min(max(n, 0), 255)):   # the log holds the first 255 waiters; group them by warp
+                        key = (buf[1 + 4 * i], buf[2 + 4 * i] // 32, buf[3 + 4 * i] & 0xFFFFFF, buf[4 + 4 * i])
+                        seen[key] = seen.get(key, 0) + 1
+                    for (cta, warp, bar, par), cnt in sorted(seen.items()):
+                        print(f"[bench]   cta {cta} warp {warp} ({cnt} threads) barrier smem {bar:#x} parity {par:#x}", file=sys.stderr)
+                except Exception as e2:  # noqa: BLE001
+                    print(f"[bench] wait log unavailable: {e2}", file=sys.stderr)
+            raise
 
 
 if __name__ == "__main__":

@@ -57,6 +57,12 @@ extern "C" {
  * workspace without waiting for the previous kernel to complete, so that it runs under that kernel's tail (about 2.5 us
  * per call at 256 tokens x 128 heads when calls follow one another); without it (the default) every CTA of that kernel
  * waits for the previous kernel's completion first, which is always safe.
+ * One more condition when the previous kernel IS an earlier mla_preprocess call on the same workspace memory: that call's q
+ * kernel lets its dependents start while it still reads its a1 rows from the workspace, and this call's quantiser then writes
+ * the first num_tokens x hidden_dim bytes of it.  With the same num_tokens / hidden_dim / quant_mode (same workspace layout)
+ * those bytes are the previous call's a0, long consumed; a different layout may put them under its a1.  So: set the flag
+ * between calls of one shape on one workspace (or on disjoint workspaces), and clear it for the first call after a change of
+ * shape.  The torch operator applies exactly this rule to the workspace it allocates (mlapo_torch_op.cpp).
  */
 #define MLAPO_FLAG_INPUT_COMPLETE 1
 
@@ -326,6 +332,8 @@ int mlapo_launches_per_call(const MlapoParams* p);
  * q kernel for every call of more than 128 tokens, bit14 = one CTA per (head, token tile) unit even when there are few units,
  * bit16 = MM1 on single CTAs (8 K-splits) where CTA pairs (4 K-splits) would run, bit17 = the CTA-per-row norm kernel at prefill sizes,
  * bit19 = 128-column weight tiles for MM1 on CTA pairs where 256-column tiles would be used (more than 256 tokens).
+ * bit20 = the CTA-pair q kernel's drain groups of every second CTA idle 6000 cycles before chunks 2 and 3 (regression test for a
+ *         barrier-phase race between consecutive units).
  * Returns the previous flags.
  */
 int mlapo_set_debug_flags(int flags);

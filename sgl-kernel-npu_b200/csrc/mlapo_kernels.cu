@@ -325,6 +325,7 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
   qa.tok_scale1 = per_token ? tok_scale + n : nullptr;
   qa.cos = p->cos; qa.sin = p->sin; qa.q_nope_scale = p->q_nope_scale;
   qa.num_heads = h; qa.m_total = n; qa.cta_tokens = cta_tokens;
+  qa.debug_drain_delay = (g_debug_flags & 1048576) ? 6000 : 0;  // debug bit20: late drain groups in the pair kernel (regression test)
   const int q_tok_tiles = (n + cta_tokens - 1) / cta_tokens;
 
   g_kernel_names[0] = "quant_hidden";

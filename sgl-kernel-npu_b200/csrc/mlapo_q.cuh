@@ -53,6 +53,7 @@ struct QArgs {
   int descale_is_i64;
   int cta_tokens;             // 256 (two token tiles per CTA, weights streamed once per 256 tokens) or 128 (more CTAs when heads are few)
   void* q_out1;               // act [N, H, 64]: written with plain stores by the split forms (kSplit > 1)
+  int debug_drain_delay;      // test hook (debug bit20): cycles the pair kernel's drain groups of the second CTA idle before chunks 2, 3
 };
 
 // Few heads (a TP slice, a small batch) leave most SMs without a (head, token tile) unit.  kSplit = 2 or 4 CTAs then share a unit:

@@ -55,9 +55,14 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
   uint64_t* qn_free = bars + 13;        // [1] absorb commit (both) -> epilogue may overwrite the q_nope tiles
   uint64_t* wuk_full = bars + 14;       // [3] leader's: TMA of both CTAs -> absorb
   uint64_t* wuk_empty = bars + 17;      // [3] absorb commit (both) -> TMA
-  uint64_t* unit_full = bars + 20;      // [2] absorb commit (both) -> drains of TMEM buffer b
-  uint64_t* buf_empty = bars + 22;      // [2] leader's: remote arrives after chunks 0 / 1 -> absorb chunk c+2
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
+  // unit_full is indexed by TMEM region AND buffer.  One barrier per buffer for both regions deadlocked (once in ~20 000
+  // launches): the commits of unit i+1's first chunks need nothing from unit i's drains, so a drain group that was late for
+  // chunk 2 / 3 of unit i could find its barrier two completions on — the parity it waits for is then the current phase's.
+  // With one barrier per (region, buffer) the next completion after a unit's two belongs to unit i+2, whose MM2 waits for
+  // region_free, i.e. for every drain group to be past these waits.
+  uint64_t* unit_full = bars + 20;      // [4] (region, buffer): absorb commit (both) -> drains
+  uint64_t* buf_empty = bars + 24;      // [2] leader's: remote arrives after chunks 0 / 1 -> absorb chunk c+2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 26);
   int2* s_cst_all = reinterpret_cast<int2*>(smem + kPBarOff + 256);
   // arrivals per completion: act out — both drain groups take part in every chunk; int8 out — group g alone drains chunks g, g+2
   constexpr uint32_t kBufEmptyCount = kInt8Out ? 2u : 4u;
@@ -74,8 +79,8 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
     ptx::prefetch_tmap(&tm_a1);
     ptx::prefetch_tmap(&tm_wuk);
     ptx::prefetch_tmap(&tm_out0);
-    for (int i = 0; i < 24; ++i) {
-      const uint32_t cnt = (i == 10 || i == 11) ? kRegionFreeCount : i == 12 ? 4u : (i == 22 || i == 23) ? kBufEmptyCount : 1u;
+    for (int i = 0; i < 26; ++i) {
+      const uint32_t cnt = (i == 10 || i == 11) ? kRegionFreeCount : i == 12 ? 4u : (i == 24 || i == 25) ? kBufEmptyCount : 1u;
       ptx::mbar_init(ptx::smem_u32(bars + i), cnt);
     }
     ptx::fence_mbar_init();
@@ -191,7 +196,7 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
               ptx::umma_f16_pair(tmem + par * 256 + (c & 1) * 128, da, db, idesc3, k > 0 ? 1u : 0u);
             }
             ptx::umma_commit_pair(ptx::smem_u32(wuk_empty + w));
-            ptx::umma_commit_pair(ptx::smem_u32(unit_full + (c & 1)));
+            ptx::umma_commit_pair(ptx::smem_u32(unit_full + par * 2 + (c & 1)));
           }
           __syncwarp();
         }
@@ -373,6 +378,13 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
       //                  int8 out: group g owns TMEM buffer g and drains whole chunks c = g, g+2 (128 int8 = one 128-byte row).
       //                  TMEM -> registers -> this group's swizzled 16 KB staging tile -> TMA store into q_out0.
       const uint32_t st_tile = ptx::smem_u32(smem + kPStageOff + g * kTile16K);
+      // test hook: a drain group that reaches its wait for chunk 2 / 3 late (tests/test_mla_preprocess_gpu.py, late drain group)
+      auto late = [&](int c) {
+        if (qa.debug_drain_delay && rank == 1 && c >= 2) {
+          const long long t0 = clock64();
+          while (clock64() - t0 < qa.debug_drain_delay) {}
+        }
+      };
       uint32_t it = 0;
       for (int u = pair; u < total_units; u += num_pairs, ++it) {
         const uint32_t par = it & 1;
@@ -383,7 +395,8 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
 #pragma unroll 1
           for (int cc = 0; cc < 2; ++cc) {
             const int c = g + 2 * cc;
-            ptx::mbar_wait(ptx::smem_u32(unit_full + g), (it * 2 + cc) & 1);
+            late(c);
+            ptx::mbar_wait(ptx::smem_u32(unit_full + par * 2 + g), cc);  // this barrier's completions 2k, 2k+1 belong to the region's k-th unit
             __syncwarp();
             ptx::tc_fence_after();
             const uint32_t acc3 = lane_base + par * 256 + g * 128;
@@ -417,7 +430,8 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
         } else {
 #pragma unroll 1
           for (int c = 0; c < 4; ++c) {
-            ptx::mbar_wait(ptx::smem_u32(unit_full + (c & 1)), (it * 2 + (c >> 1)) & 1);
+            late(c);
+            ptx::mbar_wait(ptx::smem_u32(unit_full + par * 2 + (c & 1)), c >> 1);  // completions 2k, 2k+1 belong to the region's k-th unit
             __syncwarp();
             ptx::tc_fence_after();
             uint32_t w[32];

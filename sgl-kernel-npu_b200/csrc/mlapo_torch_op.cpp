@@ -218,8 +218,11 @@ std::tuple<at::Tensor&, at::Tensor&, at::Tensor&, at::Tensor&> mla_preprocess(
   p.descale_is_int64 = dsc_dt == at::kLong;
   // The operator cannot see what precedes it on the stream, so it only takes the no-wait start (MLAPO_FLAG_INPUT_COMPLETE, see
   // include/mla_preprocess_b200.h) when the deployment says that no kernel that triggers its dependents early feeds this op.
+  // Even then the flag is set per call, below, once the workspace is known: only when the previous operator call of this thread
+  // ran on the same stream with the same shape and got the same workspace memory (see the header: a different layout could put
+  // this call's first stores under the a1 rows the previous call's q kernel is still reading).
   static const bool input_complete = [] { const char* e = std::getenv("SGL_KERNEL_NPU_MLAPO_INPUT_COMPLETE"); return e && e[0] == '1'; }();
-  p.flags = input_complete ? MLAPO_FLAG_INPUT_COMPLETE : 0;
+  p.flags = 0;
   p.hidden_state = hiddenState.data_ptr();
   p.wdqkv_km = wdqkv_km.data_ptr();
   p.descale0 = descale0.data_ptr();
@@ -254,6 +257,13 @@ std::tuple<at::Tensor&, at::Tensor&, at::Tensor&, at::Tensor&> mla_preprocess(
     check_cabi(mlapo_get_workspace_size(&p, &ws_bytes), "mlapo_get_workspace_size");
     // transient workspace from the caching allocator on the current stream (reference: at::empty, :677-680)
     at::Tensor workspace = at::empty({(int64_t)std::max<size_t>(ws_bytes, 256)}, hiddenState.options().dtype(at::kByte));
+    struct LastCall { cudaStream_t stream; const void* ws; int64_t n, h, d; int quant, cache, dev; };
+    static thread_local LastCall last{nullptr, nullptr, 0, 0, 0, -1, -1, -1};
+    const LastCall now{stream, workspace.data_ptr(), N, (int64_t)p.num_heads, D, quantMode, cacheMode, (int)hiddenState.get_device()};
+    const bool same_as_last = last.ws == now.ws && last.stream == now.stream && last.n == now.n && last.h == now.h && last.d == now.d &&
+                              last.quant == now.quant && last.cache == now.cache && last.dev == now.dev;
+    if (input_complete && same_as_last) p.flags = MLAPO_FLAG_INPUT_COMPLETE;
+    last = now;
     check_cabi(mla_preprocess_launch(&p, workspace.data_ptr(), (size_t)workspace.numel(), stream), "mla_preprocess_launch");
   }
   return std::forward_as_tuple(q_out0, kv_cache_out0, q_out1, kv_cache_out1);  // :703

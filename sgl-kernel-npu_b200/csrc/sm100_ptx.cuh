@@ -56,8 +56,12 @@ __device__ unsigned* g_wait_log = nullptr;
 __device__ __forceinline__ void wait_timeout(unsigned a, unsigned b, unsigned c, unsigned d) {
   unsigned* log = g_wait_log;
   if (log) {
-    const unsigned i = atomicAdd(log, 1u);
-    if (i < 32) { log[1 + 4 * i] = a; log[2 + 4 * i] = b; log[3 + 4 * i] = c; log[4 + 4 * i] = d; }
+    // one entry per warp (lane 0, or the lowest lane that got here), up to 250 entries: enough for every warp of a few CTAs
+    const unsigned first = __ffs(__activemask()) - 1;
+    if ((threadIdx.x & 31) == first) {
+      const unsigned i = atomicAdd(log, 1u);
+      if (i < 250) { log[1 + 4 * i] = a; log[2 + 4 * i] = b; log[3 + 4 * i] = c; log[4 + 4 * i] = d; }
+    }
     __threadfence_system();
     const long long t0 = clock64();
     while (clock64() - t0 < 200000000LL) {}  // let the other stuck waiters log too
