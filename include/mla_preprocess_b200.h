@@ -333,10 +333,15 @@ int mlapo_launches_per_call(const MlapoParams* p);
  * bit16 = MM1 on single CTAs (8 K-splits) where CTA pairs (4 K-splits) would run, bit17 = the CTA-per-row norm kernel at prefill sizes,
  * bit19 = 128-column weight tiles for MM1 on CTA pairs where 256-column tiles would be used (more than 256 tokens).
  * bit20 = the CTA-pair q kernel's drain groups of every second CTA idle 6000 cycles before chunks 2 and 3 (regression test for a
- *         barrier-phase race between consecutive units).
+ *         barrier-phase race between consecutive units),
+ * bit21 = race hunting: every fourth mbarrier wait of every kernel is preceded by a random idle period of up to 3000 cycles (set
+ *         and cleared on the current device).  Only in a library built with -DMLAPO_WAIT_JITTER (libmla_preprocess_b200_jitter.so,
+ *         used by tests/test_jitter_gpu.py; mlapo_debug_has_wait_jitter() tells): the shipped library carries no code for it.
  * Returns the previous flags.
  */
 int mlapo_set_debug_flags(int flags);
+/* 1 if this build honours debug bit21 (see above), else 0. */
+int mlapo_debug_has_wait_jitter(void);
 /* Debug (flag bit11 = log stuck barrier waits instead of trapping): {count, {cta, thread, barrier, parity} x count}. */
 int mlapo_debug_read_wait_log(unsigned* out, int cap_words);
 /* With bit2 set: per-kernel durations (ms) of the last launch, in launch order; returns how many were written. */

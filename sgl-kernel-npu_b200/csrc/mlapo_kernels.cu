@@ -583,6 +583,12 @@ const char* mlapo_last_error(void) { return g_err; }
 int mlapo_set_debug_flags(int flags) {
   const int old = g_debug_flags_word.exchange(flags);
   g_debug_flags = flags;
+#ifdef MLAPO_WAIT_JITTER
+  if ((flags ^ old) & 2097152) {  // bit21: random idle periods before barrier waits (current device; synchronises it)
+    const unsigned jitter = (flags & 2097152) ? 3000u : 0u;
+    cudaMemcpyToSymbol(ptx::g_wait_jitter, &jitter, sizeof jitter);
+  }
+#endif
   if ((flags & 2048) && !g_wait_log_host) {  // bit11: register a host-mapped log for stuck barrier waits
     unsigned* dptr = nullptr;
     if (cudaHostAlloc(reinterpret_cast<void**>(&g_wait_log_host), 4096, cudaHostAllocMapped) == cudaSuccess &&
@@ -592,6 +598,13 @@ int mlapo_set_debug_flags(int flags) {
     }
   }
   return old;
+}
+int mlapo_debug_has_wait_jitter(void) {
+#ifdef MLAPO_WAIT_JITTER
+  return 1;
+#else
+  return 0;
+#endif
 }
 // Debug: copies the stuck-wait log {count, then {cta, thread, barrier, parity} x count}; returns the count.  Reads host
 // memory only, so it still works after a trap.

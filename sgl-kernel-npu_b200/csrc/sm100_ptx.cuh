@@ -53,7 +53,8 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 // been registered (debug flag bit11) the stuck wait is first recorded there {cta, thread, barrier smem address, parity},
 // where the host can still read it after the trap has taken the context down.
 __device__ unsigned* g_wait_log = nullptr;
-__device__ __forceinline__ void wait_timeout(unsigned a, unsigned b, unsigned c, unsigned d) {
+// (out of line and never returning: the cold path costs the waits' call sites nothing but a branch)
+[[noreturn]] __device__ __noinline__ void wait_timeout(unsigned a, unsigned b, unsigned c, unsigned d) {
   unsigned* log = g_wait_log;
   if (log) {
     // one entry per warp (lane 0, or the lowest lane that got here), up to 250 entries: enough for every warp of a few CTAs
@@ -68,7 +69,28 @@ __device__ __forceinline__ void wait_timeout(unsigned a, unsigned b, unsigned c,
   }
   __trap();
 }
+// Race hunting (debug bit21, only in a library built with -DMLAPO_WAIT_JITTER: even an untaken branch per wait costs ~1 us per
+// call in the latency-critical single-thread loops, measured): every fourth barrier wait, chosen by a hash of the clock, is
+// preceded by a random idle period of up to g_wait_jitter cycles, so that warps reach their waits late in ever different
+// combinations.  A protocol that only works at the usual timing shows up as a mismatch or as a stuck wait (tests/test_jitter_gpu.py).
+#ifdef MLAPO_WAIT_JITTER
+__constant__ unsigned g_wait_jitter = 0;
+__device__ __forceinline__ void wait_jitter(uint32_t bar) {
+  const unsigned j = g_wait_jitter;
+  if (j) {
+    unsigned h = (unsigned)clock64() * 2654435761u + threadIdx.x * 40503u + bar * 97u + blockIdx.x * 7919u;
+    h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+    if ((h & 3u) == 0) {
+      const long long t0 = clock64(), d = (long long)((h >> 8) % j);
+      while (clock64() - t0 < d) {}
+    }
+  }
+}
+#else
+__device__ __forceinline__ void wait_jitter(uint32_t) {}
+#endif
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  wait_jitter(bar);
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
@@ -79,6 +101,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 // The same bound by an iteration count (try_wait itself suspends for a while): two instructions per retry instead of a clock read,
 // for loops whose waiters compete for issue slots with the working warps.
 __device__ __forceinline__ void mbar_wait_light(uint32_t bar, uint32_t parity) {
+  wait_jitter(bar);
   unsigned n = 0;
   while (!mbar_try_wait(bar, parity)) {
     if (++n > (1u << 26)) wait_timeout(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z), threadIdx.x, bar, parity);
@@ -262,6 +285,7 @@ __device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t par
   return done != 0;
 }
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  wait_jitter(bar);
   if (mbar_try_wait_cluster(bar, parity)) return;
   const long long t0 = clock64();
   while (!mbar_try_wait_cluster(bar, parity)) {
