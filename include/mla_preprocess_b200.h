@@ -335,13 +335,17 @@ int mlapo_launches_per_call(const MlapoParams* p);
  * bit20 = the CTA-pair q kernel's drain groups of every second CTA idle 6000 cycles before chunks 2 and 3 (regression test for a
  *         barrier-phase race between consecutive units),
  * bit21 = race hunting: every fourth mbarrier wait of every kernel is preceded by a random idle period of up to 3000 cycles (set
- *         and cleared on the current device).  Only in a library built with -DMLAPO_WAIT_JITTER (libmla_preprocess_b200_jitter.so,
- *         used by tests/test_jitter_gpu.py; mlapo_debug_has_wait_jitter() tells): the shipped library carries no code for it.
+ *         and cleared on the current device).
+ * Bits 3, 20 and 21 act only in the INSTRUMENTED build of the same sources (-DMLAPO_INSTRUMENTED ->
+ * libmla_preprocess_b200_instr.so; mlapo_debug_is_instrumented() tells): the shipped library compiles the clock marks, the delay
+ * hook and the jitter out — even untaken, those branches cost 3-4 % of a decode call.  tools/timeline.py, the chain spans of
+ * bench.py and tests/test_jitter_gpu.py load the instrumented library (MLAPO_LIB); everything else, the timed paths above all,
+ * runs the shipped one.
  * Returns the previous flags.
  */
 int mlapo_set_debug_flags(int flags);
-/* 1 if this build honours debug bit21 (see above), else 0. */
-int mlapo_debug_has_wait_jitter(void);
+/* 1 if this is the instrumented build (debug bits 3, 20, 21 act), else 0. */
+int mlapo_debug_is_instrumented(void);
 /* Debug (flag bit11 = log stuck barrier waits instead of trapping): {count, {cta, thread, barrier, parity} x count}. */
 int mlapo_debug_read_wait_log(unsigned* out, int cap_words);
 /* With bit2 set: per-kernel durations (ms) of the last launch, in launch order; returns how many were written. */

@@ -583,7 +583,7 @@ const char* mlapo_last_error(void) { return g_err; }
 int mlapo_set_debug_flags(int flags) {
   const int old = g_debug_flags_word.exchange(flags);
   g_debug_flags = flags;
-#ifdef MLAPO_WAIT_JITTER
+#ifdef MLAPO_INSTRUMENTED
   if ((flags ^ old) & 2097152) {  // bit21: random idle periods before barrier waits (current device; synchronises it)
     const unsigned jitter = (flags & 2097152) ? 3000u : 0u;
     cudaMemcpyToSymbol(ptx::g_wait_jitter, &jitter, sizeof jitter);
@@ -599,8 +599,8 @@ int mlapo_set_debug_flags(int flags) {
   }
   return old;
 }
-int mlapo_debug_has_wait_jitter(void) {
-#ifdef MLAPO_WAIT_JITTER
+int mlapo_debug_is_instrumented(void) {
+#ifdef MLAPO_INSTRUMENTED
   return 1;
 #else
   return 0;

@@ -604,7 +604,7 @@ q_fused_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant_
   ptx::tc_fence_after();
   c.tmem = *tmem_slot;
   if (threadIdx.x == 0) tl_mark(tl, 2);  // prologue done
-  if (threadIdx.x == 0 && tl) {  // which SM ran this CTA (timeline analysis only)
+  if (MLAPO_TL_ON && threadIdx.x == 0 && tl) {  // which SM ran this CTA (timeline analysis only)
     unsigned smid;
     asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
     tl[(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) * 16 + 13] = smid;

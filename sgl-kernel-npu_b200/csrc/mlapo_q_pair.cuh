@@ -378,12 +378,16 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
       //                  int8 out: group g owns TMEM buffer g and drains whole chunks c = g, g+2 (128 int8 = one 128-byte row).
       //                  TMEM -> registers -> this group's swizzled 16 KB staging tile -> TMA store into q_out0.
       const uint32_t st_tile = ptx::smem_u32(smem + kPStageOff + g * kTile16K);
-      // test hook: a drain group that reaches its wait for chunk 2 / 3 late (tests/test_mla_preprocess_gpu.py, late drain group)
+      // test hook (instrumented build only): a drain group that reaches its wait for chunk 2 / 3 late (tests/test_jitter_gpu.py)
       auto late = [&](int c) {
+#ifdef MLAPO_INSTRUMENTED
         if (qa.debug_drain_delay && rank == 1 && c >= 2) {
           const long long t0 = clock64();
           while (clock64() - t0 < qa.debug_drain_delay) {}
         }
+#else
+        (void)c;
+#endif
       };
       uint32_t it = 0;
       for (int u = pair; u < total_units; u += num_pairs, ++it) {

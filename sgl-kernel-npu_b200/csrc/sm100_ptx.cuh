@@ -69,11 +69,11 @@ __device__ unsigned* g_wait_log = nullptr;
   }
   __trap();
 }
-// Race hunting (debug bit21, only in a library built with -DMLAPO_WAIT_JITTER: even an untaken branch per wait costs ~1 us per
+// Race hunting (debug bit21, only in the instrumented build, -DMLAPO_INSTRUMENTED: even an untaken branch per wait costs ~1 us per
 // call in the latency-critical single-thread loops, measured): every fourth barrier wait, chosen by a hash of the clock, is
 // preceded by a random idle period of up to g_wait_jitter cycles, so that warps reach their waits late in ever different
 // combinations.  A protocol that only works at the usual timing shows up as a mismatch or as a stuck wait (tests/test_jitter_gpu.py).
-#ifdef MLAPO_WAIT_JITTER
+#ifdef MLAPO_INSTRUMENTED
 __constant__ unsigned g_wait_jitter = 0;
 __device__ __forceinline__ void wait_jitter(uint32_t bar) {
   const unsigned j = g_wait_jitter;

@@ -13,8 +13,12 @@ import os
 
 import torch
 
-# MLAPO_LIB overrides the library file (A/B timing of two builds in one session); it must still be a build of this ABI.
-_LIB_PATH = os.environ.get("MLAPO_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libmla_preprocess_b200.so")
+# MLAPO_LIB overrides the library file (A/B timing of two builds in one session; the instrumented build for the timeline and
+# race-hunting tools); it must still be a build of this ABI.
+_LIB_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib")
+_LIB_PATH = os.environ.get("MLAPO_LIB") or os.path.join(_LIB_DIR, "libmla_preprocess_b200.so")
+# Same sources with -DMLAPO_INSTRUMENTED (per-CTA clock marks, wait jitter, test hooks): for profiling tools and tests only.
+INSTRUMENTED_LIB = os.path.join(_LIB_DIR, "libmla_preprocess_b200_instr.so")
 
 CACHE_MODE_MAP = {"krope_ctkv": 1, "int8_nzcache": 2, "nzcache": 3}            # op_host/mla_preprocess.cpp:605-606
 QUANT_MODE_MAP = {"per_tensor_quant_asymm": 0, "per_token_quant_symm": 1}      # :608-611

@@ -1,5 +1,6 @@
-"""Worker of tests/test_jitter_gpu.py: runs in its own process with MLAPO_LIB pointing at the -DMLAPO_WAIT_JITTER build of the
-library (the shipped library carries no jitter code).  Exit code 0 = every result under jitter equals the undisturbed one."""
+"""Worker of tests/test_jitter_gpu.py: runs in its own process with MLAPO_LIB pointing at the instrumented build of the library
+(-DMLAPO_INSTRUMENTED; the shipped library carries neither the jitter nor the delay hook).  Exit code 0 = every disturbed result
+equals the undisturbed one."""
 import os
 import sys
 
@@ -16,6 +17,7 @@ import mla_harness as hz  # noqa: E402
 BF, FP = torch.bfloat16, torch.float16
 PT = "per_tensor_quant_asymm"
 JITTER = 2097152
+LATE_DRAIN = 1048576
 
 SHAPES = [
     # N, H, D, dtype, cache mode, extra debug flags, what it walks
@@ -35,18 +37,18 @@ def _outputs(g, taps):
     return out
 
 
-def check_shape(shape, cuda_device):
+def check_shape(shape, cuda_device, disturb=JITTER, reps=4):
     n, h, d, dt, mode, extra = shape
     case = orc.gen_case(N=n, H=h, D=d, dtype=dt, cache_mode=mode, seed=11, num_blocks=max(12, n // 64), neg_slot_frac=0.05)
     case.t["kv_cache"].fill_(3)
     case.t["kv_cache_rope"].fill_(3)
     g, taps = hz.run_cuda(case, cuda_device, quant_mode=PT, debug="tap", extra_flags=extra)
     want = _outputs(g, taps)
-    for rep in range(4):
-        g2, taps2 = hz.run_cuda(case, cuda_device, quant_mode=PT, debug="tap", extra_flags=extra | JITTER)
+    for rep in range(reps):
+        g2, taps2 = hz.run_cuda(case, cuda_device, quant_mode=PT, debug="tap", extra_flags=extra | disturb)
         got = _outputs(g2, taps2)
         for k, v in want.items():
-            assert torch.equal(got[k], v), f"{k} differs under jitter (repetition {rep})"
+            assert torch.equal(got[k], v), f"{k} differs under disturbance {disturb} (repetition {rep})"
 
 
 def check_chained(cuda_device):
@@ -88,7 +90,7 @@ def check_chained(cuda_device):
 
 def main():
     from sgl_kernel_npu import cabi
-    assert cabi.lib.mlapo_debug_has_wait_jitter() == 1, "this worker needs the -DMLAPO_WAIT_JITTER build (MLAPO_LIB)"
+    assert cabi.lib.mlapo_debug_is_instrumented() == 1, "this worker needs the -DMLAPO_INSTRUMENTED build (MLAPO_LIB)"
     dev = torch.device("cuda", 0)
     which = sys.argv[1] if len(sys.argv) > 1 else "all"
     if which in ("all", "chained"):
@@ -98,6 +100,10 @@ def main():
         if which in ("all", str(i)):
             check_shape(shape, dev)
             print("shape", i, shape[:2], "ok", flush=True)
+    if which in ("all", "late_drain"):
+        for shape in SHAPES[-2:]:   # several units per pair, int8 and act drains
+            check_shape(shape, dev, disturb=LATE_DRAIN, reps=1)
+            print("late drain groups", shape[:2], "ok", flush=True)
 
 
 if __name__ == "__main__":

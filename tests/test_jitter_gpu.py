@@ -1,6 +1,6 @@
 """Race hunting without a sanitizer (compute-sanitizer is closed on this pool: profiles/r02/sanitizer_closed.txt).
 
-Debug bit21 — in a separate build of the library with -DMLAPO_WAIT_JITTER, loaded by a worker process through MLAPO_LIB; the
+Debug bit21 — in the instrumented build of the library (-DMLAPO_INSTRUMENTED), loaded by a worker process through MLAPO_LIB; the
 shipped library carries no code for it — puts a random idle period of up to 3000 cycles in front of every fourth mbarrier wait of every kernel (chosen by a
 hash of the clock, so every launch perturbs a different set of warps).  The kernels' results do not depend on timing — integer
 sums are associative, every floating-point value is computed by one thread in a fixed order — so a run under jitter must equal
@@ -19,7 +19,7 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-JITTER_LIB = os.path.join(os.path.dirname(HERE), "sgl-kernel-npu_b200", "sgl_kernel_npu", "lib", "libmla_preprocess_b200_jitter.so")
+JITTER_LIB = os.path.join(os.path.dirname(HERE), "sgl-kernel-npu_b200", "sgl_kernel_npu", "lib", "libmla_preprocess_b200_instr.so")
 
 
 def _run_worker(which):
@@ -27,6 +27,16 @@ def _run_worker(which):
     env = dict(os.environ, MLAPO_LIB=JITTER_LIB)
     r = subprocess.run([sys.executable, os.path.join(HERE, "jitter_worker.py"), which], env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, f"jitter worker failed:\n{r.stdout[-2000:]}\n{r.stderr[-4000:]}"
+
+
+def test_pair_kernel_late_drain_group(cuda_device):
+    """Regression (160 / 192 units on 74 pairs): a pair streams several (head, 256-token) units, and the absorb of unit i+1 needs
+    nothing from the drains of unit i.  With one `unit_full` barrier per TMEM buffer (shared by both TMEM regions) a drain group
+    that reached its wait for chunk 2 / 3 of unit i late found the barrier two completions on and waited for ever (seen once in
+    ~20 000 launches at C3, after a faster dequant made unit i+1's first chunks arrive sooner).  Debug bit20 makes every second
+    CTA's drain groups 6000 cycles late before those chunks: with the barriers per (region, buffer) the call completes with the
+    undisturbed result; with the shared barriers it ran into the bounded wait every time (a trap after ~2 s)."""
+    _run_worker("late_drain")
 
 
 def test_results_do_not_depend_on_timing(cuda_device):

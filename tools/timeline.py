@@ -1,9 +1,12 @@
-"""GPU diagnostic: per-CTA clock marks of mm1_splitk and q_fused (debug flag bit3). Not a test."""
+"""GPU diagnostic: per-CTA clock marks of mm1_splitk and q_fused (debug flag bit3). Not a test.
+Loads the INSTRUMENTED build of the library (the shipped one compiles the marks out): its kernels are 3-4 % slower, so the
+periods printed here are for reading the structure of a call, not for quoting."""
 import os
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "sgl-kernel-npu_b200")]
+os.environ.setdefault("MLAPO_LIB", os.path.join(ROOT, "sgl-kernel-npu_b200", "sgl_kernel_npu", "lib", "libmla_preprocess_b200_instr.so"))
 import numpy as np
 import torch
 
