@@ -3,7 +3,7 @@
 tag=$1; libb=$2; shift 2
 out=gpurun_out/$tag
 mkdir -p $out
-for rep in 1 2 3; do
+for rep in $(seq 1 ${REPS:-3}); do
 for w in "$@"; do
   for arm in a b; do
     if [ $arm = b ]; then export MLAPO_LIB=$libb; else unset MLAPO_LIB; fi
