@@ -69,6 +69,10 @@ def _load():
     lib.mla_preprocess_launch_static.argtypes = [ctypes.POINTER(MlapoParams), ctypes.c_void_p]
     lib.mlapo_launches_per_call.argtypes = [ctypes.POINTER(MlapoParams)]
     lib.mlapo_set_debug_flags.argtypes = [ctypes.c_int]
+    # MLAPO_DEBUG_FLAGS: debug flags from the first moment (e.g. the existing tests of the other operators run under the barrier
+    # jitter of the instrumented build: tests/test_jitter_gpu.py).  Test and profiling use only, like the flags themselves.
+    if os.environ.get("MLAPO_DEBUG_FLAGS"):
+        lib.mlapo_set_debug_flags(int(os.environ["MLAPO_DEBUG_FLAGS"], 0))
     return lib
 
 

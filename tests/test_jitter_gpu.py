@@ -39,6 +39,16 @@ def test_pair_kernel_late_drain_group(cuda_device):
     _run_worker("late_drain")
 
 
+def test_other_operators_under_jitter(cuda_device):
+    """The parity tests of `batch_matmul_transpose` and of the `split_qkv_rmsnorm_rope` family (their kernels use the same bounded
+    barrier waits), run as they are in a child pytest with the instrumented library and the jitter on from the first call."""
+    assert os.path.exists(JITTER_LIB), f"{JITTER_LIB} missing: __graft_entry__.build() makes it"
+    env = dict(os.environ, MLAPO_LIB=JITTER_LIB, MLAPO_DEBUG_FLAGS="2097152")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(HERE, "test_batch_matmul_transpose.py"), os.path.join(HERE, "test_split_qkv.py"),
+                        "-m", "gpu", "-q", "-x", "-p", "no:cacheprovider", "-k", "cuda"], env=env, capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0 and " passed" in r.stdout, f"child pytest under jitter failed:\n{r.stdout[-3000:]}\n{r.stderr[-2000:]}"
+
+
 def test_results_do_not_depend_on_timing(cuda_device):
     """Every shape of jitter_worker.SHAPES (one undisturbed run, four runs under jitter: all outputs / caches / taps equal) and
     eight chained calls with the no-wait start on one workspace, in one worker process (one torch import)."""
