@@ -68,6 +68,106 @@ __global__ void __launch_bounds__(128, 1) i8_peak_kernel(int iters, unsigned see
   if (threadIdx.x < 32) ptx::tmem_dealloc(tmem, 512);
 }
 
+// ---------------------------------------------------------------------------------------------- MMA shapes of the op on CTA pairs
+// The op's own instruction shapes, on resident tiles, every pair of SMs: M = 256 (cta_group::2), N and kind as given, K = 32
+// bytes per instruction (int8: 32 elements, bf16: 16), K-major A [128 rows per CTA] and B [N/2 rows per CTA].  `chains` = how
+// many accumulators the instruction stream alternates between (1: every instruction depends on the previous one's D).
+template <bool kF16>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) pair_shape_kernel(int iters, int n, int chains, unsigned seed) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  uint32_t x = seed * 2654435761u + threadIdx.x * 40503u + blockIdx.x * 9973u + 1u;
+  for (int i = threadIdx.x; i < (kATile + kBTile / 2) / 4; i += blockDim.x) {
+    x ^= x << 13; x ^= x >> 17; x ^= x << 5;
+    // bf16 operands: keep the exponent field away from inf / nan patterns (upper bits 0x3F80 | small mantissa)
+    reinterpret_cast<uint32_t*>(smem)[i] = kF16 ? ((x & 0x007F007Fu) | 0x3F803F80u) : x;
+  }
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(ptx::smem_u32(&bar), 1);
+    ptx::fence_mbar_init();
+  }
+  if (threadIdx.x < 32) {
+    ptx::tmem_alloc_pair(ptx::smem_u32(&tmem_slot), 512);
+    ptx::tmem_relinquish_pair();
+  }
+  ptx::fence_proxy_async_smem();
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_arrive();
+  ptx::cluster_wait();
+  ptx::tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  if (ptx::cluster_ctarank() == 0 && threadIdx.x == 0) {
+    const uint32_t idesc = kF16 ? ptx::make_idesc(ptx::kCFmtF32, ptx::kFmtBF16, ptx::kFmtBF16, 0, 0, 256, (uint32_t)n)
+                                : ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, 256, (uint32_t)n);
+    const uint32_t a_base = ptx::smem_u32(smem), b_base = a_base + kATile;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint64_t da = ptx::make_smem_desc(a_base + k * 32, 1024, 0);
+        const uint64_t db = ptx::make_smem_desc(b_base + k * 32, 1024, 0);
+        const uint32_t d = tmem + (uint32_t)((it * 4 + k) % chains) * 256u;
+        if (kF16) ptx::umma_f16_pair(d, da, db, idesc, it > 0 ? 1u : 0u);
+        else ptx::umma_i8_pair(d, da, db, idesc, it > 0 ? 1u : 0u);
+      }
+    }
+    ptx::umma_commit_pair(ptx::smem_u32(&bar));
+  }
+  if (threadIdx.x == 0) ptx::mbar_wait(ptx::smem_u32(&bar), 0);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_arrive();
+  ptx::cluster_wait();
+  if (threadIdx.x < 32) ptx::tmem_dealloc_pair(tmem, 512);
+}
+
+// The same on single CTAs (cta_group::1, M = 128).
+template <bool kF16>
+__global__ void __launch_bounds__(128, 1) single_shape_kernel(int iters, int n, int chains, unsigned seed) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  uint32_t x = seed * 2654435761u + threadIdx.x * 40503u + blockIdx.x * 9973u + 1u;
+  for (int i = threadIdx.x; i < (kATile + kBTile) / 4; i += blockDim.x) {
+    x ^= x << 13; x ^= x >> 17; x ^= x << 5;
+    reinterpret_cast<uint32_t*>(smem)[i] = kF16 ? ((x & 0x007F007Fu) | 0x3F803F80u) : x;
+  }
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(ptx::smem_u32(&bar), 1);
+    ptx::fence_mbar_init();
+  }
+  if (threadIdx.x < 32) {
+    ptx::tmem_alloc(ptx::smem_u32(&tmem_slot), 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::fence_proxy_async_smem();
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  if (threadIdx.x == 0) {
+    const uint32_t idesc = kF16 ? ptx::make_idesc(ptx::kCFmtF32, ptx::kFmtBF16, ptx::kFmtBF16, 0, 0, 128, (uint32_t)n)
+                                : ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, 128, (uint32_t)n);
+    const uint32_t a_base = ptx::smem_u32(smem), b_base = a_base + kATile;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint64_t da = ptx::make_smem_desc(a_base + k * 32, 1024, 0);
+        const uint64_t db = ptx::make_smem_desc(b_base + k * 32, 1024, 0);
+        const uint32_t d = tmem + (uint32_t)((it * 4 + k) % chains) * 256u;
+        if (kF16) ptx::umma_f16(d, da, db, idesc, it > 0 ? 1u : 0u);
+        else ptx::umma_i8(d, da, db, idesc, it > 0 ? 1u : 0u);
+      }
+    }
+    ptx::umma_commit(ptx::smem_u32(&bar));
+    ptx::mbar_wait(ptx::smem_u32(&bar), 0);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (threadIdx.x < 32) ptx::tmem_dealloc(tmem, 512);
+}
+
 // ---------------------------------------------------------------------------------------------- DSMEM
 constexpr int kDsChunk = 16384;        // bytes one CTA sends to one peer per round (a [32 x 128] int32 sub-tile)
 constexpr int kDsThreads = 128;
@@ -185,6 +285,79 @@ double mlapo_mb_i8_peak(double target_ms, double* ms_out) {
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   return ops / (ms * 1e-3) / 1e12;
+}
+
+// Cycles per instruction of the op's MMA shapes on CTA pairs (M = 256): kind 0 = int8 (K = 32), 1 = bf16 (K = 16); n = MMA N;
+// chains = accumulators the stream alternates between.  Returns the achieved fraction of the nominal dense peak of that kind
+// (4.5 POPS int8, 2.25 PFLOP/s bf16, at the SM clock measured during the run) and writes the average SM cycles per instruction.
+double mlapo_mb_pair_shape(int kind, int n, int chains, double* cycles_per_mma);
+// cta_group::1, M = 128 (same conventions as mlapo_mb_pair_shape)
+double mlapo_mb_single_shape(int kind, int n, int chains, double* cycles_per_mma) {
+  int dev = 0, sms = 0, khz = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
+  if (n < 32 || n > 256 || (n % 32) || chains < 1 || chains > 2) return -1.0;
+  const int smem = kATile + kBTile;
+  auto kern = kind ? single_shape_kernel<true> : single_shape_kernel<false>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -2.0;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  auto run = [&](int iters) -> float {
+    cudaEventRecord(e0);
+    kern<<<sms, 128, smem>>>(iters, n, chains, 777u);
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess) return -1.f;
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    return ms;
+  };
+  if (run(2000) < 0.f) return -3.0;
+  const int iters = 40000;
+  const float ms = run(iters);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (ms <= 0.f) return -4.0;
+  const double mmas = 4.0 * iters;
+  if (cycles_per_mma) *cycles_per_mma = ms * 1e-3 * (khz * 1e3) / mmas;
+  const double ops = 2.0 * 128 * n * (kind ? 16 : 32) * mmas * sms;
+  return ops / (ms * 1e-3) / (kind ? 2.25e15 : 4.5e15);
+}
+
+double mlapo_mb_pair_shape(int kind, int n, int chains, double* cycles_per_mma) {
+  int dev = 0, sms = 0, khz = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
+  if (n < 32 || n > 256 || (n % 32) || chains < 1 || chains > 2) return -1.0;
+  const int smem = kATile + kBTile / 2;
+  auto kern = kind ? pair_shape_kernel<true> : pair_shape_kernel<false>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -2.0;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  auto run = [&](int iters) -> float {
+    cudaEventRecord(e0);
+    kern<<<sms & ~1, 128, smem>>>(iters, n, chains, 777u);
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess) return -1.f;
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    return ms;
+  };
+  if (run(2000) < 0.f) return -3.0;
+  const int iters = 40000;
+  const float ms = run(iters);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (ms <= 0.f) return -4.0;
+  const double mmas = 4.0 * iters;                                  // per pair
+  const double clk_hz = khz * 1e3;                                  // nominal max SM clock: short run, no power cap
+  if (cycles_per_mma) *cycles_per_mma = ms * 1e-3 * clk_hz / mmas;
+  const double ops = 2.0 * 256 * n * (kind ? 16 : 32) * mmas * ((sms & ~1) / 2);
+  const double peak = kind ? 2.25e15 : 4.5e15;
+  return ops / (ms * 1e-3) / peak;
 }
 
 // mode 0/1/2 as in the header comment; returns bytes per clock that ONE CTA sent (7 peers x 16 KB x rounds / cycles), median-ish
