@@ -124,7 +124,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) pair_shape_k
 
 // The same on single CTAs (cta_group::1, M = 128).
 template <bool kF16>
-__global__ void __launch_bounds__(128, 1) single_shape_kernel(int iters, int n, int chains, unsigned seed) {
+__global__ void __launch_bounds__(128, 1) single_shape_kernel(int iters, int m, int n, int chains, unsigned seed) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t bar;
   __shared__ uint32_t tmem_slot;
@@ -147,8 +147,8 @@ __global__ void __launch_bounds__(128, 1) single_shape_kernel(int iters, int n, 
   ptx::tc_fence_after();
   const uint32_t tmem = tmem_slot;
   if (threadIdx.x == 0) {
-    const uint32_t idesc = kF16 ? ptx::make_idesc(ptx::kCFmtF32, ptx::kFmtBF16, ptx::kFmtBF16, 0, 0, 128, (uint32_t)n)
-                                : ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, 128, (uint32_t)n);
+    const uint32_t idesc = kF16 ? ptx::make_idesc(ptx::kCFmtF32, ptx::kFmtBF16, ptx::kFmtBF16, 0, 0, (uint32_t)m, (uint32_t)n)
+                                : ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, (uint32_t)m, (uint32_t)n);
     const uint32_t a_base = ptx::smem_u32(smem), b_base = a_base + kATile;
     for (int it = 0; it < iters; ++it) {
 #pragma unroll
@@ -291,13 +291,15 @@ double mlapo_mb_i8_peak(double target_ms, double* ms_out) {
 // chains = accumulators the stream alternates between.  Returns the achieved fraction of the nominal dense peak of that kind
 // (4.5 POPS int8, 2.25 PFLOP/s bf16, at the SM clock measured during the run) and writes the average SM cycles per instruction.
 double mlapo_mb_pair_shape(int kind, int n, int chains, double* cycles_per_mma);
-// cta_group::1, M = 128 (same conventions as mlapo_mb_pair_shape)
-double mlapo_mb_single_shape(int kind, int n, int chains, double* cycles_per_mma) {
+// cta_group::1, M = 64 or 128 (same conventions as mlapo_mb_pair_shape)
+double mlapo_mb_single_shape_m(int kind, int m, int n, int chains, double* cycles_per_mma);
+double mlapo_mb_single_shape(int kind, int n, int chains, double* cycles_per_mma) { return mlapo_mb_single_shape_m(kind, 128, n, chains, cycles_per_mma); }
+double mlapo_mb_single_shape_m(int kind, int m, int n, int chains, double* cycles_per_mma) {
   int dev = 0, sms = 0, khz = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
-  if (n < 32 || n > 256 || (n % 32) || chains < 1 || chains > 2) return -1.0;
+  if (n < 32 || n > 256 || (n % 32) || chains < 1 || chains > 2 || (m != 64 && m != 128)) return -1.0;
   const int smem = kATile + kBTile;
   auto kern = kind ? single_shape_kernel<true> : single_shape_kernel<false>;
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -2.0;
@@ -306,7 +308,7 @@ double mlapo_mb_single_shape(int kind, int n, int chains, double* cycles_per_mma
   cudaEventCreate(&e1);
   auto run = [&](int iters) -> float {
     cudaEventRecord(e0);
-    kern<<<sms, 128, smem>>>(iters, n, chains, 777u);
+    kern<<<sms, 128, smem>>>(iters, m, n, chains, 777u);
     cudaEventRecord(e1);
     if (cudaEventSynchronize(e1) != cudaSuccess) return -1.f;
     float ms = 0.f;
@@ -321,7 +323,7 @@ double mlapo_mb_single_shape(int kind, int n, int chains, double* cycles_per_mma
   if (ms <= 0.f) return -4.0;
   const double mmas = 4.0 * iters;
   if (cycles_per_mma) *cycles_per_mma = ms * 1e-3 * (khz * 1e3) / mmas;
-  const double ops = 2.0 * 128 * n * (kind ? 16 : 32) * mmas * sms;
+  const double ops = 2.0 * m * n * (kind ? 16 : 32) * mmas * sms;
   return ops / (ms * 1e-3) / (kind ? 2.25e15 : 4.5e15);
 }
 

@@ -41,4 +41,12 @@ if hasattr(lib, "mlapo_mb_single_shape"):
             cyc = ctypes.c_double(0.0)
             frac = lib.mlapo_mb_single_shape(kind, n, 2, ctypes.byref(cyc))
             shapes[f"{kname} M128 N{n} K{32 if kind == 0 else 16}"] = {"frac_of_nominal_peak": round(frac, 3), "cycles_per_mma": round(cyc.value, 1)}
+    if hasattr(lib, "mlapo_mb_single_shape_m"):
+        lib.mlapo_mb_single_shape_m.restype = ctypes.c_double
+        lib.mlapo_mb_single_shape_m.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
+        for kind, kname in ((0, "i8"), (1, "bf16")):
+            for n in (128, 256):
+                cyc = ctypes.c_double(0.0)
+                frac = lib.mlapo_mb_single_shape_m(kind, 64, n, 2, ctypes.byref(cyc))
+                shapes[f"{kname} M64 N{n} K{32 if kind == 0 else 16}"] = {"frac_of_nominal_peak": round(frac, 3), "cycles_per_mma": round(cyc.value, 1)}
     print(json.dumps({"single_cta_mma_shapes": shapes}))
