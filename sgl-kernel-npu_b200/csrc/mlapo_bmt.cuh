@@ -74,22 +74,21 @@ bmt_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ 
       ptx::mbar_wait(ptx::smem_u32(full_bar + s), (i >> 2) & 1);
       __syncwarp();
       ptx::tc_fence_after();
-      if (lane == 0) {
+      {  // the converged warp issues (one elected lane inside the asm blocks): see sm100_ptx.cuh, umma_i8_elect
         const uint32_t a_base = ptx::smem_u32(smem + s * STAGE);
-        const uint32_t b_base = a_base + 2 * kTile16K;
+        const uint64_t da0 = ptx::make_smem_desc(a_base, 1024, 0);
+        const uint64_t db0 = ptx::make_smem_desc(a_base + 2 * kTile16K, 1024, kBmtAtom);  // MN-major: SBO 8 k-rows, LBO next 64 columns
         for (int t = 0; t < mt; ++t) {
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {  // 4 x UMMA_K(16) = 64
-            const uint64_t da = ptx::make_smem_desc(a_base + t * kTile16K + kk * kUmmaKBytes, 1024, 0);
-            const uint64_t db = ptx::make_smem_desc(b_base + kk * 2048, 1024, kBmtAtom);  // MN-major: SBO 8 k-rows, LBO next 64 columns
-            ptx::umma_f16(tmem + t * 128, da, db, idesc, (i > 0 || kk > 0) ? 1u : 0u);
-          }
+          for (int kk = 0; kk < 4; ++kk)  // 4 x UMMA_K(16) = 64
+            ptx::umma_f16_elect(tmem + t * 128, ptx::desc_advance(da0, t * kTile16K + kk * kUmmaKBytes), ptx::desc_advance(db0, kk * 2048), idesc,
+                                (i > 0 || kk > 0) ? 1u : 0u);
         }
-        ptx::umma_commit(ptx::smem_u32(empty_bar + s));
+        ptx::umma_commit_elect(ptx::smem_u32(empty_bar + s));
       }
       __syncwarp();
     }
-    if (lane == 0) ptx::umma_commit(ptx::smem_u32(done_bar));
+    ptx::umma_commit_elect(ptx::smem_u32(done_bar));
     __syncwarp();
   } else {
     const int quarter = warp & 3;

@@ -137,7 +137,7 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer (one thread)
+    // ------------------------------------------------------------------ MMA issuer (the converged warp; one elected lane issues)
     constexpr uint32_t idesc = ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, kBlockM, BN);
     uint32_t stage = 0, phase = 0;
     for (int i = 0; i < nkb; ++i) {
@@ -147,22 +147,23 @@ __device__ __forceinline__ void mm1_roles(const Mm1Ctx<MT, BN>& c, const CUtenso
       if (lane == 0) {
         if (i == 0) tl_mark(tl, 4);             // first stage landed
         if (i == nkb - 1) tl_mark(tl, 5);       // last stage landed
+      }
+      {
         const uint32_t a_base = ptx::smem_u32(smem + stage * STAGE_BYTES);
-        const uint32_t b_base = a_base + A_BYTES;
+        const uint64_t da0 = ptx::make_smem_desc(a_base, 1024, 0);
+        const uint64_t db0 = ptx::make_smem_desc(a_base + A_BYTES, 1024, 0);
         for (int m = 0; m < mt_valid; ++m) {
 #pragma unroll
-          for (int k = 0; k < kBlockKBytes / kUmmaKBytes; ++k) {
-            const uint64_t da = ptx::make_smem_desc(a_base + m * kTile16K + k * kUmmaKBytes, 1024, 0);
-            const uint64_t db = ptx::make_smem_desc(b_base + k * kUmmaKBytes, 1024, 0);
-            ptx::umma_i8(tmem_acc + m * BN, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
-          }
+          for (int k = 0; k < kBlockKBytes / kUmmaKBytes; ++k)
+            ptx::umma_i8_elect(tmem_acc + m * BN, ptx::desc_advance(da0, m * kTile16K + k * kUmmaKBytes), ptx::desc_advance(db0, k * kUmmaKBytes),
+                               idesc, (i > 0 || k > 0) ? 1u : 0u);
         }
-        ptx::umma_commit(ptx::smem_u32(empty_bar + stage));  // frees the smem slot when these MMAs retire
+        ptx::umma_commit_elect(ptx::smem_u32(empty_bar + stage));  // frees the smem slot when these MMAs retire
       }
       __syncwarp();
       if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }
-    if (lane == 0) ptx::umma_commit(ptx::smem_u32(done_bar));
+    ptx::umma_commit_elect(ptx::smem_u32(done_bar));
     __syncwarp();
   } else if (warp < 10) {
     // ------------------------------------------------------------------ epilogue: TMEM -> swizzled smem -> TMA store

@@ -110,20 +110,21 @@ mm1_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
         if (lane == 0) {
           if (i == 0) tl_mark(tl, 4);
           if (i == nkb - 1) tl_mark(tl, 5);
+        }
+        {  // the converged warp issues (one elected lane inside the asm blocks): see sm100_ptx.cuh, umma_i8_elect
           const uint32_t a_base = ptx::smem_u32(smem + stage * kM1PStageBytes);
-          const uint32_t b_base = a_base + kTile16K;
+          const uint64_t da0 = ptx::make_smem_desc(a_base, 1024, 0);
+          const uint64_t db0 = ptx::make_smem_desc(a_base + kTile16K, 1024, 0);
 #pragma unroll
-          for (int k = 0; k < kBlockKBytes / kUmmaKBytes; ++k) {
-            const uint64_t da = ptx::make_smem_desc(a_base + k * kUmmaKBytes, 1024, 0);
-            const uint64_t db = ptx::make_smem_desc(b_base + k * kUmmaKBytes, 1024, 0);
-            ptx::umma_i8_pair(tmem_acc, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
-          }
-          ptx::umma_commit_pair(ptx::smem_u32(empty_bar + stage));
+          for (int k = 0; k < kBlockKBytes / kUmmaKBytes; ++k)
+            ptx::umma_i8_pair_elect(tmem_acc, ptx::desc_advance(da0, k * kUmmaKBytes), ptx::desc_advance(db0, k * kUmmaKBytes), idesc,
+                                    (i > 0 || k > 0) ? 1u : 0u);
+          ptx::umma_commit_pair_elect(ptx::smem_u32(empty_bar + stage));
         }
         __syncwarp();
         if (++stage == kM1PStages) { stage = 0; phase ^= 1; }
       }
-      if (lane == 0) ptx::umma_commit_pair(ptx::smem_u32(done_bar));
+      ptx::umma_commit_pair_elect(ptx::smem_u32(done_bar));
       __syncwarp();
     }
   } else if (warp < 10) {

@@ -203,21 +203,22 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
       if (lane == 0) {
         if (kb == 0) tl_mark(tl, 4);
         if (kb == kQKBlocks - 1) tl_mark(tl, 5);
+      }
+      {  // issued by the converged warp (one elected lane inside the asm blocks): see sm100_ptx.cuh, umma_i8_elect
         const uint32_t a_base = ptx::smem_u32(smem + s * kQStageBytes);
-        const uint32_t b_base = a_base + 2 * kTile16K;
+        const uint64_t da0 = ptx::make_smem_desc(a_base, 1024, 0);
+        const uint64_t db0 = ptx::make_smem_desc(a_base + 2 * kTile16K, 1024, 0);
         for (int m = 0; m < num_mt; ++m) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const uint64_t da = ptx::make_smem_desc(a_base + m * kTile16K + k * kUmmaKBytes, 1024, 0);
-            const uint64_t db = ptx::make_smem_desc(b_base + k * kUmmaKBytes, 1024, 0);
-            ptx::umma_i8(tmem + m * 256, da, db, idesc2, (kb > 0 || k > 0) ? 1u : 0u);
-          }
+          for (int k = 0; k < 4; ++k)
+            ptx::umma_i8_elect(tmem + m * 256, ptx::desc_advance(da0, m * kTile16K + k * kUmmaKBytes), ptx::desc_advance(db0, k * kUmmaKBytes), idesc2,
+                               (kb > 0 || k > 0) ? 1u : 0u);
         }
-        ptx::umma_commit(ptx::smem_u32(empty_bar + s));
+        ptx::umma_commit_elect(ptx::smem_u32(empty_bar + s));
       }
       __syncwarp();
     }
-    if (lane == 0) ptx::umma_commit(ptx::smem_u32(mm2_done));
+    ptx::umma_commit_elect(ptx::smem_u32(mm2_done));
     __syncwarp();
     // absorb units (c, m): token tile m ping-pongs its own two TMEM buffers over this CTA's Wuk chunks
     for (int c = 0; c < CH; ++c) {
@@ -229,16 +230,14 @@ __device__ __forceinline__ void q_roles(const QCtx& c, const CUtensorMap* tm_a1,
         if (m == 0) ptx::mbar_wait(ptx::smem_u32(wuk_full + c), 0);
         __syncwarp();
         ptx::tc_fence_after();
-        if (lane == 0) {
-          const uint32_t b_base = ptx::smem_u32(smem + kQWukOff + c * 32768);
+        {
+          const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(smem + kQNopeOff + m * 2 * kTile16K), 1024, 0);
+          const uint64_t db0 = ptx::make_smem_desc(ptx::smem_u32(smem + kQWukOff + c * 32768), 1024, kTile16K);  // MN-major: SBO 8 k-rows, LBO next 64-col atom
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {  // 8 x UMMA_K(16) = 128
-            const uint32_t a_addr = ptx::smem_u32(smem + kQNopeOff + (m * 2 + (k >> 2)) * kTile16K) + (k & 3) * kUmmaKBytes;
-            const uint64_t da = ptx::make_smem_desc(a_addr, 1024, 0);
-            const uint64_t db = ptx::make_smem_desc(b_base + k * 2048, 1024, kTile16K);  // MN-major: SBO 8 k-rows, LBO next 64-col atom
-            ptx::umma_f16(tmem + m * 256 + (c & 1) * 128, da, db, idesc3, k > 0 ? 1u : 0u);
-          }
-          ptx::umma_commit(ptx::smem_u32(unit_full + ub));
+          for (int k = 0; k < 8; ++k)  // 8 x UMMA_K(16) = 128
+            ptx::umma_f16_elect(tmem + m * 256 + (c & 1) * 128, ptx::desc_advance(da0, (k >> 2) * kTile16K + (k & 3) * kUmmaKBytes),
+                                ptx::desc_advance(db0, k * 2048), idesc3, k > 0 ? 1u : 0u);
+          ptx::umma_commit_elect(ptx::smem_u32(unit_full + ub));
         }
         __syncwarp();
       }

@@ -153,21 +153,20 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
           ptx::mbar_wait(ptx::smem_u32(full_bar + s), (gk / kPStages) & 1);
           __syncwarp();
           ptx::tc_fence_after();
-          if (lane == 0) {
-            if (it == 0 && kb == 0) tl_mark(tl, 4);
+          if (lane == 0 && it == 0 && kb == 0) tl_mark(tl, 4);
+          {  // the converged warp issues (one elected lane inside the asm blocks): see sm100_ptx.cuh, umma_i8_elect
             const uint32_t a_base = ptx::smem_u32(smem + s * kPStageBytes);
-            const uint32_t b_base = a_base + kTile16K;
+            const uint64_t da0 = ptx::make_smem_desc(a_base, 1024, 0);
+            const uint64_t db0 = ptx::make_smem_desc(a_base + kTile16K, 1024, 0);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const uint64_t da = ptx::make_smem_desc(a_base + k * kUmmaKBytes, 1024, 0);
-              const uint64_t db = ptx::make_smem_desc(b_base + k * kUmmaKBytes, 1024, 0);
-              ptx::umma_i8_pair(tmem + par * 256, da, db, idesc2, (kb > 0 || k > 0) ? 1u : 0u);
-            }
-            ptx::umma_commit_pair(ptx::smem_u32(empty_bar + s));
+            for (int k = 0; k < 4; ++k)
+              ptx::umma_i8_pair_elect(tmem + par * 256, ptx::desc_advance(da0, k * kUmmaKBytes), ptx::desc_advance(db0, k * kUmmaKBytes), idesc2,
+                                      (kb > 0 || k > 0) ? 1u : 0u);
+            ptx::umma_commit_pair_elect(ptx::smem_u32(empty_bar + s));
           }
           __syncwarp();
         }
-        if (lane == 0) ptx::umma_commit_pair(ptx::smem_u32(mm2_done + par));
+        ptx::umma_commit_pair_elect(ptx::smem_u32(mm2_done + par));
         __syncwarp();
       }
     }
@@ -186,21 +185,19 @@ q_pair_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__
           ptx::mbar_wait(ptx::smem_u32(wuk_full + w), (gc / kPWukSlots) & 1);
           __syncwarp();
           ptx::tc_fence_after();
-          if (lane == 0) {
-            const uint32_t b_base = ptx::smem_u32(smem + kPWukOff + w * kTile16K);
+          {
+            const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(smem + kPNopeOff), 1024, 0);
+            const uint64_t db0 = ptx::make_smem_desc(ptx::smem_u32(smem + kPWukOff + w * kTile16K), 1024, 0);  // MN-major, one 64-column atom per CTA
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {  // 8 x UMMA_K(16) = 128
-              const uint32_t a_addr = ptx::smem_u32(smem + kPNopeOff + (k >> 2) * kTile16K) + (k & 3) * kUmmaKBytes;
-              const uint64_t da = ptx::make_smem_desc(a_addr, 1024, 0);
-              const uint64_t db = ptx::make_smem_desc(b_base + k * 2048, 1024, 0);  // MN-major, one 64-column atom per CTA
-              ptx::umma_f16_pair(tmem + par * 256 + (c & 1) * 128, da, db, idesc3, k > 0 ? 1u : 0u);
-            }
-            ptx::umma_commit_pair(ptx::smem_u32(wuk_empty + w));
-            ptx::umma_commit_pair(ptx::smem_u32(unit_full + par * 2 + (c & 1)));
+            for (int k = 0; k < 8; ++k)  // 8 x UMMA_K(16) = 128
+              ptx::umma_f16_pair_elect(tmem + par * 256 + (c & 1) * 128, ptx::desc_advance(da0, (k >> 2) * kTile16K + (k & 3) * kUmmaKBytes),
+                                       ptx::desc_advance(db0, k * 2048), idesc3, k > 0 ? 1u : 0u);
+            ptx::umma_commit_pair_elect(ptx::smem_u32(wuk_empty + w));
+            ptx::umma_commit_pair_elect(ptx::smem_u32(unit_full + par * 2 + (c & 1)));
           }
           __syncwarp();
         }
-        if (lane == 0) ptx::umma_commit_pair(ptx::smem_u32(qn_free));  // every MMA that reads the q_nope tiles has retired
+        ptx::umma_commit_pair_elect(ptx::smem_u32(qn_free));  // every MMA that reads the q_nope tiles has retired
         __syncwarp();
       }
     }

@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(128, 1) single_shape_kernel(int iters, int m, 
     reinterpret_cast<uint32_t*>(smem)[i] = kF16 ? ((x & 0x007F007Fu) | 0x3F803F80u) : x;
   }
   if (threadIdx.x == 0) {
-    ptx::mbar_init(ptx::smem_u32(&bar), 1);
+    ptx::mbar_init(ptx::smem_u32(&bar), chains == 3 ? 2 : 1);
     ptx::fence_mbar_init();
   }
   if (threadIdx.x < 32) {
@@ -146,23 +146,55 @@ __global__ void __launch_bounds__(128, 1) single_shape_kernel(int iters, int m, 
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = tmem_slot;
-  if (threadIdx.x == 0) {
+  // chains == 4: the whole of warp 0 runs the issue loop (no divergent branch around it); the asm block elects the issuing lane
+  if (chains == 4) {
+    if (threadIdx.x < 32) {
+      const uint32_t idesc = kF16 ? ptx::make_idesc(ptx::kCFmtF32, ptx::kFmtBF16, ptx::kFmtBF16, 0, 0, (uint32_t)m, (uint32_t)n)
+                                  : ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, (uint32_t)m, (uint32_t)n);
+      const uint64_t da0 = ptx::make_smem_desc(ptx::smem_u32(smem), 1024, 0), db0 = ptx::make_smem_desc(ptx::smem_u32(smem) + kATile, 1024, 0);
+      for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t da = da0 + 2 * k, db = db0 + 2 * k;   // +32 bytes = +2 in the descriptor's 16-byte address units
+          const uint32_t acc = it > 0 ? 1u : 0u;
+          if (kF16)
+            asm volatile("{\n\t.reg .pred p, q;\n\telect.sync _|q, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                         "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+          else
+            asm volatile("{\n\t.reg .pred p, q;\n\telect.sync _|q, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                         "@q tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+        }
+      }
+      if (ptx::elect_one()) ptx::umma_commit(ptx::smem_u32(&bar));
+      __syncwarp();
+    }
+    if (threadIdx.x == 0) ptx::mbar_wait(ptx::smem_u32(&bar), 0);
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < 32) ptx::tmem_dealloc(tmem, 512);
+    return;
+  }
+  // chains == 3: TWO issuing threads (warps 0 and 1), each with its own accumulator and half of the instructions
+  const bool two = chains == 3;
+  if (threadIdx.x == 0 || (two && threadIdx.x == 32)) {
+    const int who = threadIdx.x >> 5;
     const uint32_t idesc = kF16 ? ptx::make_idesc(ptx::kCFmtF32, ptx::kFmtBF16, ptx::kFmtBF16, 0, 0, (uint32_t)m, (uint32_t)n)
                                 : ptx::make_idesc(ptx::kCFmtS32, ptx::kFmtS8, ptx::kFmtS8, 0, 0, (uint32_t)m, (uint32_t)n);
     const uint32_t a_base = ptx::smem_u32(smem), b_base = a_base + kATile;
-    for (int it = 0; it < iters; ++it) {
+    const int my_iters = two ? iters / 2 : iters;
+    for (int it = 0; it < my_iters; ++it) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const uint64_t da = ptx::make_smem_desc(a_base + k * 32, 1024, 0);
         const uint64_t db = ptx::make_smem_desc(b_base + k * 32, 1024, 0);
-        const uint32_t d = tmem + (uint32_t)((it * 4 + k) % chains) * 256u;
+        const uint32_t d = tmem + (two ? (uint32_t)who * 256u : (uint32_t)((it * 4 + k) % chains) * 256u);
         if (kF16) ptx::umma_f16(d, da, db, idesc, it > 0 ? 1u : 0u);
         else ptx::umma_i8(d, da, db, idesc, it > 0 ? 1u : 0u);
       }
     }
     ptx::umma_commit(ptx::smem_u32(&bar));
-    ptx::mbar_wait(ptx::smem_u32(&bar), 0);
   }
+  if (threadIdx.x == 0) ptx::mbar_wait(ptx::smem_u32(&bar), 0);
   ptx::tc_fence_before();
   __syncthreads();
   if (threadIdx.x < 32) ptx::tmem_dealloc(tmem, 512);
@@ -299,7 +331,7 @@ double mlapo_mb_single_shape_m(int kind, int m, int n, int chains, double* cycle
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
-  if (n < 32 || n > 256 || (n % 32) || chains < 1 || chains > 2 || (m != 64 && m != 128)) return -1.0;
+  if (n < 32 || n > 256 || (n % 32) || chains < 1 || chains > 4 || (m != 64 && m != 128)) return -1.0;
   const int smem = kATile + kBTile;
   auto kern = kind ? single_shape_kernel<true> : single_shape_kernel<false>;
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -2.0;

@@ -49,4 +49,12 @@ if hasattr(lib, "mlapo_mb_single_shape"):
                 cyc = ctypes.c_double(0.0)
                 frac = lib.mlapo_mb_single_shape_m(kind, 64, n, 2, ctypes.byref(cyc))
                 shapes[f"{kname} M64 N{n} K{32 if kind == 0 else 16}"] = {"frac_of_nominal_peak": round(frac, 3), "cycles_per_mma": round(cyc.value, 1)}
+        for n in (128, 256):   # two issuing threads, each with its own accumulator (chains = 3 selects that form)
+            cyc = ctypes.c_double(0.0)
+            frac = lib.mlapo_mb_single_shape_m(0, 128, n, 3, ctypes.byref(cyc))
+            shapes[f"i8 M128 N{n} K32, two issuing warps"] = {"frac_of_nominal_peak": round(frac, 3), "cycles_per_mma": round(cyc.value, 1)}
+        for n in (128, 192, 256):   # the whole warp runs the issue loop, the asm block elects the lane (chains = 4 selects that form)
+            cyc = ctypes.c_double(0.0)
+            frac = lib.mlapo_mb_single_shape_m(0, 128, n, 4, ctypes.byref(cyc))
+            shapes[f"i8 M128 N{n} K32, convergent issue loop with elect inside"] = {"frac_of_nominal_peak": round(frac, 3), "cycles_per_mma": round(cyc.value, 1)}
     print(json.dumps({"single_cta_mma_shapes": shapes}))
