@@ -371,8 +371,8 @@ static int launch_impl(const MlapoParams* p, uint8_t* ws, const MlapoWorkspaceLa
                      reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
                      reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0, input_complete);
     } else {                 // prefill sizes: grid-stride over one resident wave, 4 independent loads in flight per thread
-      static std::atomic<int> occ[kMaxDevices];
-      e__ = launch_k(quant_hidden_kernel<T, 4>, dim3(num_sms() * resident_blocks(quant_hidden_kernel<T, 4>, 256, &occ[dev], 4)), dim3(256), 0, st, pdl,
+      static std::atomic<int> occ[kMaxDevices];   // U = 8 selects the form on pairs of vectors (32 bytes in, 16 out per thread and step)
+      e__ = launch_k(quant_hidden_kernel<T, 8>, dim3(num_sms() * resident_blocks(quant_hidden_kernel<T, 8>, 256, &occ[dev], 4)), dim3(256), 0, st, pdl,
                      reinterpret_cast<const T*>(p->hidden_state), a0, reinterpret_cast<const T*>(p->quant_scale0),
                      reinterpret_cast<const int8_t*>(p->quant_offset0), nvec, wp, tl0, input_complete);
     }

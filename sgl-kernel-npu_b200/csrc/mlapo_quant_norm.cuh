@@ -76,6 +76,46 @@ __device__ __forceinline__ void quant_vectors(const T* __restrict__ x, int8_t* _
   }
 }
 
+// The same on PAIRS of adjacent vectors (prefill sizes): 32 bytes in and 16 bytes out per thread and step — half the memory
+// instructions of quant_vectors for the same bytes.  n_vec8 must be even (hidden_dim is a multiple of 128).
+template <class T, int U>
+__device__ __forceinline__ void quant_vector_pairs(const T* __restrict__ x, int8_t* __restrict__ q, const QuantScale& qs, long long n_vec8,
+                                                   long long first, long long stride) {
+  const long long n_pair = n_vec8 >> 1;
+  for (long long i0 = first; i0 < n_pair; i0 += stride * U) {
+    uint4 v[U][2];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (i0 + u * stride < n_pair) ptx::ld_global_nc_v8(reinterpret_cast<const uint4*>(x) + 2 * (i0 + u * stride), v[u][0], v[u][1]);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i >= n_pair) break;
+      uint32_t w[4];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        float f[8];
+        unpack8<T>(v[u][h], f);
+        int r[8];
+        if (qs.fast) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float q0 = __fmul_rn(f[j], qs.rcp);
+            const float q1 = __fmaf_rn(__fmaf_rn(-q0, qs.s, f[j]), qs.rcp, q0);
+            r[j] = sat_i8(__fadd_rn(q1, qs.zp));
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) r[j] = sat_i8(__fadd_rn(__fdiv_rn(f[j], qs.s), qs.zp));
+        }
+        w[2 * h] = pack4_i8(r[0], r[1], r[2], r[3]);
+        w[2 * h + 1] = pack4_i8(r[4], r[5], r[6], r[7]);
+      }
+      ptx::st_global_v4(q + i * 16, w[0], w[1], w[2], w[3]);
+    }
+  }
+}
+
 // The call's three weight tensors (70 MB at 128 heads) fit the 126 MB L2.  The first kernel of the call asks for all of them
 // before it waits for its predecessor, so HBM streams weights while quant / MM1 / norm — which move little data — run,
 // and the weight loads of MM1 and of the q path find L2 lines (or fills already in flight) instead of starting at DRAM.
@@ -113,7 +153,8 @@ __global__ void quant_hidden_kernel(const T* __restrict__ x, int8_t* __restrict_
   QuantScale qs;
   qs.load(scale, offset);
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 14);
-  quant_vectors<T, U>(x, q, qs, n_vec8, blockIdx.x * (long long)blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
+  if (U == 8) quant_vector_pairs<T, 4>(x, q, qs, n_vec8, blockIdx.x * (long long)blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
+  else quant_vectors<T, U>(x, q, qs, n_vec8, blockIdx.x * (long long)blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
   if (threadIdx.x == 0 && blockIdx.x < 4096) tl_mark_global(tl, 15);
   if (input_complete && blockIdx.x == gridDim.x - 1) ptx::griddep_wait();
 }
